@@ -1,0 +1,229 @@
+/* nsdg_gpu.h -- C ABI of the B200 (sm_100a) hot path of neXtSIM_DG.
+ *
+ * Plain C, plain pointers and sizes, int status codes; nothing throws across this boundary
+ * and no torch/NCCL/CUDA type appears in a signature.  All floating point is FP64.
+ * Host arrays are borrowed for the duration of the call only; device state is owned by the
+ * context and stays resident in HBM between calls.
+ *
+ * Which reference interface each group replaces (paths relative to the reference tree):
+ *   thermo_*    the body of DevStep::iterate, core/src/DevStep.cpp:14-23, i.e. per cell
+ *               IPhysics1d::updateDerivedData (physics/src/modules/include/IPhysics1d.hpp:33-45),
+ *               NextsimPhysics::calculate (physics/src/modules/NextsimPhysics.cpp:116-131) incl.
+ *               ThermoIce0::calculate (physics/src/modules/ThermoIce0.cpp:34-133) and
+ *               PrognosticData::updateAndIntegrate (core/src/PrognosticData.cpp:63-71);
+ *               upload/download replace the AoS gather/scatter of core/src/DevGridIO.cpp:101-138,
+ *               160-201 (x outer, y inner, tice layer-fastest).
+ *   dyn_*       DG transport and the mEVP sub-cycle.  NOT IN THE REFERENCE SNAPSHOT ("dynamics" is
+ *               commented out of its build, CMakeLists.txt:43-46): these entry points follow
+ *               the discretisation stated in DESIGN.md; parity is against oracle/ only
+ *               ("parity unpinned against draenog/nextsimdg").
+ *   comm_*      strip decomposition halo exchange (no reference counterpart: the reference is
+ *               single-process).
+ */
+#ifndef NSDG_GPU_H
+#define NSDG_GPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NSDG_ABI_VERSION 1
+
+typedef struct nsdg_ctx nsdg_ctx;
+
+enum nsdg_status {
+    NSDG_OK = 0,
+    NSDG_EINVAL = -1, /* bad argument / unknown module combination (no fallback) */
+    NSDG_ECUDA = -2, /* CUDA runtime error (sticky per context) */
+    NSDG_ENOMEM = -3,
+    NSDG_ESTATE = -4, /* call order violated (e.g. step before init) */
+    NSDG_ECOMM = -5 /* NCCL error */
+};
+
+/* ---- module selectors: same names as the [Modules] section values of the reference
+ * (core/src/modules/modules.json, physics/src/modules/modules.json) ---- */
+enum nsdg_albedo_kind { NSDG_ALBEDO_SMU = 0, NSDG_ALBEDO_SMU2 = 1, NSDG_ALBEDO_CCSM = 2 };
+enum nsdg_freezing_kind { NSDG_FREEZING_LINEAR = 0, NSDG_FREEZING_UNESCO = 1 };
+enum nsdg_ocean_flux_kind { NSDG_OCEANFLUX_BASIC = 0 };
+
+/* One parameter set per context; the reference keeps these as process-global statics
+ * (NextsimPhysics.cpp:26-39,76-82; ThermoIce0.cpp:19-32; HiblerConcentration.cpp:16-30;
+ * CCSMIceAlbedo.cpp:16-42).  Defaults = the reference's defaults. */
+typedef struct nsdg_thermo_params {
+    double drag_ocean_q; /* nextsim_thermo.drag_ocean_q = 1.5e-3 */
+    double drag_ocean_t; /* nextsim_thermo.drag_ocean_t = 0.83e-3 */
+    double drag_ice_t; /* nextsim_thermo.drag_ice_t   = 1.3e-3 */
+    double albedo_w; /* nextsim_thermo.albedoW      = 0.07 */
+    double i0; /* nextsim_thermo.I_0          = 0.17 */
+    double min_conc; /* nextsim_thermo.min_conc     = 1e-12 */
+    double min_thick; /* nextsim_thermo.min_thick    = 0.01 */
+    double ks; /* thermoice0.ks               = 0.3096 */
+    double h0; /* Hibler.h0                   = 0.25 */
+    double phi_m; /* Hibler.phiM                 = 0.5 */
+    double ccsm_ice_albedo; /* CCSMIceAlbedo.iceAlbedo     = 0.538 */
+    double ccsm_snow_albedo; /* CCSMIceAlbedo.snowAlbedo    = 0.8256 */
+    int32_t flooding; /* thermoice0.flooding         = 1 */
+    int32_t albedo_kind; /* nsdg_albedo_kind, default SMU (first listed) */
+    int32_t freezing_kind; /* nsdg_freezing_kind, default LINEAR */
+    int32_t ocean_flux_kind; /* nsdg_ocean_flux_kind */
+} nsdg_thermo_params;
+
+/* Thermodynamics field ids for nsdg_thermo_field_ptr */
+enum nsdg_thermo_field {
+    NSDG_TF_HICE = 0,
+    NSDG_TF_CICE,
+    NSDG_TF_HSNOW,
+    NSDG_TF_SST,
+    NSDG_TF_SSS,
+    NSDG_TF_TICE0,
+    NSDG_TF_TAIR,
+    NSDG_TF_TDEW,
+    NSDG_TF_SLP,
+    NSDG_TF_QSW,
+    NSDG_TF_QLW,
+    NSDG_TF_MLD,
+    NSDG_TF_SNOWFALL,
+    NSDG_TF_WIND,
+    NSDG_TF_NEWICE, /* hidden persistent state m_newice, NextsimPhysics.hpp:257 */
+    NSDG_TF_COUNT
+};
+
+/* Per-cell diagnostics of the last step, in this order (13 arrays):
+ * rho, sphuma, sphumw, sphumi, cspec, tau   (PhysicsData.hpp:79-85)
+ * qia, qio, qow, subl, dqdt, hifroms, tsurf_new (NextsimPhysics.hpp:219-245) */
+#define NSDG_THERMO_NDIAG 13
+
+/* ---- dynamics ---- */
+enum nsdg_bc_kind {
+    NSDG_BC_PERIODIC = 0, /* doubly periodic */
+    NSDG_BC_BOX = 1 /* closed box: u=v=0 on the node lines i==0 and j==0 of the periodic
+                       topology (== walls of an nx*ny-cell box), no flux through them */
+};
+
+typedef struct nsdg_mevp_params {
+    double rho_ice; /* 900 */
+    double rho_atm; /* 1.3 */
+    double rho_ocean; /* 1026 */
+    double c_atm; /* 1.2e-3 */
+    double c_ocean; /* 5.5e-3 */
+    double f_coriolis; /* 1.46e-4 */
+    double p_star; /* 27.5e3 */
+    double c_star; /* 20 (C in P = P* H exp(-C(1-A))) */
+    double ellipse_e; /* 2 */
+    double delta_min; /* 2e-9 */
+    double alpha; /* 1500 */
+    double beta; /* 1500 */
+    double h_min; /* lower bound of nodal thickness in the momentum mass, 1e-3 */
+    int32_t bc; /* nsdg_bc_kind */
+    int32_t _pad;
+} nsdg_mevp_params;
+
+/* Dynamics field ids.  DG fields have ncomp in {1,3,6} coefficients per cell, stored
+ * component-major: a[c][j][i] (i fastest).  Basis on the reference square, SURVEY 8a' a17:
+ *   1, x-1/2, y-1/2, (x-1/2)^2-1/12, (y-1/2)^2-1/12, (x-1/2)(y-1/2).
+ * CG1 node (i,j) is the lower-left corner of cell (i,j); node arrays are [j][i], periodic. */
+enum nsdg_dyn_field {
+    NSDG_DF_H = 0, /* DG, ncomp      ice thickness */
+    NSDG_DF_A, /* DG, ncomp      ice concentration */
+    NSDG_DF_U, /* node           ice velocity x */
+    NSDG_DF_V, /* node           ice velocity y */
+    NSDG_DF_S11, /* DG1 (3 comps)  stress */
+    NSDG_DF_S12,
+    NSDG_DF_S22,
+    NSDG_DF_UATM, /* node           10 m wind */
+    NSDG_DF_VATM,
+    NSDG_DF_UOCN, /* node           ocean surface current */
+    NSDG_DF_VOCN,
+    NSDG_DF_COUNT
+};
+
+typedef struct nsdg_dyn_config {
+    int64_t nx; /* cells in x (fast index), global == local */
+    int64_t ny_global; /* cells in y over all ranks */
+    int64_t ny_local; /* rows of this rank's strip */
+    int64_t j0; /* global index of this strip's first row */
+    double hx, hy; /* cell size [m] */
+    int32_t ncomp; /* 1, 3 or 6: dG0 / dG1 / dG2 tracers */
+    int32_t rk_order; /* 0 = match ncomp (1->RK1, 3->Heun RK2, 6->SSP-RK3), else 1,2,3 */
+    int32_t limiter; /* 0 off (default), 1 bounds-preserving rescaling of higher moments */
+    int32_t _pad;
+} nsdg_dyn_config;
+
+/* ---- context ---- */
+int nsdg_abi_version(void);
+int nsdg_create(nsdg_ctx** out, int device);
+int nsdg_destroy(nsdg_ctx* ctx);
+const char* nsdg_last_error(const nsdg_ctx* ctx);
+int nsdg_synchronize(nsdg_ctx* ctx);
+/* number of kernels this context has launched since creation (claim for bench "gpu_launches") */
+int64_t nsdg_launch_count(const nsdg_ctx* ctx);
+/* time the work submitted between the two calls with CUDA events on the context's stream */
+int nsdg_timer_start(nsdg_ctx* ctx);
+int nsdg_timer_stop(nsdg_ctx* ctx, double* elapsed_ms);
+
+/* ---- column thermodynamics ---- */
+void nsdg_thermo_default_params(nsdg_thermo_params* p);
+int nsdg_thermo_init(nsdg_ctx* ctx, int64_t ncells, int32_t nlayers);
+int nsdg_thermo_set_params(nsdg_ctx* ctx, const nsdg_thermo_params* p);
+/* host -> device; tice is [ncells][nlayers] layer-fastest, only layer 0 is kept */
+int nsdg_thermo_upload_prognostic(nsdg_ctx* ctx, const double* hice, const double* cice,
+    const double* hsnow, const double* sst, const double* sss, const double* tice);
+int nsdg_thermo_upload_forcing(nsdg_ctx* ctx, const double* tair, const double* tdew,
+    const double* slp, const double* qsw, const double* qlw, const double* mld,
+    const double* snowfall, const double* wind);
+/* newice is zeroed by init; these two exist for checkpoint/resume of the hidden state */
+int nsdg_thermo_upload_newice(nsdg_ctx* ctx, const double* newice);
+int nsdg_thermo_download_newice(nsdg_ctx* ctx, double* newice);
+/* nsteps sweeps of DevStep::iterate(dt) over all cells, state stays on the device */
+int nsdg_thermo_step(nsdg_ctx* ctx, double dt, int32_t nsteps);
+/* same, additionally storing the NSDG_THERMO_NDIAG diagnostics of the last sweep */
+int nsdg_thermo_step_diag(nsdg_ctx* ctx, double dt, int32_t nsteps);
+int nsdg_thermo_download_prognostic(nsdg_ctx* ctx, double* hice, double* cice, double* hsnow,
+    double* sst, double* sss, double* tice);
+/* diag: [NSDG_THERMO_NDIAG][ncells] */
+int nsdg_thermo_download_diagnostics(nsdg_ctx* ctx, double* diag);
+/* zero-copy access for callers that already hold device data (bench, coupling) */
+int nsdg_thermo_field_ptr(nsdg_ctx* ctx, int32_t field, void** device_ptr);
+/* one call, host buffers in and out: upload prognostic+forcing, nsteps sweeps, download */
+int nsdg_thermo_run_host(nsdg_ctx* ctx, double dt, int32_t nsteps, double* hice, double* cice,
+    double* hsnow, const double* sst, const double* sss, double* tice, const double* tair,
+    const double* tdew, const double* slp, const double* qsw, const double* qlw,
+    const double* mld, const double* snowfall, const double* wind);
+
+/* ---- dynamics: DG transport + mEVP ---- */
+void nsdg_mevp_default_params(nsdg_mevp_params* p);
+int nsdg_dyn_init(nsdg_ctx* ctx, const nsdg_dyn_config* cfg);
+int nsdg_dyn_set_mevp_params(nsdg_ctx* ctx, const nsdg_mevp_params* p);
+/* interior of this rank's strip, host layout [ncomp_of_field][ny_local][nx] */
+int nsdg_dyn_upload(nsdg_ctx* ctx, int32_t field, const double* host);
+int nsdg_dyn_download(nsdg_ctx* ctx, int32_t field, double* host);
+int nsdg_dyn_field_ncomp(const nsdg_ctx* ctx, int32_t field);
+/* device pointer of component 0, row 0 of the padded array (ny_local+2 rows, row 0 and
+ * ny_local+1 are ghost rows); pitch_elems = nx, comp_stride = (ny_local+2)*nx */
+int nsdg_dyn_field_ptr(nsdg_ctx* ctx, int32_t field, void** device_ptr);
+/* advance tracer `field` (NSDG_DF_H or NSDG_DF_A) by dt with the current U,V */
+int nsdg_transport_step(nsdg_ctx* ctx, int32_t field, double dt);
+/* advance H and A together (shared velocity reads) */
+int nsdg_transport_step_HA(nsdg_ctx* ctx, double dt);
+/* nsub mEVP sub-iterations for a momentum step of length dt (U,V,S updated in place) */
+int nsdg_mevp_step(nsdg_ctx* ctx, double dt, int32_t nsub);
+/* the north-star unit: transport of H,A with the current velocity, then the mEVP sub-cycle */
+int nsdg_dyn_step(nsdg_ctx* ctx, double dt, int32_t nsub);
+/* sum over this rank's cells of the mean coefficient times cell area (mass diagnostic) */
+int nsdg_dyn_mass(nsdg_ctx* ctx, int32_t field, double* mass);
+
+/* ---- strip decomposition (one process per GPU) ---- */
+#define NSDG_COMM_ID_BYTES 128
+int nsdg_comm_get_unique_id(void* id_out /* NSDG_COMM_ID_BYTES */);
+int nsdg_comm_init(nsdg_ctx* ctx, const void* id, int32_t rank, int32_t nranks);
+int nsdg_comm_rank(const nsdg_ctx* ctx, int32_t* rank, int32_t* nranks);
+/* bytes sent per rank by halo exchanges since creation (diagnostic) */
+int64_t nsdg_comm_bytes_sent(const nsdg_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NSDG_GPU_H */
