@@ -1,0 +1,78 @@
+// Internal definitions shared by the translation units of libnsdg_gpu.so.
+// Nothing here is part of the C ABI (include/nsdg_gpu.h).
+#pragma once
+#include "../../include/nsdg_gpu.h"
+#include <cuda_runtime.h>
+#include <cstdio>
+#include <string>
+
+struct DynState; // dyn.cu
+struct CommState; // comm.cu
+
+struct ThermoState {
+    int64_t n = 0;
+    int32_t nlayers = 1;
+    double* fields[NSDG_TF_COUNT] = {};
+    double* diag = nullptr; // [NSDG_THERMO_NDIAG][n], allocated on first diag step
+    double* stage = nullptr; // device staging for tice upload/download [n*nlayers]
+    nsdg_thermo_params params;
+    bool have_prog = false, have_forcing = false;
+};
+
+struct nsdg_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr; // compute
+    cudaStream_t comm_stream = nullptr; // halo exchange
+    cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
+    int64_t launches = 0;
+    int sm_count = 148;
+    std::string error;
+    bool cuda_failed = false; // sticky
+    ThermoState* thermo = nullptr;
+    DynState* dyn = nullptr;
+    CommState* comm = nullptr;
+};
+
+int nsdg_fail(nsdg_ctx* ctx, int code, const char* fmt, ...);
+
+#define NSDG_CUDA(ctx, expr)                                                                      \
+    do {                                                                                          \
+        cudaError_t _e = (expr);                                                                  \
+        if (_e != cudaSuccess) {                                                                  \
+            (ctx)->cuda_failed = true;                                                            \
+            return nsdg_fail((ctx), NSDG_ECUDA, "%s failed at %s:%d: %s", #expr, __FILE__,        \
+                __LINE__, cudaGetErrorString(_e));                                                \
+        }                                                                                         \
+    } while (0)
+
+#define NSDG_REQUIRE(ctx, cond, code, ...)                                                        \
+    do {                                                                                          \
+        if (!(cond))                                                                              \
+            return nsdg_fail((ctx), (code), __VA_ARGS__);                                         \
+    } while (0)
+
+#define NSDG_ENTER(ctx)                                                                           \
+    do {                                                                                          \
+        if (!(ctx))                                                                               \
+            return NSDG_EINVAL;                                                                   \
+        if ((ctx)->cuda_failed)                                                                   \
+            return NSDG_ECUDA;                                                                    \
+        cudaError_t _e = cudaSetDevice((ctx)->device);                                            \
+        if (_e != cudaSuccess) {                                                                  \
+            (ctx)->cuda_failed = true;                                                            \
+            return nsdg_fail((ctx), NSDG_ECUDA, "cudaSetDevice(%d): %s", (ctx)->device,           \
+                cudaGetErrorString(_e));                                                          \
+        }                                                                                         \
+    } while (0)
+
+// after a kernel launch
+#define NSDG_LAUNCHED(ctx)                                                                        \
+    do {                                                                                          \
+        (ctx)->launches++;                                                                        \
+        NSDG_CUDA((ctx), cudaGetLastError());                                                     \
+    } while (0)
+
+// teardown hooks implemented by the owning translation unit
+void nsdg_thermo_free(nsdg_ctx* ctx);
+void nsdg_dyn_free(nsdg_ctx* ctx);
+void nsdg_comm_free(nsdg_ctx* ctx);

@@ -1,0 +1,399 @@
+// Dynamics state management and time-step orchestration (transport RK stages, mEVP sub-cycle,
+// halo exchanges of the strip decomposition).  See include/nsdg_gpu.h and dyn.h.
+#include "dyn.h"
+#include <algorithm>
+#include <cstring>
+
+namespace {
+
+int field_ncomp(const DynState* d, int field)
+{
+    switch (field) {
+    case NSDG_DF_H:
+    case NSDG_DF_A:
+        return d->nc;
+    case NSDG_DF_S11:
+    case NSDG_DF_S12:
+    case NSDG_DF_S22:
+        return 3;
+    default:
+        return 1;
+    }
+}
+
+int alloc_planes(nsdg_ctx* ctx, double** p, int nplanes)
+{
+    DynState* d = ctx->dyn;
+    size_t bytes = sizeof(double) * (size_t)nplanes * d->plane;
+    NSDG_CUDA(ctx, cudaMalloc(p, bytes));
+    NSDG_CUDA(ctx, cudaMemsetAsync(*p, 0, bytes, ctx->stream));
+    return NSDG_OK;
+}
+
+__global__ void mass_kernel(const double* mean, int64_t nx, int64_t nyl, double* out)
+{
+    double s = 0.;
+    const int64_t n = nx * nyl;
+    for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < n; q += (int64_t)gridDim.x * blockDim.x)
+        s += mean[nx + q]; // interior starts at row 1
+    for (int off = 16; off > 0; off >>= 1)
+        s += __shfl_down_sync(0xffffffffu, s, off);
+    __shared__ double part[32];
+    if ((threadIdx.x & 31) == 0)
+        part[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        s = (threadIdx.x < (blockDim.x >> 5)) ? part[threadIdx.x] : 0.;
+        for (int off = 16; off > 0; off >>= 1)
+            s += __shfl_down_sync(0xffffffffu, s, off);
+        if (threadIdx.x == 0)
+            atomicAdd(out, s);
+    }
+}
+
+PlaneSet planes_of(DynState* d, double* base, int ncomp)
+{
+    PlaneSet ps;
+    ps.n = 0;
+    for (int c = 0; c < ncomp; ++c)
+        ps.p[ps.n++] = base + (size_t)c * d->plane;
+    return ps;
+}
+void append(PlaneSet& ps, DynState* d, double* base, int ncomp)
+{
+    for (int c = 0; c < ncomp; ++c)
+        ps.p[ps.n++] = base + (size_t)c * d->plane;
+}
+
+// one RK time step for nfields tracers (phi[f] updated in place)
+int transport_fields(nsdg_ctx* ctx, int nfields, double** phi, double** s1, double** s2,
+    const double* lo, const double* hi, double dt)
+{
+    DynState* d = ctx->dyn;
+    const bool multi = nsdg_comm_active(ctx);
+    const int64_t r0 = 1, r1 = d->nyl + 1;
+    int rc;
+    auto halo = [&](double** arr) -> int {
+        if (!multi)
+            return NSDG_OK;
+        PlaneSet ps;
+        ps.n = 0;
+        for (int f = 0; f < nfields; ++f)
+            append(ps, d, arr[f], d->nc);
+        return nsdg_halo_exchange(ctx, ps, 3);
+    };
+    auto limit = [&](double** arr) -> int {
+        if (!d->cfg.limiter)
+            return NSDG_OK;
+        for (int f = 0; f < nfields; ++f) {
+            int r = nsdg_transport_limit(ctx, arr[f], lo[f], hi[f]);
+            if (r)
+                return r;
+        }
+        return NSDG_OK;
+    };
+    if (multi) { // velocity ghosts (upper node row is read by the top cell row)
+        PlaneSet ps;
+        ps.n = 0;
+        ps.p[ps.n++] = d->f[NSDG_DF_U];
+        ps.p[ps.n++] = d->f[NSDG_DF_V];
+        if ((rc = nsdg_halo_exchange(ctx, ps, 2)))
+            return rc;
+    }
+    // stage 1: s1 = phi + dt L(phi)
+    if ((rc = halo(phi)) || (rc = nsdg_transport_stage(ctx, nfields, phi, nullptr, s1, 0., 1., dt, r0, r1))
+        || (rc = limit(s1)))
+        return rc;
+    if (d->rk == 1) {
+        // copy the interior of every component (rows 1..nyl are contiguous within a plane)
+        for (int f = 0; f < nfields; ++f)
+            for (int c = 0; c < d->nc; ++c)
+                NSDG_CUDA(ctx, cudaMemcpyAsync(phi[f] + (size_t)c * d->plane + d->nx,
+                                   s1[f] + (size_t)c * d->plane + d->nx,
+                                   sizeof(double) * (size_t)d->nx * d->nyl, cudaMemcpyDeviceToDevice,
+                                   ctx->stream));
+        return NSDG_OK;
+    }
+    if (d->rk == 2) { // Heun: phi = 1/2 phi + 1/2 (s1 + dt L(s1))
+        if ((rc = halo(s1)) || (rc = nsdg_transport_stage(ctx, nfields, s1, phi, phi, 0.5, 0.5, dt, r0, r1))
+            || (rc = limit(phi)))
+            return rc;
+        return NSDG_OK;
+    }
+    // SSP-RK3: s2 = 3/4 phi + 1/4 (s1 + dt L(s1)); phi = 1/3 phi + 2/3 (s2 + dt L(s2))
+    if ((rc = halo(s1)) || (rc = nsdg_transport_stage(ctx, nfields, s1, phi, s2, 0.75, 0.25, dt, r0, r1))
+        || (rc = limit(s2)))
+        return rc;
+    if ((rc = halo(s2))
+        || (rc = nsdg_transport_stage(ctx, nfields, s2, phi, phi, 1. / 3., 2. / 3., dt, r0, r1))
+        || (rc = limit(phi)))
+        return rc;
+    return NSDG_OK;
+}
+
+int mevp_cycle(nsdg_ctx* ctx, double dt, int nsub)
+{
+    DynState* d = ctx->dyn;
+    const bool multi = nsdg_comm_active(ctx);
+    int rc;
+    if (multi) {
+        // lower ghost rows of H, A (strength and nodal means), both ghost rows of u, v, lower
+        // ghost row of S (it then evolves redundantly, bit-identical to the owner's copy)
+        PlaneSet ps = planes_of(d, d->f[NSDG_DF_H], d->nc);
+        append(ps, d, d->f[NSDG_DF_A], d->nc);
+        if ((rc = nsdg_halo_exchange(ctx, ps, 1)))
+            return rc;
+        ps = planes_of(d, d->f[NSDG_DF_S11], 3);
+        append(ps, d, d->f[NSDG_DF_S12], 3);
+        append(ps, d, d->f[NSDG_DF_S22], 3);
+        if ((rc = nsdg_halo_exchange(ctx, ps, 1)))
+            return rc;
+        ps.n = 0;
+        ps.p[ps.n++] = d->f[NSDG_DF_U];
+        ps.p[ps.n++] = d->f[NSDG_DF_V];
+        if ((rc = nsdg_halo_exchange(ctx, ps, 3)))
+            return rc;
+    }
+    if ((rc = nsdg_mevp_prepare(ctx)))
+        return rc;
+    double *u = d->f[NSDG_DF_U], *v = d->f[NSDG_DF_V], *u2 = d->u2, *v2 = d->v2;
+    const int64_t s0 = multi ? 0 : 1;
+    for (int p = 0; p < nsub; ++p) {
+        if ((rc = nsdg_mevp_stress(ctx, u, v, s0, d->nyl + 1)))
+            return rc;
+        if ((rc = nsdg_mevp_velocity(ctx, dt, u, v, u2, v2, 1, d->nyl + 1)))
+            return rc;
+        if (multi) {
+            PlaneSet ps;
+            ps.n = 0;
+            ps.p[ps.n++] = u2;
+            ps.p[ps.n++] = v2;
+            if ((rc = nsdg_halo_exchange(ctx, ps, 3)))
+                return rc;
+        }
+        std::swap(u, u2);
+        std::swap(v, v2);
+    }
+    d->f[NSDG_DF_U] = u;
+    d->f[NSDG_DF_V] = v;
+    d->u2 = u2;
+    d->v2 = v2;
+    return NSDG_OK;
+}
+
+} // namespace
+
+void nsdg_dyn_free(nsdg_ctx* ctx)
+{
+    DynState* d = ctx->dyn;
+    if (!d)
+        return;
+    for (int q = 0; q < NSDG_DF_COUNT; ++q)
+        cudaFree(d->f[q]);
+    for (int f = 0; f < 2; ++f) {
+        cudaFree(d->stage1[f]);
+        cudaFree(d->stage2[f]);
+    }
+    double* w[] = { d->pg, d->hn, d->an, d->un, d->vn, d->u2, d->v2, d->taux, d->tauy, d->scratch,
+        d->send_lo, d->send_hi, d->recv_lo, d->recv_hi };
+    for (double* p : w)
+        cudaFree(p);
+    if (d->host_stage)
+        cudaFreeHost(d->host_stage);
+    delete d;
+    ctx->dyn = nullptr;
+}
+
+extern "C" {
+
+void nsdg_mevp_default_params(nsdg_mevp_params* p)
+{
+    if (!p)
+        return;
+    p->rho_ice = 900.;
+    p->rho_atm = 1.3;
+    p->rho_ocean = 1026.;
+    p->c_atm = 1.2e-3;
+    p->c_ocean = 5.5e-3;
+    p->f_coriolis = 1.46e-4;
+    p->p_star = 27.5e3;
+    p->c_star = 20.;
+    p->ellipse_e = 2.;
+    p->delta_min = 2e-9;
+    p->alpha = 1500.;
+    p->beta = 1500.;
+    p->h_min = 1e-3;
+    p->bc = NSDG_BC_PERIODIC;
+    p->_pad = 0;
+}
+
+int nsdg_dyn_init(nsdg_ctx* ctx, const nsdg_dyn_config* cfg)
+{
+    NSDG_ENTER(ctx);
+    NSDG_REQUIRE(ctx, cfg, NSDG_EINVAL, "cfg is null");
+    NSDG_REQUIRE(ctx, cfg->nx >= 2 && cfg->ny_local >= 2 && cfg->ny_global >= cfg->ny_local
+            && cfg->j0 >= 0 && cfg->j0 + cfg->ny_local <= cfg->ny_global,
+        NSDG_EINVAL, "bad grid: nx=%lld ny_local=%lld ny_global=%lld j0=%lld", (long long)cfg->nx,
+        (long long)cfg->ny_local, (long long)cfg->ny_global, (long long)cfg->j0);
+    NSDG_REQUIRE(ctx, cfg->hx > 0 && cfg->hy > 0, NSDG_EINVAL, "cell sizes must be positive");
+    NSDG_REQUIRE(ctx, cfg->ncomp == 1 || cfg->ncomp == 3 || cfg->ncomp == 6, NSDG_EINVAL,
+        "ncomp must be 1 (dG0), 3 (dG1) or 6 (dG2), got %d", cfg->ncomp);
+    NSDG_REQUIRE(ctx, cfg->rk_order >= 0 && cfg->rk_order <= 3, NSDG_EINVAL, "rk_order in 0..3");
+    const bool multi = nsdg_comm_active(ctx);
+    NSDG_REQUIRE(ctx, multi || cfg->ny_local == cfg->ny_global, NSDG_EINVAL,
+        "a strip (ny_local < ny_global) needs nsdg_comm_init before nsdg_dyn_init");
+    nsdg_dyn_free(ctx);
+    DynState* d = new DynState;
+    ctx->dyn = d;
+    d->cfg = *cfg;
+    nsdg_mevp_default_params(&d->mp);
+    d->nx = cfg->nx;
+    d->nyl = cfg->ny_local;
+    d->rows = d->nyl + 2;
+    d->plane = d->rows * d->nx;
+    d->nc = cfg->ncomp;
+    d->rk = cfg->rk_order ? cfg->rk_order : (d->nc == 1 ? 1 : (d->nc == 3 ? 2 : 3));
+    d->wrap = !multi;
+    int rc;
+    for (int q = 0; q < NSDG_DF_COUNT; ++q) {
+        d->ncomp[q] = field_ncomp(d, q);
+        if ((rc = alloc_planes(ctx, &d->f[q], d->ncomp[q])))
+            return rc;
+    }
+    for (int f = 0; f < 2; ++f) {
+        if ((rc = alloc_planes(ctx, &d->stage1[f], d->nc)))
+            return rc;
+        if (d->rk == 3 && (rc = alloc_planes(ctx, &d->stage2[f], d->nc)))
+            return rc;
+    }
+    double** one[] = { &d->hn, &d->an, &d->un, &d->vn, &d->u2, &d->v2, &d->taux, &d->tauy };
+    for (double** p : one)
+        if ((rc = alloc_planes(ctx, p, 1)))
+            return rc;
+    if ((rc = alloc_planes(ctx, &d->pg, 4)))
+        return rc;
+    NSDG_CUDA(ctx, cudaMalloc(&d->scratch, 64));
+    if (multi) {
+        d->halo_capacity = 12 * (size_t)d->nx;
+        double** hb[] = { &d->send_lo, &d->send_hi, &d->recv_lo, &d->recv_hi };
+        for (double** p : hb)
+            NSDG_CUDA(ctx, cudaMalloc(p, sizeof(double) * d->halo_capacity));
+    }
+    NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return NSDG_OK;
+}
+
+int nsdg_dyn_set_mevp_params(nsdg_ctx* ctx, const nsdg_mevp_params* p)
+{
+    NSDG_ENTER(ctx);
+    NSDG_REQUIRE(ctx, ctx->dyn, NSDG_ESTATE, "nsdg_dyn_init has not been called");
+    NSDG_REQUIRE(ctx, p, NSDG_EINVAL, "params is null");
+    NSDG_REQUIRE(ctx, p->bc == NSDG_BC_PERIODIC || p->bc == NSDG_BC_BOX, NSDG_EINVAL,
+        "unknown boundary condition %d", p->bc);
+    NSDG_REQUIRE(ctx, p->alpha > 0 && p->beta >= 0 && p->ellipse_e > 0 && p->delta_min > 0,
+        NSDG_EINVAL, "alpha, ellipse_e, delta_min must be positive");
+    ctx->dyn->mp = *p;
+    return NSDG_OK;
+}
+
+int nsdg_dyn_field_ncomp(const nsdg_ctx* ctx, int32_t field)
+{
+    if (!ctx || !ctx->dyn || field < 0 || field >= NSDG_DF_COUNT)
+        return NSDG_EINVAL;
+    return ctx->dyn->ncomp[field];
+}
+
+int nsdg_dyn_upload(nsdg_ctx* ctx, int32_t field, const double* host)
+{
+    NSDG_ENTER(ctx);
+    DynState* d = ctx->dyn;
+    NSDG_REQUIRE(ctx, d, NSDG_ESTATE, "nsdg_dyn_init has not been called");
+    NSDG_REQUIRE(ctx, field >= 0 && field < NSDG_DF_COUNT && host, NSDG_EINVAL, "bad field/host");
+    const size_t inner = (size_t)d->nx * d->nyl;
+    for (int c = 0; c < d->ncomp[field]; ++c)
+        NSDG_CUDA(ctx, cudaMemcpyAsync(d->f[field] + (size_t)c * d->plane + d->nx, host + c * inner,
+                           sizeof(double) * inner, cudaMemcpyHostToDevice, ctx->stream));
+    NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return NSDG_OK;
+}
+
+int nsdg_dyn_download(nsdg_ctx* ctx, int32_t field, double* host)
+{
+    NSDG_ENTER(ctx);
+    DynState* d = ctx->dyn;
+    NSDG_REQUIRE(ctx, d, NSDG_ESTATE, "nsdg_dyn_init has not been called");
+    NSDG_REQUIRE(ctx, field >= 0 && field < NSDG_DF_COUNT && host, NSDG_EINVAL, "bad field/host");
+    const size_t inner = (size_t)d->nx * d->nyl;
+    for (int c = 0; c < d->ncomp[field]; ++c)
+        NSDG_CUDA(ctx, cudaMemcpyAsync(host + c * inner, d->f[field] + (size_t)c * d->plane + d->nx,
+                           sizeof(double) * inner, cudaMemcpyDeviceToHost, ctx->stream));
+    NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return NSDG_OK;
+}
+
+int nsdg_dyn_field_ptr(nsdg_ctx* ctx, int32_t field, void** device_ptr)
+{
+    NSDG_ENTER(ctx);
+    NSDG_REQUIRE(ctx, ctx->dyn, NSDG_ESTATE, "nsdg_dyn_init has not been called");
+    NSDG_REQUIRE(ctx, field >= 0 && field < NSDG_DF_COUNT && device_ptr, NSDG_EINVAL, "bad field");
+    *device_ptr = ctx->dyn->f[field];
+    return NSDG_OK;
+}
+
+int nsdg_transport_step(nsdg_ctx* ctx, int32_t field, double dt)
+{
+    NSDG_ENTER(ctx);
+    DynState* d = ctx->dyn;
+    NSDG_REQUIRE(ctx, d, NSDG_ESTATE, "nsdg_dyn_init has not been called");
+    NSDG_REQUIRE(ctx, field == NSDG_DF_H || field == NSDG_DF_A, NSDG_EINVAL,
+        "only the tracers H and A can be transported");
+    double* phi[1] = { d->f[field] };
+    double* s1[1] = { d->stage1[0] };
+    double* s2[1] = { d->stage2[0] };
+    const double lo[1] = { 0. }, hi[1] = { field == NSDG_DF_A ? 1. : 1e300 };
+    return transport_fields(ctx, 1, phi, s1, s2, lo, hi, dt);
+}
+
+int nsdg_transport_step_HA(nsdg_ctx* ctx, double dt)
+{
+    NSDG_ENTER(ctx);
+    DynState* d = ctx->dyn;
+    NSDG_REQUIRE(ctx, d, NSDG_ESTATE, "nsdg_dyn_init has not been called");
+    double* phi[2] = { d->f[NSDG_DF_H], d->f[NSDG_DF_A] };
+    const double lo[2] = { 0., 0. }, hi[2] = { 1e300, 1. };
+    return transport_fields(ctx, 2, phi, d->stage1, d->stage2, lo, hi, dt);
+}
+
+int nsdg_mevp_step(nsdg_ctx* ctx, double dt, int32_t nsub)
+{
+    NSDG_ENTER(ctx);
+    NSDG_REQUIRE(ctx, ctx->dyn, NSDG_ESTATE, "nsdg_dyn_init has not been called");
+    NSDG_REQUIRE(ctx, dt > 0 && nsub >= 0, NSDG_EINVAL, "dt > 0 and nsub >= 0 required");
+    return mevp_cycle(ctx, dt, nsub);
+}
+
+int nsdg_dyn_step(nsdg_ctx* ctx, double dt, int32_t nsub)
+{
+    int rc = nsdg_transport_step_HA(ctx, dt);
+    if (rc)
+        return rc;
+    return nsdg_mevp_step(ctx, dt, nsub);
+}
+
+int nsdg_dyn_mass(nsdg_ctx* ctx, int32_t field, double* mass)
+{
+    NSDG_ENTER(ctx);
+    DynState* d = ctx->dyn;
+    NSDG_REQUIRE(ctx, d, NSDG_ESTATE, "nsdg_dyn_init has not been called");
+    NSDG_REQUIRE(ctx, (field == NSDG_DF_H || field == NSDG_DF_A) && mass, NSDG_EINVAL, "bad field");
+    NSDG_CUDA(ctx, cudaMemsetAsync(d->scratch, 0, sizeof(double), ctx->stream));
+    mass_kernel<<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(d->f[field], d->nx, d->nyl, d->scratch);
+    NSDG_LAUNCHED(ctx);
+    double s = 0.;
+    NSDG_CUDA(ctx, cudaMemcpyAsync(&s, d->scratch, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    *mass = s * d->cfg.hx * d->cfg.hy;
+    return NSDG_OK;
+}
+
+} // extern "C"

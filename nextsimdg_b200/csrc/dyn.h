@@ -1,0 +1,66 @@
+// Device-resident state of the dynamics (DG transport + mEVP) and the internal launchers.
+//
+// HBM layout.  Every array is a stack of planes; a plane is (ny_local+2) rows of nx doubles,
+// row 0 and row ny_local+1 being ghost rows of the strip decomposition (unused when one rank
+// owns the whole periodic domain: kernels then wrap row indices instead).  DG fields are
+// component-major, a[c][row][i], so that each coefficient is its own coalesced stream.  Node
+// (CG1) arrays use the same plane shape; node (i,row) is the lower-left corner of cell (i,row).
+#pragma once
+#include "ctx.h"
+
+struct DynState {
+    nsdg_dyn_config cfg;
+    nsdg_mevp_params mp;
+    int64_t nx = 0, nyl = 0, rows = 0, plane = 0; // rows = nyl+2, plane = rows*nx
+    int nc = 0; // tracer components
+    int rk = 0; // RK order actually used
+    bool wrap = true; // single rank: periodic wrap in y inside the kernels
+    double* f[NSDG_DF_COUNT] = {};
+    int ncomp[NSDG_DF_COUNT] = {};
+    // RK stage buffers for H and A
+    double* stage1[2] = {};
+    double* stage2[2] = {};
+    // per-step mEVP work arrays
+    double* pg = nullptr; // ice strength at the 2x2 Gauss points, 4 planes
+    double* hn = nullptr; // nodal thickness
+    double* an = nullptr; // nodal concentration
+    double* un = nullptr; // velocity at the start of the momentum step
+    double* vn = nullptr;
+    double* u2 = nullptr; // ping-pong partner of U,V
+    double* v2 = nullptr;
+    double* taux = nullptr; // C_a rho_a |u_a| u_a
+    double* tauy = nullptr;
+    double* scratch = nullptr; // reductions
+    double* host_stage = nullptr; // pinned staging for upload/download
+    size_t host_stage_bytes = 0;
+    // halo pack buffers (comm.cu)
+    double* send_lo = nullptr; // to rank-1
+    double* send_hi = nullptr; // to rank+1
+    double* recv_lo = nullptr; // from rank-1
+    double* recv_hi = nullptr; // from rank+1
+    size_t halo_capacity = 0; // doubles per buffer
+};
+
+struct PlaneSet { // up to 12 planes handled by one halo exchange
+    double* p[12];
+    int n;
+};
+
+// transport.cu ------------------------------------------------------------------------------
+// dst = a*base + b*(src + dt*L(src)) for nfields tracers sharing the velocity; rows [r0,r1)
+int nsdg_transport_stage(nsdg_ctx* ctx, int nfields, double* const* src, double* const* base,
+    double* const* dst, double a, double b, double dt, int64_t r0, int64_t r1);
+int nsdg_transport_limit(nsdg_ctx* ctx, double* phi, double lo, double hi);
+
+// mevp.cu -----------------------------------------------------------------------------------
+int nsdg_mevp_prepare(nsdg_ctx* ctx); // pg, hn, an, tau, un/vn from the current H, A, U, V
+int nsdg_mevp_stress(nsdg_ctx* ctx, const double* u, const double* v, int64_t r0, int64_t r1);
+int nsdg_mevp_velocity(nsdg_ctx* ctx, double dt, const double* u, const double* v, double* unew,
+    double* vnew, int64_t r0, int64_t r1);
+
+// comm.cu -----------------------------------------------------------------------------------
+// fill ghost rows of the given planes: row nyl -> upper neighbour's row 0, row 1 -> lower
+// neighbour's row nyl+1 (ring).  which: 1 = lower ghost only, 2 = upper ghost only, 3 = both.
+// No-op on a single rank (kernels wrap).
+int nsdg_halo_exchange(nsdg_ctx* ctx, const PlaneSet& planes, int which);
+bool nsdg_comm_active(const nsdg_ctx* ctx);

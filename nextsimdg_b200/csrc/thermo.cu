@@ -1,0 +1,630 @@
+// Fused column-thermodynamics step: one launch = one DevStep::iterate sweep over all cells.
+//
+// Replaces, per cell, the reference call chain (paths relative to the reference tree)
+//   DevStep::iterate                      core/src/DevStep.cpp:14-23
+//   IPhysics1d::updateDerivedData         physics/src/modules/include/IPhysics1d.hpp:33-45
+//   NextsimPhysics::calculate             physics/src/modules/NextsimPhysics.cpp:116-131
+//   ThermoIce0::calculate                 physics/src/modules/ThermoIce0.cpp:34-133
+//   PrognosticData::updateAndIntegrate    core/src/PrognosticData.cpp:63-71
+// The per-cell virtual plug-ins (IIceAlbedo, IFreezingPoint, IIceOceanHeatFlux,
+// IConcentrationModel, IThermodynamics) become switches on the enums of nsdg_thermo_params.
+//
+// Layout: 15 structure-of-arrays FP64 streams of length ncells (14 inputs + the hidden
+// persistent newice); 5 are written back.  160 algorithmic bytes per
+// cell-update, HBM-bound; two cells per thread so every access is a 16-byte vector.
+// This file is compiled with -fmad=false: the operation order of the reference is kept so
+// that data-dependent branches (t1<tf, hi<minh, draught>hi, c<minc) resolve identically.
+#include "ctx.h"
+
+namespace {
+
+// core/src/include/constants.hpp:18-123
+constexpr double SIGMA_SB = 5.670374419e-8;
+constexpr double ICE_EPSILON = 0.996;
+constexpr double ICE_KAPPA = 2.0334;
+constexpr double ICE_LF = 333.55e3;
+constexpr double ICE_RHO = 917.;
+constexpr double ICE_RHOSNOW = 330.;
+constexpr double ICE_S = 5.;
+constexpr double AIR_CP = 1004.64;
+constexpr double AIR_RA = 287.058;
+constexpr double VAPOUR_CP = 1860.;
+constexpr double VAPOUR_LV0 = 2500.79e3;
+constexpr double VAPOUR_RA = 461.5;
+constexpr double WATER_CP = 4186.84;
+constexpr double WATER_MU = 0.055;
+constexpr double WATER_RHOOCEAN = 1025.;
+constexpr double WATER_TF = 273.15;
+
+struct SphCoef {
+    double a, b, c, d, bigA, bigB, bigC;
+};
+// NextsimPhysics.cpp:309-312 (water), :345-348 (ice)
+__device__ constexpr SphCoef SPH_WATER = { 6.1121e2, 18.729, 257.87, 227.3, 7.2e-4, 3.20e-6, 5.9e-10 };
+__device__ constexpr SphCoef SPH_ICE = { 6.1115e2, 23.036, 279.82, 333.7, 2.2e-4, 3.83e-6, 6.4e-10 };
+constexpr double SPH_ALPHA = 0.62197; // :324-325
+constexpr double SPH_BETA = 1 - 0.62197;
+
+__device__ __forceinline__ double kelvin(double c) { return c + WATER_TF; }
+__device__ __forceinline__ double sq(double x) { return x * x; }
+
+// NextsimPhysics.cpp:371-375
+__device__ __forceinline__ double sph_f(const SphCoef& k, double t, double pPa)
+{
+    double pmb = pPa * 0.01;
+    return 1 + k.bigA + pmb * (k.bigB + k.bigC * t * t);
+}
+// NextsimPhysics.cpp:377-381
+__device__ __forceinline__ double sph_est(const SphCoef& k, double t, double sal)
+{
+    double salFactor = 1 - 5.37e-4 * sal;
+    return k.a * exp((k.b - t / k.d) * t / (t + k.c)) * salFactor;
+}
+// NextsimPhysics.cpp:383-386; pow(x,4) as two squarings
+__device__ __forceinline__ double stefan_boltzmann(double tC)
+{
+    return ICE_EPSILON * SIGMA_SB * sq(sq(kelvin(tC)));
+}
+// NextsimPhysics.cpp:297-302
+__device__ __forceinline__ double latent_heat_water(double t)
+{
+    return VAPOUR_LV0 + t * (-2.36418e3 + t * (1.58927 + t * (-6.14342e-2)));
+}
+// NextsimPhysics.cpp:304-307
+__device__ __forceinline__ double latent_heat_ice(double t)
+{
+    return VAPOUR_LV0 + ICE_LF - 240. + t * (-290. + t * (-4.));
+}
+
+struct CellIn {
+    double hice, cice, hsnow, sst, sss, tice0, tair, tdew, slp, qsw, qlw, mld, snowfall, wind,
+        newice;
+};
+struct CellOut {
+    double hice, cice, hsnow, tice0, newice;
+};
+
+template <bool DIAG>
+__device__ __forceinline__ CellOut thermo_cell(
+    const nsdg_thermo_params& P, double dt, const CellIn& in, double* diag)
+{
+    const double hice = in.hice, cice = in.cice, hsnow = in.hsnow, tice0 = in.tice0;
+    const double sst = in.sst, sss = in.sss, slp = in.slp, wind = in.wind;
+    double newice = in.newice;
+
+    // ---- updateDerivedData: IPhysics1d.hpp:33-45, NextsimPhysics.cpp:85-114 ----
+    // specific humidities (NextsimPhysics.cpp:333-343); est/f of the ice surface are reused
+    // by dq_dT below (the reference recomputes them, :356-369)
+    double estA = sph_est(SPH_WATER, in.tdew, 0.), fA = sph_f(SPH_WATER, in.tdew, slp);
+    double sphuma = SPH_ALPHA * fA * estA / (slp - SPH_BETA * fA * estA);
+    double estW = sph_est(SPH_WATER, sst, sss), fW = sph_f(SPH_WATER, sst, slp);
+    double sphumw = SPH_ALPHA * fW * estW / (slp - SPH_BETA * fW * estW);
+    double estI = sph_est(SPH_ICE, tice0, 0.), fI = sph_f(SPH_ICE, tice0, slp);
+    double sphumi = SPH_ALPHA * fI * estI / (slp - SPH_BETA * fI * estI);
+    double Ra_wet = AIR_RA / (1 - sphuma * (1 - VAPOUR_RA / AIR_RA));
+    double rho = slp / (Ra_wet * kelvin(in.tair));
+    double cspec = AIR_CP + sphuma * VAPOUR_CP;
+    const double hiTrue = (cice != 0) ? hice / cice : 0; // PrognosticData.hpp:56
+    const double hsTrue = (cice != 0) ? hsnow / cice : 0; // PrognosticData.hpp:75
+    double hs_new = hsTrue, hi_new = hiTrue;
+
+    // ---- NextsimPhysics::calculate :116-131 ----
+    double evap = P.drag_ocean_q * rho * wind * (sphumw - sphuma); // :133-137
+    double tau = rho * (1e-3 * fmax(1.0, fmin(2.0, 0.61 + 0.063 * wind))); // :139-142,291-295
+    // heatFluxOpenWater :144-162
+    double Qlhow = evap * latent_heat_water(sst);
+    double Qshow = P.drag_ocean_t * rho * cspec * wind * (sst - in.tair);
+    double Qswow = -in.qsw * (1 - P.albedo_w);
+    double Qlwow = stefan_boltzmann(sst) - in.qlw;
+    double Qow = Qlhow + Qshow + Qlwow + Qswow;
+    // massFluxIceAtmosphere :164-168
+    double subl = P.drag_ice_t * rho * wind * (sphumi - sphuma);
+    // heatFluxIceAtmosphere :170-198
+    double lhi = latent_heat_ice(tice0);
+    double Qlhi = subl * lhi;
+    double dq_dT;
+    { // SpecificHumidityIce::dq_dT :356-369
+        const SphCoef& k = SPH_ICE;
+        double df_dT = 2 * k.bigC * k.bigB * tice0;
+        double numerator = k.b * k.c * k.d - tice0 * (2 * k.c + tice0);
+        double denominator = k.d * sq(k.c + tice0);
+        double dest_dT = numerator / denominator * estI;
+        numerator = SPH_ALPHA * slp * (fI * dest_dT + estI * df_dT);
+        denominator = sq(slp - SPH_BETA * estI * fI);
+        dq_dT = numerator / denominator;
+    }
+    double dmdot_dT = P.drag_ice_t * rho * wind * dq_dT;
+    double dQlh_dT = lhi * dmdot_dT;
+    double Qshi = P.drag_ice_t * rho * cspec * wind * (tice0 - in.tair);
+    double dQsh_dT = P.drag_ice_t * rho * cspec * wind;
+    double albedoValue;
+    { // IIceAlbedo::albedo, argument as NextsimPhysics.cpp:185-186
+        const double hsArg = (cice > 0) ? (hsnow / cice) : 0.;
+        const double ICE_ALBEDO = 0.64, SNOW_ALBEDO = 0.85;
+        if (P.albedo_kind == NSDG_ALBEDO_CCSM) { // CCSMIceAlbedo.cpp:28-36
+            double iceAlbedoT = P.ccsm_ice_albedo - fmax(0., 0.075 * (tice0 - (-1.)));
+            double snowAlbedoT = P.ccsm_snow_albedo - fmax(0., 0.124 * (tice0 - (-1.)));
+            double snowCoverFraction = hsArg / (hsArg + 0.02);
+            albedoValue = snowCoverFraction * snowAlbedoT + (1 - snowCoverFraction) * iceAlbedoT;
+        } else if (hsArg > 0.) {
+            albedoValue = (P.albedo_kind == NSDG_ALBEDO_SMU) // SMUIceAlbedo.cpp:19-26
+                ? SNOW_ALBEDO
+                : fmin(SNOW_ALBEDO, // SMU2IceAlbedo.cpp:21-29
+                    ICE_ALBEDO + (SNOW_ALBEDO - ICE_ALBEDO) * hsArg / 0.2);
+        } else {
+            albedoValue = ICE_ALBEDO + 0.4 * (1 - ICE_ALBEDO) * P.i0;
+        }
+    }
+    double Qswi = -in.qsw * (1. - P.i0) * (1 - albedoValue);
+    double sbI = stefan_boltzmann(tice0);
+    double Qlwi = sbI - in.qlw;
+    double dQlw_dT = 4 / kelvin(tice0) * sbI;
+    double Qia = Qlhi + Qshi + Qlwi + Qswi;
+    double dQ_dT = dQlh_dT + dQsh_dT + dQlw_dT;
+    // heatFluxIceOcean :222-226 -> BasicIceOceanHeatFlux.cpp:16-25, ExternalData.hpp:60
+    double tf;
+    if (P.freezing_kind == NSDG_FREEZING_UNESCO) { // UnescoFreezing.hpp:28-38
+        tf = sss * (-0.0575 + 1.710523e-3 * sqrt(sss) + -2.154996e-4 * sss) + -7.53e-4 * 0.;
+    } else { // LinearFreezing.hpp:30-34
+        tf = -WATER_MU * sss;
+    }
+    const double mlBulkCp = in.mld * WATER_RHOOCEAN * WATER_CP;
+    double Qio = (sst - tf) * mlBulkCp / dt;
+
+    // ---- massFluxIceOcean :200-220 ----
+    double hifroms = 0;
+    double t_new;
+    { // ThermoIce0::calculate, ThermoIce0.cpp:34-133
+        const double freezingPointIce = -WATER_MU * ICE_S;
+        const double bulkLHFusionSnow = ICE_LF * ICE_RHOSNOW;
+        const double bulkLHFusionIce = ICE_LF * ICE_RHO;
+        if (hice == 0 || cice == 0) { // :45-51
+            hi_new = 0;
+            hs_new = 0;
+            t_new = freezingPointIce;
+        } else {
+            double k_lSlab = P.ks * ICE_KAPPA / (P.ks * hiTrue + ICE_KAPPA * hsTrue);
+            double QIceConduction = k_lSlab * (tf - tice0);
+            double remainingFlux = QIceConduction - Qia;
+            t_new = tice0 + remainingFlux / (k_lSlab + dQ_dT);
+            double meltingLimit = (hsTrue > 0.) ? 0 : freezingPointIce;
+            t_new = fmin(meltingLimit, t_new);
+            double snowMeltRate = fmin(-remainingFlux, 0.) / bulkLHFusionSnow;
+            double snowSublRate = subl / ICE_RHOSNOW;
+            hs_new += (snowMeltRate - snowSublRate) * dt;
+            double excessIceMelt = fmin(hs_new, 0.) * bulkLHFusionSnow / bulkLHFusionIce;
+            hs_new = fmax(hs_new, 0.);
+            hs_new += in.snowfall * dt / ICE_RHOSNOW;
+            double iceBottomChange = (QIceConduction - Qio) * dt / bulkLHFusionIce;
+            double iceThicknessChange = excessIceMelt + iceBottomChange;
+            hi_new += iceThicknessChange;
+            double iceDraught = (hi_new * ICE_RHO + hs_new * ICE_RHOSNOW) / WATER_RHOOCEAN;
+            if (P.flooding && iceDraught > hi_new) { // :95-106
+                double newIce = iceDraught - hi_new;
+                hifroms += newIce;
+                hi_new = iceDraught;
+                hs_new -= newIce * ICE_RHO / ICE_RHOSNOW;
+            }
+            if (hi_new < P.min_thick) { // :108-132
+                hifroms = 0;
+                double deltaQio = hi_new * bulkLHFusionIce / dt + hs_new * bulkLHFusionSnow / dt;
+                Qio += deltaQio;
+                hi_new = 0;
+                hs_new = 0;
+                t_new = freezingPointIce;
+            }
+        }
+    }
+    { // newIceFormation :228-254
+        double coolingFlux = Qow;
+        double deltaTml = -coolingFlux / mlBulkCp * dt;
+        double t1 = sst + deltaTml;
+        if (t1 < tf) {
+            double sensibleFlux = (tf - sst) / deltaTml * coolingFlux;
+            double latentFlux = coolingFlux - sensibleFlux;
+            Qow = sensibleFlux;
+            newice = latentFlux * dt * (1 - cice) / (ICE_LF * ICE_RHO);
+        }
+    }
+    double c_new;
+    { // lateralGrowth :262-289, HiblerConcentration.cpp:32-47, updateThickness :257-260
+        double del_c = newice * (1. / P.h0);
+        if (hi_new < hiTrue) {
+            double m = 0;
+            if (!(cice >= 1)) {
+                double del_hi = hi_new - hiTrue;
+                m = del_hi * cice * P.phi_m / hiTrue;
+            }
+            del_c += m;
+        }
+        c_new = cice + del_c;
+        if (c_new >= P.min_conc) {
+            hi_new += (newice - hi_new * del_c) / (cice + del_c);
+            if (del_c < 0) {
+                Qow -= del_c * hs_new * ICE_LF * ICE_RHOSNOW / dt;
+            } else {
+                hs_new += (0. - hs_new * del_c) / (cice + del_c);
+            }
+        }
+    }
+    if (c_new < P.min_conc || hi_new < P.min_thick) { // NextsimPhysics.cpp:210-219
+        Qow += c_new * ICE_LF * (hi_new * ICE_RHO + hs_new * ICE_RHOSNOW) / dt;
+        c_new = 0;
+        hi_new = 0;
+        hs_new = 0;
+    }
+    if (DIAG) {
+        diag[0] = rho;
+        diag[1] = sphuma;
+        diag[2] = sphumw;
+        diag[3] = sphumi;
+        diag[4] = cspec;
+        diag[5] = tau;
+        diag[6] = Qia;
+        diag[7] = Qio;
+        diag[8] = Qow;
+        diag[9] = subl;
+        diag[10] = dQ_dT;
+        diag[11] = hifroms;
+        diag[12] = t_new;
+    }
+    // updateAndIntegrate: PrognosticData.cpp:63-71, PhysicsData.hpp:61,66
+    CellOut o;
+    o.hice = hi_new * c_new;
+    o.cice = c_new;
+    o.hsnow = hs_new * c_new;
+    o.tice0 = t_new;
+    o.newice = newice;
+    return o;
+}
+
+struct ThermoPtrs {
+    double* f[NSDG_TF_COUNT];
+    double* diag;
+};
+
+__device__ __forceinline__ double2 ldg2(const double* p, int64_t k2)
+{
+    return __ldg(reinterpret_cast<const double2*>(p) + k2);
+}
+
+// two cells per thread: every global access is a 16-byte vector, fully coalesced
+template <bool DIAG>
+__global__ void __launch_bounds__(256) thermo_kernel(const __grid_constant__ nsdg_thermo_params P,
+    const __grid_constant__ ThermoPtrs ptr, double dt, int64_t n)
+{
+    const int64_t npair = n >> 1;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t k2 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k2 < npair; k2 += stride) {
+        double2 v[NSDG_TF_COUNT];
+#pragma unroll
+        for (int q = 0; q < NSDG_TF_COUNT; ++q)
+            v[q] = ldg2(ptr.f[q], k2);
+        CellIn a = { v[0].x, v[1].x, v[2].x, v[3].x, v[4].x, v[5].x, v[6].x, v[7].x, v[8].x,
+            v[9].x, v[10].x, v[11].x, v[12].x, v[13].x, v[14].x };
+        CellIn b = { v[0].y, v[1].y, v[2].y, v[3].y, v[4].y, v[5].y, v[6].y, v[7].y, v[8].y,
+            v[9].y, v[10].y, v[11].y, v[12].y, v[13].y, v[14].y };
+        double da[NSDG_THERMO_NDIAG], db[NSDG_THERMO_NDIAG];
+        CellOut oa = thermo_cell<DIAG>(P, dt, a, da);
+        CellOut ob = thermo_cell<DIAG>(P, dt, b, db);
+        reinterpret_cast<double2*>(ptr.f[NSDG_TF_HICE])[k2] = make_double2(oa.hice, ob.hice);
+        reinterpret_cast<double2*>(ptr.f[NSDG_TF_CICE])[k2] = make_double2(oa.cice, ob.cice);
+        reinterpret_cast<double2*>(ptr.f[NSDG_TF_HSNOW])[k2] = make_double2(oa.hsnow, ob.hsnow);
+        reinterpret_cast<double2*>(ptr.f[NSDG_TF_TICE0])[k2] = make_double2(oa.tice0, ob.tice0);
+        reinterpret_cast<double2*>(ptr.f[NSDG_TF_NEWICE])[k2] = make_double2(oa.newice, ob.newice);
+        if (DIAG) {
+#pragma unroll
+            for (int q = 0; q < NSDG_THERMO_NDIAG; ++q)
+                reinterpret_cast<double2*>(ptr.diag + (size_t)q * n)[k2] = make_double2(da[q], db[q]);
+        }
+    }
+    // odd tail cell
+    if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
+        const int64_t k = n - 1;
+        CellIn a = { ptr.f[0][k], ptr.f[1][k], ptr.f[2][k], ptr.f[3][k], ptr.f[4][k], ptr.f[5][k],
+            ptr.f[6][k], ptr.f[7][k], ptr.f[8][k], ptr.f[9][k], ptr.f[10][k], ptr.f[11][k],
+            ptr.f[12][k], ptr.f[13][k], ptr.f[14][k] };
+        double da[NSDG_THERMO_NDIAG];
+        CellOut oa = thermo_cell<DIAG>(P, dt, a, da);
+        ptr.f[NSDG_TF_HICE][k] = oa.hice;
+        ptr.f[NSDG_TF_CICE][k] = oa.cice;
+        ptr.f[NSDG_TF_HSNOW][k] = oa.hsnow;
+        ptr.f[NSDG_TF_TICE0][k] = oa.tice0;
+        ptr.f[NSDG_TF_NEWICE][k] = oa.newice;
+        if (DIAG)
+            for (int q = 0; q < NSDG_THERMO_NDIAG; ++q)
+                ptr.diag[(size_t)q * n + k] = da[q];
+    }
+}
+
+// tice[k*nlayers + l] <-> tice0[k]
+__global__ void gather_layer0(const double* tice, double* tice0, int64_t n, int nlayers)
+{
+    int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < n)
+        tice0[k] = tice[k * nlayers];
+}
+// all layers take the surface value (PrognosticData.cpp:82-94)
+__global__ void broadcast_layers(const double* tice0, double* tice, int64_t n, int nlayers)
+{
+    int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q < n * nlayers)
+        tice[q] = tice0[q / nlayers];
+}
+
+int thermo_launch(nsdg_ctx* ctx, double dt, int nsteps, bool diag)
+{
+    ThermoState* t = ctx->thermo;
+    NSDG_REQUIRE(ctx, t, NSDG_ESTATE, "nsdg_thermo_init has not been called");
+    NSDG_REQUIRE(ctx, t->have_prog && t->have_forcing, NSDG_ESTATE,
+        "prognostic and forcing data must be uploaded before stepping");
+    NSDG_REQUIRE(ctx, dt > 0 && nsteps >= 0, NSDG_EINVAL, "dt must be > 0 and nsteps >= 0");
+    if (t->n == 0)
+        return NSDG_OK;
+    if (diag && !t->diag)
+        NSDG_CUDA(ctx, cudaMalloc(&t->diag, sizeof(double) * NSDG_THERMO_NDIAG * (size_t)t->n));
+    ThermoPtrs p;
+    for (int q = 0; q < NSDG_TF_COUNT; ++q)
+        p.f[q] = t->fields[q];
+    p.diag = t->diag;
+    const int block = 256;
+    int64_t npair = (t->n + 1) / 2;
+    int64_t want = (npair + block - 1) / block;
+    int64_t cap = (int64_t)ctx->sm_count * 16; // grid-stride beyond 16 CTAs/SM worth of work
+    int grid = (int)(want < cap ? (want > 0 ? want : 1) : cap);
+    for (int s = 0; s < nsteps; ++s) {
+        if (diag && s == nsteps - 1)
+            thermo_kernel<true><<<grid, block, 0, ctx->stream>>>(t->params, p, dt, t->n);
+        else
+            thermo_kernel<false><<<grid, block, 0, ctx->stream>>>(t->params, p, dt, t->n);
+        NSDG_LAUNCHED(ctx);
+    }
+    return NSDG_OK;
+}
+
+} // namespace
+
+void nsdg_thermo_free(nsdg_ctx* ctx)
+{
+    ThermoState* t = ctx->thermo;
+    if (!t)
+        return;
+    for (int q = 0; q < NSDG_TF_COUNT; ++q)
+        cudaFree(t->fields[q]);
+    cudaFree(t->diag);
+    cudaFree(t->stage);
+    delete t;
+    ctx->thermo = nullptr;
+}
+
+extern "C" {
+
+void nsdg_thermo_default_params(nsdg_thermo_params* p)
+{
+    if (!p)
+        return;
+    p->drag_ocean_q = 1.5e-3;
+    p->drag_ocean_t = 0.83e-3;
+    p->drag_ice_t = 1.3e-3;
+    p->albedo_w = 0.07;
+    p->i0 = 0.17;
+    p->min_conc = 1e-12;
+    p->min_thick = 0.01;
+    p->ks = 0.3096;
+    p->h0 = 0.25;
+    p->phi_m = 0.5;
+    p->ccsm_ice_albedo = 0.538;
+    p->ccsm_snow_albedo = 0.8256;
+    p->flooding = 1;
+    p->albedo_kind = NSDG_ALBEDO_SMU;
+    p->freezing_kind = NSDG_FREEZING_LINEAR;
+    p->ocean_flux_kind = NSDG_OCEANFLUX_BASIC;
+}
+
+int nsdg_thermo_init(nsdg_ctx* ctx, int64_t ncells, int32_t nlayers)
+{
+    NSDG_ENTER(ctx);
+    NSDG_REQUIRE(ctx, ncells >= 0 && nlayers >= 1, NSDG_EINVAL, "ncells >= 0 and nlayers >= 1");
+    nsdg_thermo_free(ctx);
+    ThermoState* t = new ThermoState;
+    ctx->thermo = t;
+    t->n = ncells;
+    t->nlayers = nlayers;
+    nsdg_thermo_default_params(&t->params);
+    // even-padded so the vector path may read the pair that holds the last cell
+    size_t bytes = sizeof(double) * (size_t)(ncells + 2);
+    for (int q = 0; q < NSDG_TF_COUNT; ++q) {
+        NSDG_CUDA(ctx, cudaMalloc(&t->fields[q], bytes));
+        NSDG_CUDA(ctx, cudaMemsetAsync(t->fields[q], 0, bytes, ctx->stream));
+    }
+    if (nlayers > 1)
+        NSDG_CUDA(ctx, cudaMalloc(&t->stage, sizeof(double) * (size_t)ncells * nlayers + 16));
+    return NSDG_OK;
+}
+
+int nsdg_thermo_set_params(nsdg_ctx* ctx, const nsdg_thermo_params* p)
+{
+    NSDG_ENTER(ctx);
+    NSDG_REQUIRE(ctx, ctx->thermo, NSDG_ESTATE, "nsdg_thermo_init has not been called");
+    NSDG_REQUIRE(ctx, p, NSDG_EINVAL, "params is null");
+    // unknown module combination => error, never a fallback
+    NSDG_REQUIRE(ctx, p->albedo_kind >= 0 && p->albedo_kind <= NSDG_ALBEDO_CCSM, NSDG_EINVAL,
+        "unknown IIceAlbedo implementation id %d", p->albedo_kind);
+    NSDG_REQUIRE(ctx, p->freezing_kind >= 0 && p->freezing_kind <= NSDG_FREEZING_UNESCO,
+        NSDG_EINVAL, "unknown IFreezingPoint implementation id %d", p->freezing_kind);
+    NSDG_REQUIRE(ctx, p->ocean_flux_kind == NSDG_OCEANFLUX_BASIC, NSDG_EINVAL,
+        "unknown IIceOceanHeatFlux implementation id %d", p->ocean_flux_kind);
+    NSDG_REQUIRE(ctx, p->h0 != 0., NSDG_EINVAL, "Hibler.h0 must be non-zero");
+    ctx->thermo->params = *p;
+    return NSDG_OK;
+}
+
+static int upload(nsdg_ctx* ctx, int field, const double* host)
+{
+    ThermoState* t = ctx->thermo;
+    NSDG_REQUIRE(ctx, host || t->n == 0, NSDG_EINVAL, "null host array for field %d", field);
+    if (t->n)
+        NSDG_CUDA(ctx, cudaMemcpyAsync(t->fields[field], host, sizeof(double) * (size_t)t->n,
+                           cudaMemcpyHostToDevice, ctx->stream));
+    return NSDG_OK;
+}
+static int download(nsdg_ctx* ctx, int field, double* host)
+{
+    ThermoState* t = ctx->thermo;
+    NSDG_REQUIRE(ctx, host || t->n == 0, NSDG_EINVAL, "null host array for field %d", field);
+    if (t->n)
+        NSDG_CUDA(ctx, cudaMemcpyAsync(host, t->fields[field], sizeof(double) * (size_t)t->n,
+                           cudaMemcpyDeviceToHost, ctx->stream));
+    return NSDG_OK;
+}
+
+int nsdg_thermo_upload_prognostic(nsdg_ctx* ctx, const double* hice, const double* cice,
+    const double* hsnow, const double* sst, const double* sss, const double* tice)
+{
+    NSDG_ENTER(ctx);
+    ThermoState* t = ctx->thermo;
+    NSDG_REQUIRE(ctx, t, NSDG_ESTATE, "nsdg_thermo_init has not been called");
+    int rc;
+    if ((rc = upload(ctx, NSDG_TF_HICE, hice)) || (rc = upload(ctx, NSDG_TF_CICE, cice))
+        || (rc = upload(ctx, NSDG_TF_HSNOW, hsnow)) || (rc = upload(ctx, NSDG_TF_SST, sst))
+        || (rc = upload(ctx, NSDG_TF_SSS, sss)))
+        return rc;
+    if (t->nlayers == 1) {
+        if ((rc = upload(ctx, NSDG_TF_TICE0, tice)))
+            return rc;
+    } else if (t->n) {
+        NSDG_REQUIRE(ctx, tice, NSDG_EINVAL, "null tice");
+        NSDG_CUDA(ctx, cudaMemcpyAsync(t->stage, tice, sizeof(double) * (size_t)t->n * t->nlayers,
+                           cudaMemcpyHostToDevice, ctx->stream));
+        gather_layer0<<<(unsigned)((t->n + 255) / 256), 256, 0, ctx->stream>>>(
+            t->stage, t->fields[NSDG_TF_TICE0], t->n, t->nlayers);
+        NSDG_LAUNCHED(ctx);
+    }
+    NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->stream)); // host arrays are borrowed for the call only
+    t->have_prog = true;
+    return NSDG_OK;
+}
+
+int nsdg_thermo_upload_forcing(nsdg_ctx* ctx, const double* tair, const double* tdew,
+    const double* slp, const double* qsw, const double* qlw, const double* mld,
+    const double* snowfall, const double* wind)
+{
+    NSDG_ENTER(ctx);
+    ThermoState* t = ctx->thermo;
+    NSDG_REQUIRE(ctx, t, NSDG_ESTATE, "nsdg_thermo_init has not been called");
+    const double* src[8] = { tair, tdew, slp, qsw, qlw, mld, snowfall, wind };
+    for (int q = 0; q < 8; ++q) {
+        int rc = upload(ctx, NSDG_TF_TAIR + q, src[q]);
+        if (rc)
+            return rc;
+    }
+    NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    t->have_forcing = true;
+    return NSDG_OK;
+}
+
+int nsdg_thermo_upload_newice(nsdg_ctx* ctx, const double* newice)
+{
+    NSDG_ENTER(ctx);
+    NSDG_REQUIRE(ctx, ctx->thermo, NSDG_ESTATE, "nsdg_thermo_init has not been called");
+    int rc = upload(ctx, NSDG_TF_NEWICE, newice);
+    if (rc)
+        return rc;
+    NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return NSDG_OK;
+}
+
+int nsdg_thermo_download_newice(nsdg_ctx* ctx, double* newice)
+{
+    NSDG_ENTER(ctx);
+    NSDG_REQUIRE(ctx, ctx->thermo, NSDG_ESTATE, "nsdg_thermo_init has not been called");
+    int rc = download(ctx, NSDG_TF_NEWICE, newice);
+    if (rc)
+        return rc;
+    NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return NSDG_OK;
+}
+
+int nsdg_thermo_step(nsdg_ctx* ctx, double dt, int32_t nsteps)
+{
+    NSDG_ENTER(ctx);
+    return thermo_launch(ctx, dt, nsteps, false);
+}
+
+int nsdg_thermo_step_diag(nsdg_ctx* ctx, double dt, int32_t nsteps)
+{
+    NSDG_ENTER(ctx);
+    return thermo_launch(ctx, dt, nsteps, true);
+}
+
+int nsdg_thermo_download_prognostic(nsdg_ctx* ctx, double* hice, double* cice, double* hsnow,
+    double* sst, double* sss, double* tice)
+{
+    NSDG_ENTER(ctx);
+    ThermoState* t = ctx->thermo;
+    NSDG_REQUIRE(ctx, t, NSDG_ESTATE, "nsdg_thermo_init has not been called");
+    int rc;
+    if ((rc = download(ctx, NSDG_TF_HICE, hice)) || (rc = download(ctx, NSDG_TF_CICE, cice))
+        || (rc = download(ctx, NSDG_TF_HSNOW, hsnow)))
+        return rc;
+    if (sst && (rc = download(ctx, NSDG_TF_SST, sst)))
+        return rc;
+    if (sss && (rc = download(ctx, NSDG_TF_SSS, sss)))
+        return rc;
+    if (t->nlayers == 1) {
+        if ((rc = download(ctx, NSDG_TF_TICE0, tice)))
+            return rc;
+    } else if (t->n) {
+        NSDG_REQUIRE(ctx, tice, NSDG_EINVAL, "null tice");
+        int64_t tot = t->n * t->nlayers;
+        broadcast_layers<<<(unsigned)((tot + 255) / 256), 256, 0, ctx->stream>>>(
+            t->fields[NSDG_TF_TICE0], t->stage, t->n, t->nlayers);
+        NSDG_LAUNCHED(ctx);
+        NSDG_CUDA(ctx, cudaMemcpyAsync(tice, t->stage, sizeof(double) * (size_t)tot,
+                           cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return NSDG_OK;
+}
+
+int nsdg_thermo_download_diagnostics(nsdg_ctx* ctx, double* diag)
+{
+    NSDG_ENTER(ctx);
+    ThermoState* t = ctx->thermo;
+    NSDG_REQUIRE(ctx, t && t->diag, NSDG_ESTATE, "no diagnostics: call nsdg_thermo_step_diag first");
+    NSDG_REQUIRE(ctx, diag, NSDG_EINVAL, "diag is null");
+    NSDG_CUDA(ctx, cudaMemcpyAsync(diag, t->diag, sizeof(double) * NSDG_THERMO_NDIAG * (size_t)t->n,
+                       cudaMemcpyDeviceToHost, ctx->stream));
+    NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return NSDG_OK;
+}
+
+int nsdg_thermo_field_ptr(nsdg_ctx* ctx, int32_t field, void** device_ptr)
+{
+    NSDG_ENTER(ctx);
+    ThermoState* t = ctx->thermo;
+    NSDG_REQUIRE(ctx, t, NSDG_ESTATE, "nsdg_thermo_init has not been called");
+    NSDG_REQUIRE(ctx, field >= 0 && field < NSDG_TF_COUNT && device_ptr, NSDG_EINVAL,
+        "bad field id %d", field);
+    *device_ptr = t->fields[field];
+    // a caller that writes through these pointers owns the "uploaded" state
+    t->have_prog = t->have_forcing = true;
+    return NSDG_OK;
+}
+
+int nsdg_thermo_run_host(nsdg_ctx* ctx, double dt, int32_t nsteps, double* hice, double* cice,
+    double* hsnow, const double* sst, const double* sss, double* tice, const double* tair,
+    const double* tdew, const double* slp, const double* qsw, const double* qlw,
+    const double* mld, const double* snowfall, const double* wind)
+{
+    int rc;
+    if ((rc = nsdg_thermo_upload_prognostic(ctx, hice, cice, hsnow, sst, sss, tice)))
+        return rc;
+    if ((rc = nsdg_thermo_upload_forcing(ctx, tair, tdew, slp, qsw, qlw, mld, snowfall, wind)))
+        return rc;
+    if ((rc = nsdg_thermo_step(ctx, dt, nsteps)))
+        return rc;
+    return nsdg_thermo_download_prognostic(ctx, hice, cice, hsnow, nullptr, nullptr, tice);
+}
+
+} // extern "C"

@@ -1,0 +1,302 @@
+// DG tracer transport: one fused kernel per Runge-Kutta stage.
+//
+// NOT IN THE REFERENCE SNAPSHOT (its CMakeLists.txt:43-46 comments "dynamics" out); the scheme
+// is the one stated in oracle/dg_transport.c and DESIGN.md, parity is against that oracle only.
+//
+// One thread owns one cell and gathers everything it needs (no atomics, deterministic):
+//   volume term + the four edge upwind fluxes + inverse mass + the RK stage combination
+//     dst = a*base + b*(src + dt*L(src))
+// for NF tracers that share the velocity reads.  Each thread computes both fluxes of its own
+// edges (the neighbour recomputes the shared one): 2x redundant flops, zero extra DRAM bytes.
+// Coefficients are component-major planes, so every load below is a fully coalesced stream;
+// the +-1 neighbours in x and y hit L1/L2 (counting rule of SURVEY.md 8d: neighbour re-reads
+// are free).  Algorithmic bytes per cell per stage: (NC src + NC base + NC dst)*NF*8 + 2*8.
+#include "dyn.h"
+
+namespace {
+
+template <int NQ> struct Gauss;
+template <> struct Gauss<1> {
+    static __device__ __forceinline__ double x(int) { return 0.5; }
+    static __device__ __forceinline__ double w(int) { return 1.0; }
+};
+template <> struct Gauss<2> {
+    static __device__ __forceinline__ double x(int k)
+    {
+        return k == 0 ? 0.5 - 0.28867513459481287 : 0.5 + 0.28867513459481287;
+    }
+    static __device__ __forceinline__ double w(int) { return 0.5; }
+};
+template <> struct Gauss<3> {
+    static __device__ __forceinline__ double x(int k)
+    {
+        return k == 0 ? 0.5 - 0.3872983346207417 : (k == 1 ? 0.5 : 0.5 + 0.3872983346207417);
+    }
+    static __device__ __forceinline__ double w(int k) { return k == 1 ? 8. / 18. : 5. / 18.; }
+};
+
+template <int NC> __device__ __forceinline__ double eval(const double (&c)[NC], double xi, double eta)
+{
+    double a = xi - 0.5, b = eta - 0.5;
+    double s = c[0];
+    if (NC >= 3)
+        s += c[1] * a + c[2] * b;
+    if (NC >= 6)
+        s += c[3] * (a * a - 1. / 12.) + c[4] * (b * b - 1. / 12.) + c[5] * a * b;
+    return s;
+}
+
+// r[i] += F * psi_i(xi,eta)
+template <int NC> __device__ __forceinline__ void add_psi(double (&r)[NC], double F, double xi, double eta)
+{
+    double a = xi - 0.5, b = eta - 0.5;
+    r[0] += F;
+    if (NC >= 3) {
+        r[1] += F * a;
+        r[2] += F * b;
+    }
+    if (NC >= 6) {
+        r[3] += F * (a * a - 1. / 12.);
+        r[4] += F * (b * b - 1. / 12.);
+        r[5] += F * a * b;
+    }
+}
+
+template <int NC> __device__ __forceinline__ void load_cell(double (&c)[NC], const double* p, int64_t plane, int64_t k)
+{
+#pragma unroll
+    for (int q = 0; q < NC; ++q)
+        c[q] = __ldg(p + q * plane + k);
+}
+
+struct StageArgs {
+    const double* src[2];
+    const double* base[2];
+    double* dst[2];
+    const double* u;
+    const double* v;
+    double a, b, dt, ihx, ihy;
+    int64_t nx, nyl, plane, r0, r1;
+    int wrap;
+};
+
+template <int NC, int NF, bool HAS_BASE>
+__global__ void __launch_bounds__(256) transport_stage_kernel(const __grid_constant__ StageArgs A)
+{
+    constexpr int NQ = (NC == 1) ? 1 : (NC == 3 ? 2 : 3);
+    using G = Gauss<NQ>;
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t r = A.r0 + (int64_t)blockIdx.y * blockDim.y + threadIdx.y;
+    if (i >= A.nx || r >= A.r1)
+        return;
+    int64_t rm = r - 1, rp = r + 1;
+    if (A.wrap) {
+        if (rm < 1)
+            rm = A.nyl;
+        if (rp > A.nyl)
+            rp = 1;
+    }
+    const int64_t im = (i == 0) ? A.nx - 1 : i - 1;
+    const int64_t ip = (i == A.nx - 1) ? 0 : i + 1;
+    const int64_t k = r * A.nx + i;
+
+    const double u00 = __ldg(A.u + r * A.nx + i), u10 = __ldg(A.u + r * A.nx + ip);
+    const double u01 = __ldg(A.u + rp * A.nx + i), u11 = __ldg(A.u + rp * A.nx + ip);
+    const double v00 = __ldg(A.v + r * A.nx + i), v10 = __ldg(A.v + r * A.nx + ip);
+    const double v01 = __ldg(A.v + rp * A.nx + i), v11 = __ldg(A.v + rp * A.nx + ip);
+
+    // edge-normal velocities at the edge Gauss points, split into outflow/inflow parts
+    double uLp[NQ], uLm[NQ], uRp[NQ], uRm[NQ], vBp[NQ], vBm[NQ], vTp[NQ], vTm[NQ];
+#pragma unroll
+    for (int g = 0; g < NQ; ++g) {
+        const double s = G::x(g), w = G::w(g);
+        double uL = (u00 * (1 - s) + u01 * s) * A.ihx * w;
+        double uR = (u10 * (1 - s) + u11 * s) * A.ihx * w;
+        double vB = (v00 * (1 - s) + v10 * s) * A.ihy * w;
+        double vT = (v01 * (1 - s) + v11 * s) * A.ihy * w;
+        uLp[g] = fmax(uL, 0.);
+        uLm[g] = fmin(uL, 0.);
+        uRp[g] = fmax(uR, 0.);
+        uRm[g] = fmin(uR, 0.);
+        vBp[g] = fmax(vB, 0.);
+        vBm[g] = fmin(vB, 0.);
+        vTp[g] = fmax(vT, 0.);
+        vTm[g] = fmin(vT, 0.);
+    }
+
+#pragma unroll
+    for (int f = 0; f < NF; ++f) {
+        double c[NC], cn[NC], rr[NC];
+        load_cell<NC>(c, A.src[f], A.plane, k);
+#pragma unroll
+        for (int q = 0; q < NC; ++q)
+            rr[q] = 0.;
+        // volume term: int phi (u/hx dpsi/dxi + v/hy dpsi/deta)
+        if (NC > 1) {
+#pragma unroll
+            for (int ga = 0; ga < NQ; ++ga)
+#pragma unroll
+                for (int gb = 0; gb < NQ; ++gb) {
+                    const double xi = G::x(ga), eta = G::x(gb), w = G::w(ga) * G::w(gb);
+                    const double uu = (u00 * (1 - xi) + u10 * xi) * (1 - eta) + (u01 * (1 - xi) + u11 * xi) * eta;
+                    const double vv = (v00 * (1 - xi) + v10 * xi) * (1 - eta) + (v01 * (1 - xi) + v11 * xi) * eta;
+                    const double p = w * eval<NC>(c, xi, eta);
+                    const double fx = p * uu * A.ihx, fy = p * vv * A.ihy;
+                    rr[1] += fx;
+                    rr[2] += fy;
+                    if (NC >= 6) {
+                        rr[3] += fx * 2. * (xi - 0.5);
+                        rr[4] += fy * 2. * (eta - 0.5);
+                        rr[5] += fx * (eta - 0.5) + fy * (xi - 0.5);
+                    }
+                }
+        }
+        // left edge (xi = 0): inflow from the left neighbour's right trace
+        load_cell<NC>(cn, A.src[f], A.plane, r * A.nx + im);
+#pragma unroll
+        for (int g = 0; g < NQ; ++g) {
+            const double s = G::x(g);
+            double F = uLp[g] * eval<NC>(cn, 1., s) + uLm[g] * eval<NC>(c, 0., s);
+            add_psi<NC>(rr, F, 0., s);
+        }
+        // right edge (xi = 1)
+        load_cell<NC>(cn, A.src[f], A.plane, r * A.nx + ip);
+#pragma unroll
+        for (int g = 0; g < NQ; ++g) {
+            const double s = G::x(g);
+            double F = uRp[g] * eval<NC>(c, 1., s) + uRm[g] * eval<NC>(cn, 0., s);
+            add_psi<NC>(rr, -F, 1., s);
+        }
+        // bottom edge (eta = 0)
+        load_cell<NC>(cn, A.src[f], A.plane, rm * A.nx + i);
+#pragma unroll
+        for (int g = 0; g < NQ; ++g) {
+            const double s = G::x(g);
+            double F = vBp[g] * eval<NC>(cn, s, 1.) + vBm[g] * eval<NC>(c, s, 0.);
+            add_psi<NC>(rr, F, s, 0.);
+        }
+        // top edge (eta = 1)
+        load_cell<NC>(cn, A.src[f], A.plane, rp * A.nx + i);
+#pragma unroll
+        for (int g = 0; g < NQ; ++g) {
+            const double s = G::x(g);
+            double F = vTp[g] * eval<NC>(c, s, 1.) + vTm[g] * eval<NC>(cn, s, 0.);
+            add_psi<NC>(rr, -F, s, 1.);
+        }
+        constexpr double IM[6] = { 1., 12., 12., 180., 180., 144. };
+#pragma unroll
+        for (int q = 0; q < NC; ++q) {
+            double val = c[q] + A.dt * IM[q] * rr[q];
+            if (HAS_BASE)
+                val = A.a * __ldg(A.base[f] + q * A.plane + k) + A.b * val;
+            A.dst[f][q * A.plane + k] = val;
+        }
+    }
+}
+
+// bounds-preserving rescaling of the higher moments about the cell mean (oracle/dg_transport.c)
+template <int NC>
+__global__ void limit_kernel(double* phi, int64_t nx, int64_t nyl, int64_t plane, double lo, double hi)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t r = 1 + (int64_t)blockIdx.y;
+    if (i >= nx || r > nyl)
+        return;
+    const int64_t k = r * nx + i;
+    double c[NC];
+#pragma unroll
+    for (int q = 0; q < NC; ++q)
+        c[q] = phi[q * plane + k];
+    double mean = c[0], mn = mean, mx = mean;
+#pragma unroll
+    for (int a = 0; a < 3; ++a)
+#pragma unroll
+        for (int b = 0; b < 3; ++b) {
+            double p = eval<NC>(c, 0.5 * a, 0.5 * b);
+            mn = fmin(mn, p);
+            mx = fmax(mx, p);
+        }
+    double theta = 1.;
+    if (mn < lo)
+        theta = fmin(theta, fmax(0., (mean - lo) / (mean - mn)));
+    if (mx > hi)
+        theta = fmin(theta, fmax(0., (hi - mean) / (mx - mean)));
+    if (theta < 1.) {
+#pragma unroll
+        for (int q = 1; q < NC; ++q)
+            phi[q * plane + k] = c[q] * theta;
+    }
+}
+
+template <int NC, int NF>
+void launch_stage(const StageArgs& A, bool has_base, dim3 grid, dim3 block, cudaStream_t s)
+{
+    if (has_base)
+        transport_stage_kernel<NC, NF, true><<<grid, block, 0, s>>>(A);
+    else
+        transport_stage_kernel<NC, NF, false><<<grid, block, 0, s>>>(A);
+}
+
+} // namespace
+
+int nsdg_transport_stage(nsdg_ctx* ctx, int nfields, double* const* src, double* const* base,
+    double* const* dst, double a, double b, double dt, int64_t r0, int64_t r1)
+{
+    DynState* d = ctx->dyn;
+    if (r1 <= r0)
+        return NSDG_OK;
+    StageArgs A;
+    for (int f = 0; f < 2; ++f) {
+        A.src[f] = f < nfields ? src[f] : nullptr;
+        A.base[f] = (f < nfields && base) ? base[f] : nullptr;
+        A.dst[f] = f < nfields ? dst[f] : nullptr;
+    }
+    A.u = d->f[NSDG_DF_U];
+    A.v = d->f[NSDG_DF_V];
+    A.a = a;
+    A.b = b;
+    A.dt = dt;
+    A.ihx = 1. / d->cfg.hx;
+    A.ihy = 1. / d->cfg.hy;
+    A.nx = d->nx;
+    A.nyl = d->nyl;
+    A.plane = d->plane;
+    A.r0 = r0;
+    A.r1 = r1;
+    A.wrap = d->wrap ? 1 : 0;
+    dim3 block(64, 4);
+    dim3 grid((unsigned)((d->nx + 63) / 64), (unsigned)((r1 - r0 + 3) / 4));
+    const bool hb = base != nullptr;
+    if (d->nc == 1) {
+        if (nfields == 1)
+            launch_stage<1, 1>(A, hb, grid, block, ctx->stream);
+        else
+            launch_stage<1, 2>(A, hb, grid, block, ctx->stream);
+    } else if (d->nc == 3) {
+        if (nfields == 1)
+            launch_stage<3, 1>(A, hb, grid, block, ctx->stream);
+        else
+            launch_stage<3, 2>(A, hb, grid, block, ctx->stream);
+    } else {
+        if (nfields == 1)
+            launch_stage<6, 1>(A, hb, grid, block, ctx->stream);
+        else
+            launch_stage<6, 2>(A, hb, grid, block, ctx->stream);
+    }
+    NSDG_LAUNCHED(ctx);
+    return NSDG_OK;
+}
+
+int nsdg_transport_limit(nsdg_ctx* ctx, double* phi, double lo, double hi)
+{
+    DynState* d = ctx->dyn;
+    if (d->nc == 1)
+        return NSDG_OK;
+    dim3 block(128), grid((unsigned)((d->nx + 127) / 128), (unsigned)d->nyl);
+    if (d->nc == 3)
+        limit_kernel<3><<<grid, block, 0, ctx->stream>>>(phi, d->nx, d->nyl, d->plane, lo, hi);
+    else
+        limit_kernel<6><<<grid, block, 0, ctx->stream>>>(phi, d->nx, d->nyl, d->plane, lo, hi);
+    NSDG_LAUNCHED(ctx);
+    return NSDG_OK;
+}

@@ -1,0 +1,227 @@
+"""Python host side above the C ABI.  Mirrors the reference's step interface for the path:
+`GpuStep` has the IModelStep verbs (core/src/include/IModelStep.hpp:16-34: setInitialData,
+init, start, iterate, stop, writeRestartFile) over structure-of-arrays state; `GpuDynamics`
+drives DG transport + mEVP.  All compute goes through csrc/libnsdg_gpu.so; nothing here
+computes on the CPU and there is no fallback.
+"""
+import ctypes
+
+import numpy as np
+
+from . import _abi
+from ._abi import (DYN_FIELDS, THERMO_DIAG, THERMO_FIELDS, DynConfig, MevpParams, ThermoParams,
+                   c_double_p, check)
+
+PROGNOSTIC = ("hice", "cice", "hsnow", "sst", "sss", "tice")
+FORCING = ("tair", "tdew", "slp", "qsw", "qlw", "mld", "snowfall", "wind")
+
+
+def _f64(a, n=None):
+    a = np.ascontiguousarray(a, dtype=np.float64)
+    if n is not None and a.size != n:
+        raise ValueError(f"expected {n} values, got {a.size}")
+    return a
+
+
+def _p(a):
+    return a.ctypes.data_as(c_double_p)
+
+
+class Context:
+    """One nsdg_ctx: one GPU, one compute stream."""
+
+    def __init__(self, device=0):
+        self.lib = _abi.load()
+        h = ctypes.c_void_p()
+        rc = self.lib.nsdg_create(ctypes.byref(h), int(device))
+        if rc != 0:
+            raise _abi.NsdgError(rc, f"nsdg_create(device={device}) failed: no CUDA device; "
+                                     "this package has no CPU path")
+        self.h = h
+        self.device = device
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.nsdg_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def synchronize(self):
+        check(self.h, self.lib.nsdg_synchronize(self.h))
+
+    @property
+    def launches(self):
+        return int(self.lib.nsdg_launch_count(self.h))
+
+    def timer_start(self):
+        check(self.h, self.lib.nsdg_timer_start(self.h))
+
+    def timer_stop(self):
+        ms = ctypes.c_double()
+        check(self.h, self.lib.nsdg_timer_stop(self.h, ctypes.byref(ms)))
+        return ms.value
+
+    # strip decomposition -----------------------------------------------------------------
+    def comm_init(self, rank, nranks, unique_id=None):
+        buf = (ctypes.c_char * _abi.COMM_ID_BYTES).from_buffer_copy(
+            unique_id if unique_id is not None else bytes(_abi.COMM_ID_BYTES))
+        check(self.h, self.lib.nsdg_comm_init(self.h, ctypes.cast(buf, ctypes.c_void_p), rank,
+                                              nranks))
+
+    @staticmethod
+    def comm_unique_id():
+        buf = (ctypes.c_char * _abi.COMM_ID_BYTES)()
+        rc = _abi.load().nsdg_comm_get_unique_id(ctypes.cast(buf, ctypes.c_void_p))
+        if rc != 0:
+            raise _abi.NsdgError(rc, "ncclGetUniqueId failed")
+        return bytes(buf)
+
+    @property
+    def comm_bytes_sent(self):
+        return int(self.lib.nsdg_comm_bytes_sent(self.h))
+
+
+class GpuStep:
+    """Drop-in for the reference's DevStep (core/src/DevStep.cpp:14-23) over SoA arrays.
+
+    setInitialData gathers/uploads, iterate(dt) launches the fused kernel on device-resident
+    state, stop()/get_prognostic() scatter back.  Cell order = the reference's cursor order
+    (DevGrid: index i*nx + j, core/src/DevGridIO.cpp:107-109); tice is [cell][layer].
+    """
+
+    def __init__(self, ctx, ncells, nlayers=1, params=None):
+        self.ctx, self.lib, self.h = ctx, ctx.lib, ctx.h
+        self.n, self.nlayers = int(ncells), int(nlayers)
+        check(self.h, self.lib.nsdg_thermo_init(self.h, self.n, self.nlayers))
+        self.set_params(params if params is not None else ThermoParams.defaults())
+
+    def set_params(self, params):
+        self.params = params
+        check(self.h, self.lib.nsdg_thermo_set_params(self.h, ctypes.byref(params)))
+
+    # IModelStep verbs ----------------------------------------------------------------------
+    def setInitialData(self, prognostic, forcing):
+        n = self.n
+        pr = [_f64(prognostic[k], n * (self.nlayers if k == "tice" else 1)) for k in PROGNOSTIC]
+        check(self.h, self.lib.nsdg_thermo_upload_prognostic(self.h, *[_p(a) for a in pr]))
+        self.setForcing(forcing)
+
+    def setForcing(self, forcing):
+        fo = [_f64(forcing[k], self.n) for k in FORCING]
+        check(self.h, self.lib.nsdg_thermo_upload_forcing(self.h, *[_p(a) for a in fo]))
+
+    def init(self):
+        pass
+
+    def start(self, start_time=0):
+        pass
+
+    def iterate(self, dt, nsteps=1, diagnostics=False):
+        fn = self.lib.nsdg_thermo_step_diag if diagnostics else self.lib.nsdg_thermo_step
+        check(self.h, fn(self.h, float(dt), int(nsteps)))
+
+    def stop(self, stop_time=0):
+        self.ctx.synchronize()
+
+    def writeRestartFile(self, path):
+        """Minimal restart: the 6 prognostic fields + the hidden newice state, as .npz."""
+        d = self.get_prognostic()
+        d["newice"] = self.get_newice()
+        np.savez(path, **d)
+
+    # accessors -----------------------------------------------------------------------------
+    def get_prognostic(self):
+        n = self.n
+        out = {k: np.empty(n * (self.nlayers if k == "tice" else 1)) for k in PROGNOSTIC}
+        check(self.h, self.lib.nsdg_thermo_download_prognostic(
+            self.h, *[_p(out[k]) for k in PROGNOSTIC]))
+        return out
+
+    def get_newice(self):
+        a = np.empty(self.n)
+        check(self.h, self.lib.nsdg_thermo_download_newice(self.h, _p(a)))
+        return a
+
+    def set_newice(self, a):
+        a = _f64(a, self.n)
+        check(self.h, self.lib.nsdg_thermo_upload_newice(self.h, _p(a)))
+
+    def get_diagnostics(self):
+        d = np.empty((len(THERMO_DIAG), self.n))
+        check(self.h, self.lib.nsdg_thermo_download_diagnostics(self.h, _p(d)))
+        return {k: d[q] for q, k in enumerate(THERMO_DIAG)}
+
+    def field_ptr(self, name):
+        p = ctypes.c_void_p()
+        check(self.h, self.lib.nsdg_thermo_field_ptr(self.h, THERMO_FIELDS.index(name),
+                                                     ctypes.byref(p)))
+        return p.value
+
+    def run_host(self, dt, nsteps, prognostic, forcing):
+        """One C-ABI call with host buffers: upload, nsteps sweeps, download (in place)."""
+        n = self.n
+        pr = {k: _f64(prognostic[k], n * (self.nlayers if k == "tice" else 1)) for k in PROGNOSTIC}
+        fo = [_f64(forcing[k], n) for k in FORCING]
+        check(self.h, self.lib.nsdg_thermo_run_host(
+            self.h, float(dt), int(nsteps), _p(pr["hice"]), _p(pr["cice"]), _p(pr["hsnow"]),
+            _p(pr["sst"]), _p(pr["sss"]), _p(pr["tice"]), *[_p(a) for a in fo]))
+        return pr
+
+
+class GpuDynamics:
+    """DG transport (dG0/1/2) + mEVP on one strip of a structured periodic grid."""
+
+    def __init__(self, ctx, nx, ny_global, hx, hy, ncomp=6, ny_local=None, j0=0, rk_order=0,
+                 limiter=0, mevp=None):
+        self.ctx, self.lib, self.h = ctx, ctx.lib, ctx.h
+        self.nx, self.ny_global = int(nx), int(ny_global)
+        self.ny = int(ny_local if ny_local is not None else ny_global)
+        self.ncomp = int(ncomp)
+        self.cfg = DynConfig(self.nx, self.ny_global, self.ny, int(j0), float(hx), float(hy),
+                             self.ncomp, int(rk_order), int(limiter), 0)
+        check(self.h, self.lib.nsdg_dyn_init(self.h, ctypes.byref(self.cfg)))
+        self.set_mevp_params(mevp if mevp is not None else MevpParams.defaults())
+
+    def set_mevp_params(self, p):
+        self.mevp = p
+        check(self.h, self.lib.nsdg_dyn_set_mevp_params(self.h, ctypes.byref(p)))
+
+    def field_shape(self, name):
+        nc = self.lib.nsdg_dyn_field_ncomp(self.h, DYN_FIELDS.index(name))
+        return (nc, self.ny, self.nx) if nc > 1 or name in ("H", "A") else (self.ny, self.nx)
+
+    def upload(self, name, host):
+        shape = self.field_shape(name)
+        a = _f64(host, int(np.prod(shape)))
+        check(self.h, self.lib.nsdg_dyn_upload(self.h, DYN_FIELDS.index(name), _p(a)))
+
+    def download(self, name):
+        out = np.empty(self.field_shape(name))
+        check(self.h, self.lib.nsdg_dyn_download(self.h, DYN_FIELDS.index(name), _p(out)))
+        return out
+
+    def upload_all(self, fields):
+        for k, v in fields.items():
+            self.upload(k, v)
+
+    def transport_step(self, dt, field=None):
+        if field is None:
+            check(self.h, self.lib.nsdg_transport_step_HA(self.h, float(dt)))
+        else:
+            check(self.h, self.lib.nsdg_transport_step(self.h, DYN_FIELDS.index(field), float(dt)))
+
+    def mevp_step(self, dt, nsub=100):
+        check(self.h, self.lib.nsdg_mevp_step(self.h, float(dt), int(nsub)))
+
+    def step(self, dt, nsub=100):
+        check(self.h, self.lib.nsdg_dyn_step(self.h, float(dt), int(nsub)))
+
+    def mass(self, name):
+        m = ctypes.c_double()
+        check(self.h, self.lib.nsdg_dyn_mass(self.h, DYN_FIELDS.index(name), ctypes.byref(m)))
+        return m.value
