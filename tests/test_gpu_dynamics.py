@@ -1,0 +1,196 @@
+"""GPU parity tests of DG transport and the mEVP sub-cycle, through the C ABI, against the CPU
+restatement (oracle/dg_transport.c, oracle/mevp.c).  Tolerance (BASELINE.json north_star):
+1e-11 relative (to the field's max-norm) on the DG coefficients after N steps.
+PARITY UNPINNED against draenog/nextsimdg: its snapshot has no dynamics code."""
+import numpy as np
+import pytest
+
+from nextsimdg_b200 import synthetic as S
+from nextsimdg_b200._abi import BC_BOX, BC_PERIODIC, MevpParams, NsdgError
+from nextsimdg_b200.gpu import GpuDynamics
+from oracle import cpu_oracle as O
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-11
+
+
+def maxrel(got, ref):
+    return np.abs(got - ref).max() / max(np.abs(ref).max(), 1e-300)
+
+
+def random_velocity(nx, ny, seed, scale=1.0):
+    r = np.random.default_rng(seed)
+    return scale * r.standard_normal((ny, nx)), scale * r.standard_normal((ny, nx))
+
+
+@pytest.mark.parametrize("ncomp", [1, 3, 6])
+@pytest.mark.parametrize("shape", [(64, 48), (37, 29), (130, 5)])
+def test_transport_matches_oracle(ctx, ncomp, shape):
+    """dG0/dG1/dG2, ragged grid sizes (not multiples of the CTA tile), random velocity with
+    sign changes along every edge (pointwise upwinding), N = 5 steps."""
+    nx, ny = shape
+    hx, hy = 1.0 / nx, 1.0 / ny
+    rng = np.random.default_rng(7)
+    f = lambda x, y: np.sin(2 * np.pi * x) * np.cos(2 * np.pi * y) + 2
+    phi = S.project(f, nx, ny, hx, hy, ncomp) + 0.05 * rng.standard_normal((ncomp, ny, nx))
+    u, v = random_velocity(nx, ny, 9)
+    dt = 0.02 * min(hx, hy)
+    dyn = GpuDynamics(ctx, nx, ny, hx, hy, ncomp)
+    dyn.upload("H", phi)
+    dyn.upload("U", u)
+    dyn.upload("V", v)
+    ref = phi
+    m0 = dyn.mass("H")
+    for _ in range(5):
+        dyn.transport_step(dt, "H")
+        ref = O.transport_step(ref, u, v, hx, hy, dt)
+    got = dyn.download("H")
+    assert maxrel(got, ref) < RTOL
+    assert abs(dyn.mass("H") - m0) / abs(m0) < 1e-13  # conservation on the GPU itself
+    assert dyn.mass("H") == pytest.approx(ref[0].sum() * hx * hy, rel=1e-12)
+
+
+@pytest.mark.parametrize("rk", [1, 2, 3])
+def test_rk_orders_and_two_field_kernel(ctx, rk):
+    nx, ny, nc = 48, 40, 6
+    hx, hy = 1.0 / nx, 1.0 / ny
+    rng = np.random.default_rng(rk)
+    H = rng.standard_normal((nc, ny, nx))
+    A = rng.standard_normal((nc, ny, nx))
+    u, v = random_velocity(nx, ny, 4)
+    dyn = GpuDynamics(ctx, nx, ny, hx, hy, nc, rk_order=rk)
+    dyn.upload_all(dict(H=H, A=A, U=u, V=v))
+    dt = 0.01 * hx
+    for _ in range(3):
+        dyn.transport_step(dt)  # H and A in one launch per stage
+        H = O.transport_step(H, u, v, hx, hy, dt, rk)
+        A = O.transport_step(A, u, v, hx, hy, dt, rk)
+    assert maxrel(dyn.download("H"), H) < RTOL
+    assert maxrel(dyn.download("A"), A) < RTOL
+
+
+def test_limiter_matches_oracle(ctx):
+    nx, ny, nc = 40, 32, 6
+    hx, hy = 1.0 / nx, 1.0 / ny
+    f = lambda x, y: ((np.abs(x - 0.5) < 0.2) & (np.abs(y - 0.5) < 0.2)).astype(float)
+    A = S.project(f, nx, ny, hx, hy, nc)
+    u, v = np.full((ny, nx), 1.0), np.full((ny, nx), 0.5)
+    dyn = GpuDynamics(ctx, nx, ny, hx, hy, nc, limiter=1)
+    dyn.upload_all(dict(A=A, U=u, V=v))
+    dt = 0.05 * hx
+    ref = A
+    for _ in range(10):
+        dyn.transport_step(dt, "A")
+        ref = O.transport_step(ref, u, v, hx, hy, dt, 0, 1, 0.0, 1.0)
+    got = dyn.download("A")
+    assert maxrel(got, ref) < 1e-10
+    for a in (0, 0.5, 1):
+        for b in (0, 0.5, 1):
+            val = S.evaluate(got, a, b)
+            assert val.min() > -1e-12 and val.max() < 1 + 1e-12
+
+
+def test_cone_rotation_dg1_quarter_turn(ctx):
+    """BASELINE config 2 at reduced size (128^2 dG1): compact bump in a tapered rotation;
+    mass conserved and GPU == oracle after the run."""
+    n, nc = 128, 3
+    phi, u, v, hx, hy, f0 = S.cone_case(n, n, nc)
+    dyn = GpuDynamics(ctx, n, n, hx, hy, nc)
+    dyn.upload_all(dict(H=phi, U=u, V=v))
+    nsteps = 60
+    dt = 0.25 / nsteps / 4
+    ref = phi
+    m0 = dyn.mass("H")
+    for _ in range(nsteps):
+        dyn.transport_step(dt, "H")
+        ref = O.transport_step(ref, u, v, hx, hy, dt)
+    got = dyn.download("H")
+    assert maxrel(got, ref) < RTOL
+    assert abs(dyn.mass("H") - m0) / m0 < 1e-13
+
+
+@pytest.mark.parametrize("bc", [BC_PERIODIC, BC_BOX])
+@pytest.mark.parametrize("shape", [(64, 48), (33, 21)])
+def test_mevp_matches_oracle(ctx, bc, shape):
+    nx, ny = shape
+    F, hx, hy = S.box_case(nx, ny, 6)
+    rng = np.random.default_rng(5)
+    F["U"] = 0.05 * rng.standard_normal((ny, nx))
+    F["V"] = 0.05 * rng.standard_normal((ny, nx))
+    F["S11"] = 100 * rng.standard_normal((3, ny, nx))
+    F["S12"] = 100 * rng.standard_normal((3, ny, nx))
+    F["S22"] = 100 * rng.standard_normal((3, ny, nx))
+    F["A"][0] = rng.uniform(0.7, 1.0, (ny, nx))
+    mp = MevpParams.defaults()
+    mp.bc = bc
+    mp.alpha = mp.beta = 300.0
+    dyn = GpuDynamics(ctx, nx, ny, hx, hy, 6, mevp=mp)
+    dyn.upload_all(F)
+    for nsub in (1, 7):  # odd counts exercise the ping-pong pointer swap
+        dyn.mevp_step(120.0, nsub)
+        ref = O.mevp_step(mp, F["H"], F["A"], F["U"], F["V"], F["S11"], F["S12"], F["S22"],
+                          F["UATM"], F["VATM"], F["UOCN"], F["VOCN"], hx, hy, 120.0, nsub)
+        for name, r in zip(("U", "V", "S11", "S12", "S22"), ref):
+            assert maxrel(dyn.download(name), r) < RTOL, (name, nsub)
+            F[name] = r
+    if bc == BC_BOX:
+        u = dyn.download("U")
+        assert np.all(u[0] == 0) and np.all(u[:, 0] == 0)
+
+
+def test_north_star_step_box_100_substeps(ctx):
+    """BASELINE config 3 at reduced size (96^2): 2 x (dG2 transport of H,A + 100 mEVP
+    sub-iterations), every state field against the oracle."""
+    n = 96
+    F, hx, hy = S.box_case(n, n, 6)
+    mp = MevpParams.defaults()
+    mp.bc = BC_BOX
+    dyn = GpuDynamics(ctx, n, n, hx, hy, 6, mevp=mp)
+    dyn.upload_all(F)
+    st = [F[k] for k in ("H", "A", "U", "V", "S11", "S12", "S22")]
+    for _ in range(2):
+        dyn.step(120.0, 100)
+        st = list(O.dyn_step(mp, *st, F["UATM"], F["VATM"], F["UOCN"], F["VOCN"], hx, hy, 120.0,
+                             100))
+    for name, r in zip(("H", "A", "U", "V", "S11", "S12", "S22"), st):
+        assert maxrel(dyn.download(name), r) < RTOL, name
+    assert 1e-4 < np.abs(st[2]).max() < 0.1  # the ice actually moves
+
+
+def test_size_independent_properties_large_grid(ctx):
+    """2048^2 dG2 (too large for the oracle in seconds): constants are preserved, mass is
+    conserved to round-off, zero forcing keeps a state of rest."""
+    n = 2048
+    F, hx, hy = S.box_case(n, n, 6)
+    mp = MevpParams.defaults()
+    mp.bc = BC_BOX
+    dyn = GpuDynamics(ctx, n, n, hx, hy, 6, mevp=mp)
+    dyn.upload_all(F)
+    dyn.step(120.0, 10)
+    mH, mA = dyn.mass("H"), dyn.mass("A")
+    dyn.step(120.0, 10)
+    assert abs(dyn.mass("H") - mH) / mH < 1e-13
+    assert abs(dyn.mass("A") - mA) / mA < 1e-13
+    A = dyn.download("A")
+    assert np.abs(A[0] - 1).max() < 1e-3
+    # state of rest
+    z = np.zeros((n, n))
+    dyn2 = GpuDynamics(ctx, n, n, hx, hy, 6, mevp=mp)
+    H = np.zeros((6, n, n))
+    H[0] = 1.0
+    dyn2.upload_all(dict(H=H, A=F["A"], U=z, V=z, UATM=z, VATM=z, UOCN=z, VOCN=z))
+    dyn2.step(120.0, 5)
+    assert np.abs(dyn2.download("U")).max() == 0.0
+    assert np.array_equal(dyn2.download("H")[0], H[0])
+
+
+def test_error_behaviour(ctx):
+    with pytest.raises(NsdgError):
+        GpuDynamics(ctx, 16, 16, 1.0, 1.0, ncomp=4)
+    with pytest.raises(NsdgError):  # a strip needs a communicator first
+        GpuDynamics(ctx, 16, 32, 1.0, 1.0, 6, ny_local=16)
+    dyn = GpuDynamics(ctx, 16, 16, 1.0, 1.0, 3)
+    with pytest.raises(NsdgError):
+        dyn.transport_step(0.1, "U")
+    with pytest.raises(ValueError):
+        dyn.upload("H", np.zeros((3, 16, 15)))

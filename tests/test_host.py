@@ -1,0 +1,160 @@
+"""CPU-side tests of the host logic: C-ABI exports, reference-compatible configuration, strip
+partitioning and the halo layout (2-rank gloo emulation of the exchange the GPU path does)."""
+import ctypes
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from nextsimdg_b200 import _abi, strips
+from nextsimdg_b200.config import thermo_params_from_ini
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    header = open(os.path.join(ROOT, "include", "nsdg_gpu.h")).read()
+    declared = set(re.findall(r"\b(nsdg_[A-Za-z0-9_]+)\s*\(", header))
+    declared -= {"nsdg_ctx"}
+    assert declared == set(_abi.SYMBOLS), declared ^ set(_abi.SYMBOLS)
+    lib = _abi.load()  # raises AttributeError on a missing export
+    assert lib.nsdg_abi_version() == 1
+    for name in declared:
+        assert hasattr(lib, name)
+
+
+def test_struct_layout_matches_header():
+    assert ctypes.sizeof(_abi.ThermoParams) == 12 * 8 + 4 * 4
+    assert ctypes.sizeof(_abi.MevpParams) == 13 * 8 + 8
+    assert ctypes.sizeof(_abi.DynConfig) == 4 * 8 + 2 * 8 + 4 * 4
+    lib = _abi.load()
+    p = _abi.ThermoParams()
+    lib.nsdg_thermo_default_params(ctypes.byref(p))
+    d = _abi.ThermoParams.defaults()
+    for f, _ in _abi.ThermoParams._fields_:
+        assert getattr(p, f) == getattr(d, f), f
+    m = _abi.MevpParams()
+    lib.nsdg_mevp_default_params(ctypes.byref(m))
+    dm = _abi.MevpParams.defaults()
+    for f, _ in _abi.MevpParams._fields_:
+        assert getattr(m, f) == getattr(dm, f), f
+
+
+@pytest.mark.skipif(os.path.exists("/dev/nvidia0"), reason="GPU present")
+def test_no_cpu_fallback():
+    """On a box without a GPU the product path must fail loudly, not compute on the CPU."""
+    from nextsimdg_b200.gpu import Context
+    with pytest.raises(_abi.NsdgError):
+        Context(0)
+
+
+def test_config_keys_and_module_names_follow_the_reference():
+    # same text as physics/test/NextsimPhysics_test.cpp:178-187
+    p = thermo_params_from_ini(
+        "[Modules]\nNextsim::IFreezingPoint = Nextsim::UnescoFreezing\n"
+        "Nextsim::IIceAlbedo = Nextsim::CCSMIceAlbedo\n\n[CCSMIceAlbedo]\niceAlbedo = 0.63\n"
+        "snowAlbedo = 0.88\n")
+    assert (p.freezing_kind, p.albedo_kind) == (1, 2)
+    assert (p.ccsm_ice_albedo, p.ccsm_snow_albedo) == (0.63, 0.88)
+    # NextsimPhysics_test.cpp:21-45 (config plumbing)
+    p = thermo_params_from_ini("[nextsim_thermo]\nmin_conc = 1e-5\nmin_thick = 0.02\nI_0 = 0.18\n"
+                               "[thermoice0]\nflooding = false\nks = 0.31\n[Hibler]\nh0 = 0.3\n")
+    assert (p.min_conc, p.min_thick, p.i0, p.flooding, p.ks, p.h0) == (1e-5, 0.02, 0.18, 0, 0.31,
+                                                                      0.3)
+    d = thermo_params_from_ini("")
+    assert (d.drag_ocean_q, d.albedo_w, d.phi_m, d.albedo_kind, d.freezing_kind) == (
+        1.5e-3, 0.07, 0.5, 0, 0)
+    # unknown implementation: the reference throws std::domain_error (ConfiguredModule.cpp:47-53)
+    with pytest.raises(ValueError, match="Invalid implementation"):
+        thermo_params_from_ini("[Modules]\nNextsim::IIceAlbedo = Nextsim::NoSuchAlbedo\n")
+
+
+def test_strip_partition_is_exact_cover():
+    for ny, nr in ((16384, 8), (4096, 3), (17, 4), (10, 5)):
+        rows = [strips.strip_rows(ny, nr, r) for r in range(nr)]
+        assert rows[0][0] == 0
+        for (a, n), (b, _) in zip(rows, rows[1:]):
+            assert a + n == b
+        assert rows[-1][0] + rows[-1][1] == ny
+        assert max(n for _, n in rows) - min(n for _, n in rows) <= 1
+    with pytest.raises(ValueError):
+        strips.strip_rows(5, 4, 0)
+    assert strips.neighbours(8, 0) == (7, 1) and strips.neighbours(8, 7) == (6, 0)
+    assert strips.neighbours(2, 0) == (1, 1)
+
+
+def test_halo_layout_is_plane_major():
+    n, sl = strips.halo_layout(5, 3)
+    assert n == 15 and sl == [(0, 5), (5, 10), (10, 15)]
+    g = np.arange(2 * 6 * 5, dtype=float).reshape(2, 6, 5)
+    # single rank ring: my own rows come back (periodic wrap)
+    p = strips.exchange_ghosts(strips.pad(g), lambda up, down: (up, down))
+    assert np.array_equal(p[:, 0], g[:, -1]) and np.array_equal(p[:, -1], g[:, 0])
+    assert np.array_equal(p[:, 1:-1], g)
+
+
+_GLOO_WORKER = r"""
+import os, sys
+import numpy as np
+import torch, torch.distributed as dist
+sys.path.insert(0, %r)
+from nextsimdg_b200 import strips, synthetic as S
+from oracle import cpu_oracle as O
+
+dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%%s" %% os.environ["PORT"],
+                        rank=int(os.environ["RANK"]), world_size=2)
+rank, nr = dist.get_rank(), 2
+nx, ny, nc = 24, 20, 6
+hx, hy = 1.0 / nx, 1.0 / ny
+rng = np.random.default_rng(3)
+phi = S.project(lambda x, y: np.sin(2*np.pi*x)*np.cos(2*np.pi*y) + 2, nx, ny, hx, hy, nc)
+u, v = rng.standard_normal((ny, nx)), rng.standard_normal((ny, nx))
+full = O.transport_rhs(phi, u, v, hx, hy)           # single-domain answer
+
+down, up = strips.neighbours(nr, rank)
+def send_recv(to_up, to_down):
+    # same order as csrc/comm.cu: send(up) recv(down) send(down) recv(up)
+    fd, fu = np.empty_like(to_up), np.empty_like(to_down)
+    ops = [dist.P2POp(dist.isend, torch.from_numpy(to_up), up, tag=1),
+           dist.P2POp(dist.irecv, torch.from_numpy(fd), down, tag=1),
+           dist.P2POp(dist.isend, torch.from_numpy(to_down), down, tag=2),
+           dist.P2POp(dist.irecv, torch.from_numpy(fu), up, tag=2)]
+    for w in dist.batch_isend_irecv(ops):
+        w.wait()
+    return fd, fu
+
+j0, nl = strips.strip_rows(ny, nr, rank)
+loc = strips.exchange_ghosts(strips.pad(strips.cut(phi, nr, rank)), send_recv)
+lu = strips.exchange_ghosts(strips.pad(strips.cut(u, nr, rank)), send_recv)
+lv = strips.exchange_ghosts(strips.pad(strips.cut(v, nr, rank)), send_recv)
+# ghost rows must be the neighbours' rows of the global array, bit exact
+assert np.array_equal(loc[:, 0], phi[:, (j0 - 1) %% ny]) and np.array_equal(loc[:, -1], phi[:, (j0 + nl) %% ny])
+# the operator on the padded strip (periodic wrap only touches ghost rows) == global rows
+r = O.transport_rhs(loc, lu, lv, hx, hy)[:, 1:-1]
+assert np.abs(r - full[:, j0:j0 + nl]).max() < 1e-12, np.abs(r - full[:, j0:j0+nl]).max()
+dist.barrier()
+print("rank", rank, "ok")
+"""
+
+
+def test_two_rank_strips_reproduce_single_domain_gloo(tmp_path):
+    """world_size-2 gloo run of the strip logic: cut, pack, exchange, unpack, apply the
+    operator on each strip, compare with the single-domain operator."""
+    import socket
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    script = tmp_path / "w.py"
+    script.write_text(_GLOO_WORKER % (ROOT,))
+    procs = []
+    for r in range(2):
+        env = dict(os.environ, RANK=str(r), PORT=str(port))
+        procs.append(subprocess.Popen([sys.executable, str(script)], env=env,
+                                      stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True))
+    outs = [p.communicate(timeout=240)[0] for p in procs]
+    for r, (p, o) in enumerate(zip(procs, outs)):
+        assert p.returncode == 0 and f"rank {r} ok" in o, o
