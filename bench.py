@@ -1,0 +1,341 @@
+#!/usr/bin/env python
+"""Benchmark of the north-star unit: one dG2 transport (H, A; SSP-RK3) + 100 mEVP sub-iterations
+step on a synthetic box-test grid.  `python bench.py --gpus N --steps K --warmup W`.
+
+metric   cell-updates/s = cells of the whole job x steps / max-over-ranks device time
+N = 1    BASELINE.json configs[2]: 4096 x 4096 cells, state resident in HBM
+N > 1    weak scaling: every rank owns a 4096 x 4096 strip of a 4096 x (4096 N) grid (ring of
+         strips over y, one-row halo per sub-iteration via NCCL send/recv); `--workload 16384sq`
+         runs BASELINE configs[4] (16384^2 split over N >= 2 ranks, strong scaling) instead
+e2e      same step through the C ABI with HOST (pinned) buffers: every step uploads the full
+         state + forcing and downloads the full state inside the timed region
+--impl reference   the CPU arm: the oracle's restatement of the same step on the host cores
+         (the reference snapshot has no dynamics code to run), bounded sample
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+NSUB = 100
+DT = 120.0
+NCOMP = 6
+# algorithmic bytes per cell (DESIGN.md "Roofline accounting"; counting rule of SURVEY.md 8d)
+BYTES_STRESS = (9 + 2 + 4 + 9) * 8  # r S(9) u,v(2) P_g(4)  w S(9)
+BYTES_VELOCITY = (9 + 2 + 2 + 2 + 2 + 2 + 2) * 8  # r S(9) u,v un,vn tau uo,vo Hn,An  w u,v
+BYTES_FUSED = (9 + 2 + 4 + 2 + 2 + 2 + 2 + 9 + 2) * 8  # one fused sub-iteration kernel
+BYTES_TRANSPORT_STEP = (2 * 8 * NCOMP + 6) * 8  # H and A, SSP-RK3, shared velocity reads
+BYTES_PREPARE = (12 + 4 + 2 + 2 + 2 + 2 + 2 + 2) * 8  # P_g, nodal H/A, wind stress, u^n copy
+BYTES_STEP = BYTES_TRANSPORT_STEP + BYTES_PREPARE + NSUB * (BYTES_STRESS + BYTES_VELOCITY)
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region."""
+
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx = float(f[1])
+            except ValueError:
+                continue
+            for nm, val in zip(names, f[2:6]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_step(F, hx, hy, mp, nsteps=1):
+    """The oracle's restatement of the bench step on the host cores (OpenMP, all threads)."""
+    from oracle import cpu_oracle as O
+    st = [F[k] for k in ("H", "A", "U", "V", "S11", "S12", "S22")]
+    t0 = time.perf_counter()
+    for _ in range(nsteps):
+        st = list(O.dyn_step(mp, *st, F["UATM"], F["VATM"], F["UOCN"], F["VOCN"], hx, hy, DT, NSUB))
+    return time.perf_counter() - t0
+
+
+def run_reference(args):
+    """--impl reference: CPU arm.  DG transport + mEVP do not exist in the reference snapshot
+    (CMakeLists.txt:43-46), so the arm is the oracle port of the same step, all host threads,
+    on a bounded sample (a 768^2 window of the same box test) per step."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from nextsimdg_b200 import synthetic as S
+    from nextsimdg_b200._abi import BC_BOX, MevpParams
+    n = args.cpu_sample
+    F, hx, hy = S.box_case(n, n, NCOMP)
+    mp = MevpParams.defaults()
+    mp.bc = BC_BOX
+    cores = os.cpu_count() or 1
+    for _ in range(args.warmup if args.warmup < 2 else 1):
+        cpu_step(F, hx, hy, mp)
+    secs = cpu_step(F, hx, hy, mp, args.steps)
+    value = n * n * args.steps / secs
+    sample = f"{n}x{n}-cell window of the box test, {args.steps} full steps (transport + {NSUB} sub-iterations)"
+    line = {"impl": "reference", "metric": "cell-updates/sec (dG2 transport+mEVP step)",
+            "value": value, "unit": "cell-updates/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * secs / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": workload_config(args, args.gpus),
+            "cpu_baseline": {"value": value, "unit": "cell-updates/s", "cores": cores,
+                             "kind": "port", "sample": sample,
+                             "note": "parity unpinned against draenog/nextsimdg: the reference "
+                                     "snapshot has no dynamics code; this is oracle/ (C, OpenMP)"},
+            "e2e": {"value": value, "unit": "cell-updates/s", "h2d_bytes_per_step": 0,
+                    "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, n):
+    if args.workload == "16384sq":
+        name = "synthetic 16384x16384 dG2 transport + mEVP (100 substeps), strips over y"
+        nx, ny = 16384, 16384
+    elif n == 1:
+        name = "synthetic 4096x4096 dG2 transport + mEVP rheology subcycle (100 substeps), 1 GPU"
+        nx, ny = args.nx, args.ny
+    else:
+        name = (f"synthetic {args.nx}x{args.ny * n} dG2 transport + mEVP (100 substeps): "
+                f"{n} strips of {args.nx}x{args.ny}, ring halo")
+        nx, ny = args.nx, args.ny * n
+    return {"workload": name, "nx": nx, "ny": ny, "substeps": NSUB, "dt_s": DT, "dg": "dG2",
+            "rk": "SSP-RK3", "bc": "box", "l2": "working set >> 126 MB L2 (>= 10 GB per GPU)",
+            "parity": "unpinned against draenog/nextsimdg (no dynamics in the reference snapshot)"}
+
+
+def run_gpu(args):
+    import torch
+    import torch.distributed as dist
+    from nextsimdg_b200 import strips, synthetic as S
+    from nextsimdg_b200._abi import BC_BOX, MevpParams
+    from nextsimdg_b200.gpu import Context, GpuDynamics
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torchrun")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; this framework has no CPU path")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    ctx = Context(local)
+    # ---- grid of this rank
+    if args.workload == "16384sq":
+        nx, ny_glob = 16384, 16384
+        j0, nyl = strips.strip_rows(ny_glob, world, rank)
+        Lx = Ly = 512e3
+    else:
+        nx, nyl = args.nx, args.ny
+        ny_glob, j0 = nyl * world, nyl * rank
+        Lx, Ly = 512e3, 512e3 * world
+    if world > 1:
+        uid = [Context.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        ctx.comm_init(rank, world, uid[0])
+    F, hx, hy = S.box_case(nx, ny_glob, NCOMP, L=Lx, Ly=Ly, rows=(j0, nyl))
+    mp = MevpParams.defaults()
+    mp.bc = BC_BOX
+    dyn = GpuDynamics(ctx, nx, ny_glob, hx, hy, NCOMP, ny_local=nyl, j0=j0, mevp=mp)
+    dyn.upload_all(F)
+    cells_local = nx * nyl
+    cells_total = nx * ny_glob
+
+    # ---- resident-state timing: W warm-up steps, then exactly K steps
+    for _ in range(args.warmup):
+        dyn.step(DT, NSUB)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = ctx.launches
+    ctx.profile_begin()
+    ctx.timer_start()
+    for _ in range(args.steps):
+        dyn.step(DT, NSUB)
+    ms = ctx.timer_stop()
+    prof = ctx.profile_end()
+    launches = ctx.launches - l0
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max = float(t.item())
+    value = cells_total * args.steps / (ms_max * 1e-3)
+    umax = float(np.abs(dyn.download("U")).max())
+    if not np.isfinite(umax):
+        raise SystemExit("bench.py: non-finite velocity after the timed steps")
+
+    # ---- e2e: host (pinned) buffers in and out through the C ABI every step
+    names = ("H", "A", "U", "V", "S11", "S12", "S22", "UATM", "VATM", "UOCN", "VOCN")
+    outs = ("H", "A", "U", "V", "S11", "S12", "S22")
+    host = {}
+    for k in names:
+        a = np.ascontiguousarray(F[k])
+        tpin = torch.empty(a.shape, dtype=torch.float64).pin_memory()
+        tpin.numpy()[...] = a
+        host[k] = tpin
+    h2d = sum(host[k].numel() * 8 for k in names)
+    d2h = sum(host[k].numel() * 8 for k in outs)
+    import ctypes
+    from nextsimdg_b200._abi import DYN_FIELDS, c_double_p, check
+
+    def ptr(tn):
+        return ctypes.cast(tn.data_ptr(), c_double_p)
+
+    def e2e_step():
+        for k in names:
+            check(ctx.h, ctx.lib.nsdg_dyn_upload(ctx.h, DYN_FIELDS.index(k), ptr(host[k])))
+        check(ctx.h, ctx.lib.nsdg_dyn_step(ctx.h, DT, NSUB))
+        for k in outs:
+            check(ctx.h, ctx.lib.nsdg_dyn_download(ctx.h, DYN_FIELDS.index(k), ptr(host[k])))
+
+    e2e_steps = max(1, min(args.steps, args.e2e_steps))
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    barrier()
+    te = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_value = cells_total * e2e_steps / float(te.item())
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        # dominant kernel of the step by measured share
+        dom = max(prof.items(), key=lambda kv: kv[1][0])
+        per_kernel_bytes = {"stress_kernel": BYTES_STRESS, "velocity_kernel": BYTES_VELOCITY,
+                            "mevp_fused_kernel": BYTES_FUSED,
+                            "transport_stage_kernel": BYTES_TRANSPORT_STEP / 3.0}
+        kname, (ktot, kcnt) = dom
+        kbytes = per_kernel_bytes.get(kname, 0) * cells_local
+        kavg_ms = ktot / kcnt
+        achieved = kbytes / (kavg_ms * 1e-3) / 1e9
+        step_gbs = BYTES_STEP * cells_local * args.steps / (ms * 1e-3) / 1e9
+        roof = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak,
+                "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
+                "traffic": args.traffic,
+                "algorithmic_bytes_per_launch": kbytes, "avg_launch_ms": kavg_ms,
+                "launches": kcnt, "share_of_step": ktot / ms,
+                "whole_step": {"bytes_per_cell": BYTES_STEP, "achieved": step_gbs,
+                               "frac": step_gbs / peak},
+                "kernels": {k: {"ms_total": v[0], "launches": v[1], "share": v[0] / ms}
+                            for k, v in sorted(prof.items(), key=lambda kv: -kv[1][0])}}
+        cpu = None
+        if args.gpus == 1 and not args.no_cpu:
+            n = args.cpu_sample
+            Fc, hxc, hyc = S.box_case(n, n, NCOMP)
+            secs = cpu_step(Fc, hxc, hyc, mp, 1)
+            cpu = {"value": n * n / secs, "unit": "cell-updates/s", "cores": os.cpu_count() or 1,
+                   "kind": "port",
+                   "sample": f"{n}x{n}-cell window of the same box test, 1 full step "
+                             f"(transport + {NSUB} sub-iterations), oracle/ C + OpenMP",
+                   "note": "parity unpinned against draenog/nextsimdg (no dynamics in the snapshot)"}
+        line = {"metric": "cell-updates/sec (dG2 transport+mEVP step)", "value": value,
+                "unit": "cell-updates/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms_max / args.steps,
+                "higher_is_better": True,
+                "scaling": "strong" if args.workload == "16384sq" else "weak",
+                "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": workload_config(args, world), "clocks": clocks,
+                "e2e": {"value": e2e_value, "unit": "cell-updates/s", "h2d_bytes_per_step": h2d,
+                        "d2h_bytes_per_step": d2h, "steps": e2e_steps,
+                        "what": "full state + forcing uploaded from pinned host memory, one "
+                                "nsdg_dyn_step, full state downloaded, every step"},
+                "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu,
+                "max_abs_u": umax,
+                "halo_bytes_sent_per_rank": ctx.comm_bytes_sent if world > 1 else 0}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    ctx.close()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="auto", choices=["auto", "16384sq"])
+    ap.add_argument("--nx", type=int, default=4096)
+    ap.add_argument("--ny", type=int, default=4096, help="rows per GPU")
+    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--cpu-sample", type=int, default=768, help="edge of the CPU sample window")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--traffic", type=float, default=None,
+                    help="dram bytes per launch of the dominant kernel from an ncu capture")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -164,6 +164,14 @@ int64_t nsdg_launch_count(const nsdg_ctx* ctx);
 int nsdg_timer_start(nsdg_ctx* ctx);
 int nsdg_timer_stop(nsdg_ctx* ctx, double* elapsed_ms);
 
+/* per-kernel timing: while enabled every launch is bracketed by a CUDA event pair on the
+ * context's stream; nsdg_profile_end resolves them.  Kernel ids 0..N-1, names via
+ * nsdg_profile_kernel_name (NULL past the end). */
+int nsdg_profile_begin(nsdg_ctx* ctx);
+int nsdg_profile_end(nsdg_ctx* ctx);
+int nsdg_profile_query(const nsdg_ctx* ctx, int32_t kernel, double* total_ms, int64_t* launches);
+const char* nsdg_profile_kernel_name(int32_t kernel);
+
 /* ---- column thermodynamics ---- */
 void nsdg_thermo_default_params(nsdg_thermo_params* p);
 int nsdg_thermo_init(nsdg_ctx* ctx, int64_t ncells, int32_t nlayers);

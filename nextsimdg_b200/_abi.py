@@ -72,6 +72,10 @@ SYMBOLS = {
     "nsdg_launch_count": (_i64, [_ctx]),
     "nsdg_timer_start": (ctypes.c_int, [_ctx]),
     "nsdg_timer_stop": (ctypes.c_int, [_ctx, c_double_p]),
+    "nsdg_profile_begin": (ctypes.c_int, [_ctx]),
+    "nsdg_profile_end": (ctypes.c_int, [_ctx]),
+    "nsdg_profile_query": (ctypes.c_int, [_ctx, _i32, c_double_p, ctypes.POINTER(_i64)]),
+    "nsdg_profile_kernel_name": (ctypes.c_char_p, [_i32]),
     "nsdg_thermo_default_params": (None, [ctypes.POINTER(ThermoParams)]),
     "nsdg_thermo_init": (ctypes.c_int, [_ctx, _i64, _i32]),
     "nsdg_thermo_set_params": (ctypes.c_int, [_ctx, ctypes.POINTER(ThermoParams)]),

@@ -121,8 +121,7 @@ int nsdg_halo_exchange(nsdg_ctx* ctx, const PlaneSet& planes, int which)
     A.buf_hi = fill_lo ? d->send_hi : nullptr;
     A.buf_lo = fill_hi ? d->send_lo : nullptr;
     dim3 block(256), grid((unsigned)((d->nx + 255) / 256), (unsigned)planes.n, 2);
-    pack_rows<<<grid, block, 0, ctx->stream>>>(A);
-    NSDG_LAUNCHED(ctx);
+    NSDG_KERNEL(ctx, NSDG_K_PACK, pack_rows<<<grid, block, 0, ctx->stream>>>(A));
     NSDG_NCCL(ctx, c, c->GroupStart());
     if (fill_lo) {
         NSDG_NCCL(ctx, c, c->Send(d->send_hi, count, ncclFloat64, up, c->comm, ctx->stream));
@@ -139,8 +138,7 @@ int nsdg_halo_exchange(nsdg_ctx* ctx, const PlaneSet& planes, int which)
     A.row_hi = d->nyl + 1;
     A.buf_lo = fill_lo ? d->recv_lo : nullptr;
     A.buf_hi = fill_hi ? d->recv_hi : nullptr;
-    unpack_rows<<<grid, block, 0, ctx->stream>>>(A);
-    NSDG_LAUNCHED(ctx);
+    NSDG_KERNEL(ctx, NSDG_K_UNPACK, unpack_rows<<<grid, block, 0, ctx->stream>>>(A));
     return NSDG_OK;
 }
 

@@ -14,7 +14,92 @@ int nsdg_fail(nsdg_ctx* ctx, int code, const char* fmt, ...)
     return code;
 }
 
+static void prof_flush(nsdg_ctx* ctx)
+{
+    NsdgProfiler& p = ctx->prof;
+    if (!p.used)
+        return;
+    cudaEventSynchronize(p.ev[2 * (p.used - 1) + 1]);
+    for (size_t i = 0; i < p.used; ++i) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, p.ev[2 * i], p.ev[2 * i + 1]) == cudaSuccess) {
+            p.total_ms[p.kid[i]] += ms;
+            p.count[p.kid[i]]++;
+        }
+    }
+    p.used = 0;
+}
+
+void nsdg_prof_begin(nsdg_ctx* ctx, int kid)
+{
+    NsdgProfiler& p = ctx->prof;
+    if (!p.on)
+        return;
+    if (p.used >= 16384)
+        prof_flush(ctx);
+    if (p.ev.size() < 2 * (p.used + 1)) {
+        cudaEvent_t a, b;
+        cudaEventCreate(&a);
+        cudaEventCreate(&b);
+        p.ev.push_back(a);
+        p.ev.push_back(b);
+        p.kid.push_back(kid);
+    }
+    p.kid[p.used] = kid;
+    cudaEventRecord(p.ev[2 * p.used], ctx->stream);
+}
+
+void nsdg_prof_end(nsdg_ctx* ctx)
+{
+    NsdgProfiler& p = ctx->prof;
+    if (!p.on)
+        return;
+    cudaEventRecord(p.ev[2 * p.used + 1], ctx->stream);
+    p.used++;
+}
+
+static const char* const KERNEL_NAMES[NSDG_K_COUNT] = { "thermo_kernel", "transport_stage_kernel",
+    "limit_kernel", "pressure_kernel", "nodal_kernel", "stress_kernel", "velocity_kernel",
+    "mevp_fused_kernel", "pack_rows", "unpack_rows", "other" };
+
 extern "C" {
+
+int nsdg_profile_begin(nsdg_ctx* ctx)
+{
+    NSDG_ENTER(ctx);
+    NsdgProfiler& p = ctx->prof;
+    prof_flush(ctx);
+    for (int k = 0; k < NSDG_K_COUNT; ++k) {
+        p.total_ms[k] = 0.;
+        p.count[k] = 0;
+    }
+    p.on = true;
+    return NSDG_OK;
+}
+
+int nsdg_profile_end(nsdg_ctx* ctx)
+{
+    NSDG_ENTER(ctx);
+    prof_flush(ctx);
+    ctx->prof.on = false;
+    return NSDG_OK;
+}
+
+int nsdg_profile_query(const nsdg_ctx* ctx, int32_t kernel, double* total_ms, int64_t* launches)
+{
+    if (!ctx || kernel < 0 || kernel >= NSDG_K_COUNT)
+        return NSDG_EINVAL;
+    if (total_ms)
+        *total_ms = ctx->prof.total_ms[kernel];
+    if (launches)
+        *launches = ctx->prof.count[kernel];
+    return NSDG_OK;
+}
+
+const char* nsdg_profile_kernel_name(int32_t kernel)
+{
+    return (kernel >= 0 && kernel < NSDG_K_COUNT) ? KERNEL_NAMES[kernel] : nullptr;
+}
 
 int nsdg_abi_version(void) { return NSDG_ABI_VERSION; }
 
@@ -56,6 +141,8 @@ int nsdg_destroy(nsdg_ctx* ctx)
     nsdg_comm_free(ctx);
     nsdg_dyn_free(ctx);
     nsdg_thermo_free(ctx);
+    for (cudaEvent_t e : ctx->prof.ev)
+        cudaEventDestroy(e);
     if (ctx->ev_start)
         cudaEventDestroy(ctx->ev_start);
     if (ctx->ev_stop)

@@ -5,6 +5,7 @@
 #include <cuda_runtime.h>
 #include <cstdio>
 #include <string>
+#include <vector>
 
 struct DynState; // dyn.cu
 struct CommState; // comm.cu
@@ -19,6 +20,31 @@ struct ThermoState {
     bool have_prog = false, have_forcing = false;
 };
 
+// kernel classes for the per-launch event profiler (nsdg_profile_*)
+enum NsdgKernelId {
+    NSDG_K_THERMO = 0,
+    NSDG_K_TRANSPORT,
+    NSDG_K_LIMIT,
+    NSDG_K_PRESSURE,
+    NSDG_K_NODAL,
+    NSDG_K_STRESS,
+    NSDG_K_VELOCITY,
+    NSDG_K_MEVP_FUSED,
+    NSDG_K_PACK,
+    NSDG_K_UNPACK,
+    NSDG_K_OTHER,
+    NSDG_K_COUNT
+};
+
+struct NsdgProfiler {
+    bool on = false;
+    std::vector<cudaEvent_t> ev; // pairs: 2*i start, 2*i+1 stop
+    std::vector<int> kid;
+    size_t used = 0; // pairs in flight
+    double total_ms[NSDG_K_COUNT] = {};
+    int64_t count[NSDG_K_COUNT] = {};
+};
+
 struct nsdg_ctx {
     int device = 0;
     cudaStream_t stream = nullptr; // compute
@@ -28,6 +54,7 @@ struct nsdg_ctx {
     int sm_count = 148;
     std::string error;
     bool cuda_failed = false; // sticky
+    NsdgProfiler prof;
     ThermoState* thermo = nullptr;
     DynState* dyn = nullptr;
     CommState* comm = nullptr;
@@ -70,6 +97,19 @@ int nsdg_fail(nsdg_ctx* ctx, int code, const char* fmt, ...);
     do {                                                                                          \
         (ctx)->launches++;                                                                        \
         NSDG_CUDA((ctx), cudaGetLastError());                                                     \
+    } while (0)
+
+// event pair around one launch when profiling is on (ctx.cu)
+void nsdg_prof_begin(nsdg_ctx* ctx, int kid);
+void nsdg_prof_end(nsdg_ctx* ctx);
+
+// NSDG_KERNEL(ctx, NSDG_K_X, kernel<<<grid, block, smem, ctx->stream>>>(args));
+#define NSDG_KERNEL(ctx, kid, ...)                                                                \
+    do {                                                                                          \
+        nsdg_prof_begin((ctx), (kid));                                                            \
+        __VA_ARGS__;                                                                              \
+        nsdg_prof_end((ctx));                                                                     \
+        NSDG_LAUNCHED(ctx);                                                                       \
     } while (0)
 
 // teardown hooks implemented by the owning translation unit

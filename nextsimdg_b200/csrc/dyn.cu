@@ -387,8 +387,7 @@ int nsdg_dyn_mass(nsdg_ctx* ctx, int32_t field, double* mass)
     NSDG_REQUIRE(ctx, d, NSDG_ESTATE, "nsdg_dyn_init has not been called");
     NSDG_REQUIRE(ctx, (field == NSDG_DF_H || field == NSDG_DF_A) && mass, NSDG_EINVAL, "bad field");
     NSDG_CUDA(ctx, cudaMemsetAsync(d->scratch, 0, sizeof(double), ctx->stream));
-    mass_kernel<<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(d->f[field], d->nx, d->nyl, d->scratch);
-    NSDG_LAUNCHED(ctx);
+    NSDG_KERNEL(ctx, NSDG_K_OTHER, mass_kernel<<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(d->f[field], d->nx, d->nyl, d->scratch));
     double s = 0.;
     NSDG_CUDA(ctx, cudaMemcpyAsync(&s, d->scratch, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
     NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));

@@ -277,8 +277,7 @@ int nsdg_mevp_prepare(nsdg_ctx* ctx)
     A.r1 = d->nyl + 1;
     A.out0 = d->pg;
     dim3 block(256), grid((unsigned)((d->nx + 255) / 256), (unsigned)(A.r1 - A.r0));
-    pressure_kernel<<<grid, block, 0, ctx->stream>>>(A);
-    NSDG_LAUNCHED(ctx);
+    NSDG_KERNEL(ctx, NSDG_K_PRESSURE, pressure_kernel<<<grid, block, 0, ctx->stream>>>(A));
     A.r0 = 1;
     A.r1 = d->nyl + 1;
     A.out0 = d->hn;
@@ -288,8 +287,7 @@ int nsdg_mevp_prepare(nsdg_ctx* ctx)
     A.out4 = d->un;
     A.out5 = d->vn;
     grid = dim3((unsigned)((d->nx + 255) / 256), (unsigned)d->nyl);
-    nodal_kernel<<<grid, block, 0, ctx->stream>>>(A);
-    NSDG_LAUNCHED(ctx);
+    NSDG_KERNEL(ctx, NSDG_K_NODAL, nodal_kernel<<<grid, block, 0, ctx->stream>>>(A));
     return NSDG_OK;
 }
 
@@ -304,8 +302,7 @@ int nsdg_mevp_stress(nsdg_ctx* ctx, const double* u, const double* v, int64_t r0
     A.r0 = r0;
     A.r1 = r1;
     dim3 block(64, 4), grid((unsigned)((d->nx + 63) / 64), (unsigned)((r1 - r0 + 3) / 4));
-    stress_kernel<<<grid, block, 0, ctx->stream>>>(A);
-    NSDG_LAUNCHED(ctx);
+    NSDG_KERNEL(ctx, NSDG_K_STRESS, stress_kernel<<<grid, block, 0, ctx->stream>>>(A));
     return NSDG_OK;
 }
 
@@ -324,7 +321,6 @@ int nsdg_mevp_velocity(nsdg_ctx* ctx, double dt, const double* u, const double* 
     A.r0 = r0;
     A.r1 = r1;
     dim3 block(64, 4), grid((unsigned)((d->nx + 63) / 64), (unsigned)((r1 - r0 + 3) / 4));
-    velocity_kernel<<<grid, block, 0, ctx->stream>>>(A);
-    NSDG_LAUNCHED(ctx);
+    NSDG_KERNEL(ctx, NSDG_K_VELOCITY, velocity_kernel<<<grid, block, 0, ctx->stream>>>(A));
     return NSDG_OK;
 }

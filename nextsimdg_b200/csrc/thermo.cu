@@ -374,10 +374,9 @@ int thermo_launch(nsdg_ctx* ctx, double dt, int nsteps, bool diag)
     int grid = (int)(want < cap ? (want > 0 ? want : 1) : cap);
     for (int s = 0; s < nsteps; ++s) {
         if (diag && s == nsteps - 1)
-            thermo_kernel<true><<<grid, block, 0, ctx->stream>>>(t->params, p, dt, t->n);
+            NSDG_KERNEL(ctx, NSDG_K_THERMO, thermo_kernel<true><<<grid, block, 0, ctx->stream>>>(t->params, p, dt, t->n));
         else
-            thermo_kernel<false><<<grid, block, 0, ctx->stream>>>(t->params, p, dt, t->n);
-        NSDG_LAUNCHED(ctx);
+            NSDG_KERNEL(ctx, NSDG_K_THERMO, thermo_kernel<false><<<grid, block, 0, ctx->stream>>>(t->params, p, dt, t->n));
     }
     return NSDG_OK;
 }

@@ -267,6 +267,7 @@ int nsdg_transport_stage(nsdg_ctx* ctx, int nfields, double* const* src, double*
     dim3 block(64, 4);
     dim3 grid((unsigned)((d->nx + 63) / 64), (unsigned)((r1 - r0 + 3) / 4));
     const bool hb = base != nullptr;
+    nsdg_prof_begin(ctx, NSDG_K_TRANSPORT);
     if (d->nc == 1) {
         if (nfields == 1)
             launch_stage<1, 1>(A, hb, grid, block, ctx->stream);
@@ -283,6 +284,7 @@ int nsdg_transport_stage(nsdg_ctx* ctx, int nfields, double* const* src, double*
         else
             launch_stage<6, 2>(A, hb, grid, block, ctx->stream);
     }
+    nsdg_prof_end(ctx);
     NSDG_LAUNCHED(ctx);
     return NSDG_OK;
 }
@@ -294,9 +296,8 @@ int nsdg_transport_limit(nsdg_ctx* ctx, double* phi, double lo, double hi)
         return NSDG_OK;
     dim3 block(128), grid((unsigned)((d->nx + 127) / 128), (unsigned)d->nyl);
     if (d->nc == 3)
-        limit_kernel<3><<<grid, block, 0, ctx->stream>>>(phi, d->nx, d->nyl, d->plane, lo, hi);
+        NSDG_KERNEL(ctx, NSDG_K_LIMIT, limit_kernel<3><<<grid, block, 0, ctx->stream>>>(phi, d->nx, d->nyl, d->plane, lo, hi));
     else
-        limit_kernel<6><<<grid, block, 0, ctx->stream>>>(phi, d->nx, d->nyl, d->plane, lo, hi);
-    NSDG_LAUNCHED(ctx);
+        NSDG_KERNEL(ctx, NSDG_K_LIMIT, limit_kernel<6><<<grid, block, 0, ctx->stream>>>(phi, d->nx, d->nyl, d->plane, lo, hi));
     return NSDG_OK;
 }

@@ -66,6 +66,23 @@ class Context:
         check(self.h, self.lib.nsdg_timer_stop(self.h, ctypes.byref(ms)))
         return ms.value
 
+    def profile_begin(self):
+        check(self.h, self.lib.nsdg_profile_begin(self.h))
+
+    def profile_end(self):
+        """-> {kernel name: (total_ms, launches)} for the launches since profile_begin"""
+        check(self.h, self.lib.nsdg_profile_end(self.h))
+        out, k = {}, 0
+        while True:
+            name = self.lib.nsdg_profile_kernel_name(k)
+            if not name:
+                return out
+            ms, cnt = ctypes.c_double(), ctypes.c_int64()
+            self.lib.nsdg_profile_query(self.h, k, ctypes.byref(ms), ctypes.byref(cnt))
+            if cnt.value:
+                out[name.decode()] = (ms.value, cnt.value)
+            k += 1
+
     # strip decomposition -----------------------------------------------------------------
     def comm_init(self, rank, nranks, unique_id=None):
         buf = (ctypes.c_char * _abi.COMM_ID_BYTES).from_buffer_copy(

@@ -41,12 +41,12 @@ def basis(xi, eta):
     return [np.ones_like(a), a, b, a * a - 1 / 12, b * b - 1 / 12, a * b]
 
 
-def project(fn, nx, ny, hx, hy, ncomp, nq=4):
-    """L2 projection of fn(x,y) onto the modal dG basis: [ncomp][ny][nx]."""
+def project(fn, nx, ny, hx, hy, ncomp, nq=4, j0=0):
+    """L2 projection of fn(x,y) onto the modal dG basis: [ncomp][ny][nx] (rows j0..j0+ny)."""
     gx, gw = np.polynomial.legendre.leggauss(nq)
     gx, gw = 0.5 * (gx + 1), 0.5 * gw
     i = np.arange(nx)[None, :]
-    j = np.arange(ny)[:, None]
+    j = (j0 + np.arange(ny))[:, None]
     out = np.zeros((ncomp, ny, nx))
     for a in range(nq):
         for b in range(nq):
@@ -103,18 +103,22 @@ def cone_case(nx, ny, ncomp):
     return project(f0, nx, ny, hx, hy, ncomp), u, v, hx, hy, f0
 
 
-def box_case(nx, ny, ncomp, L=512e3, t=0.0):
+def box_case(nx, ny, ncomp, L=512e3, t=0.0, rows=None, Ly=None):
     """Configs 3/5: Mehlmann et al. (2021)-style box test scaled to the grid: 512 km square,
     H = 0.3 + 0.005 (sin(6e-5 x) + sin(3e-5 y)), A = 1, anticyclonic ocean gyre, moving
-    cyclone wind; closed box (NSDG_BC_BOX).  Returns dict of fields + hx, hy."""
-    hx, hy = L / nx, L / ny
+    cyclone wind; closed box (NSDG_BC_BOX).  `rows=(j0, nl)` returns only that strip of the
+    global nx x ny grid.  Returns dict of fields + hx, hy."""
+    Ly = L if Ly is None else Ly
+    hx, hy = L / nx, Ly / ny
+    j0, nl = (0, ny) if rows is None else rows
     H = project(lambda x, y: 0.3 + 0.005 * (np.sin(6e-5 * x) + np.sin(3e-5 * y)),
-                nx, ny, hx, hy, ncomp, nq=3)
+                nx, nl, hx, hy, ncomp, nq=3, j0=j0)
     A = np.zeros_like(H)
     A[0] = 1.0
-    xn = (np.arange(nx) * hx)[None, :] + 0.0 * np.arange(ny)[:, None]
-    yn = (np.arange(ny) * hy)[:, None] + 0.0 * np.arange(nx)[None, :]
-    uocn = 0.1 * (2 * yn - L) / L
+    xn = (np.arange(nx) * hx)[None, :] + 0.0 * np.arange(nl)[:, None]
+    yn = ((j0 + np.arange(nl)) * hy)[:, None] + 0.0 * np.arange(nx)[None, :]
+    ny = nl
+    uocn = 0.1 * (2 * yn - Ly) / Ly
     vocn = -0.1 * (2 * xn - L) / L
     # cyclone centred at (256 km + 51.2 km/day * t) moving along the diagonal
     tday = t / 86400.0
