@@ -149,8 +149,11 @@ typedef struct nsdg_dyn_config {
     int32_t ncomp; /* 1, 3 or 6: dG0 / dG1 / dG2 tracers */
     int32_t rk_order; /* 0 = match ncomp (1->RK1, 3->Heun RK2, 6->SSP-RK3), else 1,2,3 */
     int32_t limiter; /* 0 off (default), 1 bounds-preserving rescaling of higher moments */
-    int32_t _pad;
+    int32_t flags; /* NSDG_DYN_* bits, 0 = defaults */
 } nsdg_dyn_config;
+
+/* use the two-kernel (stress, velocity) sub-iteration instead of the fused kernel */
+#define NSDG_DYN_SPLIT_MEVP 1
 
 /* ---- context ---- */
 int nsdg_abi_version(void);

@@ -57,7 +57,10 @@ class DynConfig(ctypes.Structure):
     _fields_ = [("nx", ctypes.c_int64), ("ny_global", ctypes.c_int64), ("ny_local", ctypes.c_int64),
                 ("j0", ctypes.c_int64), ("hx", ctypes.c_double), ("hy", ctypes.c_double),
                 ("ncomp", ctypes.c_int32), ("rk_order", ctypes.c_int32),
-                ("limiter", ctypes.c_int32), ("_pad", ctypes.c_int32)]
+                ("limiter", ctypes.c_int32), ("flags", ctypes.c_int32)]
+
+
+DYN_SPLIT_MEVP = 1
 
 
 # every symbol include/nsdg_gpu.h declares: name -> (restype, argtypes)

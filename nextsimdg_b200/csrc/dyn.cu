@@ -158,11 +158,21 @@ int mevp_cycle(nsdg_ctx* ctx, double dt, int nsub)
         return rc;
     double *u = d->f[NSDG_DF_U], *v = d->f[NSDG_DF_V], *u2 = d->u2, *v2 = d->v2;
     const int64_t s0 = multi ? 0 : 1;
+    const bool fused = !(d->cfg.flags & NSDG_DYN_SPLIT_MEVP);
+    double* sa[3] = { d->f[NSDG_DF_S11], d->f[NSDG_DF_S12], d->f[NSDG_DF_S22] };
+    double* sb[3] = { d->s2[0], d->s2[1], d->s2[2] };
     for (int p = 0; p < nsub; ++p) {
-        if ((rc = nsdg_mevp_stress(ctx, u, v, s0, d->nyl + 1)))
-            return rc;
-        if ((rc = nsdg_mevp_velocity(ctx, dt, u, v, u2, v2, 1, d->nyl + 1)))
-            return rc;
+        if (fused) {
+            if ((rc = nsdg_mevp_fused(ctx, dt, u, v, u2, v2, sa, sb, 1, d->nyl + 1)))
+                return rc;
+            for (int q = 0; q < 3; ++q)
+                std::swap(sa[q], sb[q]);
+        } else {
+            if ((rc = nsdg_mevp_stress(ctx, u, v, s0, d->nyl + 1)))
+                return rc;
+            if ((rc = nsdg_mevp_velocity(ctx, dt, u, v, u2, v2, 1, d->nyl + 1)))
+                return rc;
+        }
         if (multi) {
             PlaneSet ps;
             ps.n = 0;
@@ -178,6 +188,11 @@ int mevp_cycle(nsdg_ctx* ctx, double dt, int nsub)
     d->f[NSDG_DF_V] = v;
     d->u2 = u2;
     d->v2 = v2;
+    d->f[NSDG_DF_S11] = sa[0];
+    d->f[NSDG_DF_S12] = sa[1];
+    d->f[NSDG_DF_S22] = sa[2];
+    for (int q = 0; q < 3; ++q)
+        d->s2[q] = sb[q];
     return NSDG_OK;
 }
 
@@ -194,6 +209,8 @@ void nsdg_dyn_free(nsdg_ctx* ctx)
         cudaFree(d->stage1[f]);
         cudaFree(d->stage2[f]);
     }
+    for (int q = 0; q < 3; ++q)
+        cudaFree(d->s2[q]);
     double* w[] = { d->pg, d->hn, d->an, d->un, d->vn, d->u2, d->v2, d->taux, d->tauy, d->scratch,
         d->send_lo, d->send_hi, d->recv_lo, d->recv_hi };
     for (double* p : w)
@@ -239,6 +256,7 @@ int nsdg_dyn_init(nsdg_ctx* ctx, const nsdg_dyn_config* cfg)
     NSDG_REQUIRE(ctx, cfg->ncomp == 1 || cfg->ncomp == 3 || cfg->ncomp == 6, NSDG_EINVAL,
         "ncomp must be 1 (dG0), 3 (dG1) or 6 (dG2), got %d", cfg->ncomp);
     NSDG_REQUIRE(ctx, cfg->rk_order >= 0 && cfg->rk_order <= 3, NSDG_EINVAL, "rk_order in 0..3");
+    NSDG_REQUIRE(ctx, (cfg->flags & ~NSDG_DYN_SPLIT_MEVP) == 0, NSDG_EINVAL, "unknown flags 0x%x", cfg->flags);
     const bool multi = nsdg_comm_active(ctx);
     NSDG_REQUIRE(ctx, multi || cfg->ny_local == cfg->ny_global, NSDG_EINVAL,
         "a strip (ny_local < ny_global) needs nsdg_comm_init before nsdg_dyn_init");
@@ -272,6 +290,10 @@ int nsdg_dyn_init(nsdg_ctx* ctx, const nsdg_dyn_config* cfg)
             return rc;
     if ((rc = alloc_planes(ctx, &d->pg, 4)))
         return rc;
+    if (!(cfg->flags & NSDG_DYN_SPLIT_MEVP))
+        for (int q = 0; q < 3; ++q)
+            if ((rc = alloc_planes(ctx, &d->s2[q], 3)))
+                return rc;
     NSDG_CUDA(ctx, cudaMalloc(&d->scratch, 64));
     if (multi) {
         d->halo_capacity = 12 * (size_t)d->nx;

@@ -26,6 +26,7 @@ struct DynState {
     double* an = nullptr; // nodal concentration
     double* un = nullptr; // velocity at the start of the momentum step
     double* vn = nullptr;
+    double* s2[3] = {}; // ping-pong partners of S11, S12, S22 (fused sub-iteration)
     double* u2 = nullptr; // ping-pong partner of U,V
     double* v2 = nullptr;
     double* taux = nullptr; // C_a rho_a |u_a| u_a
@@ -57,6 +58,9 @@ int nsdg_mevp_prepare(nsdg_ctx* ctx); // pg, hn, an, tau, un/vn from the current
 int nsdg_mevp_stress(nsdg_ctx* ctx, const double* u, const double* v, int64_t r0, int64_t r1);
 int nsdg_mevp_velocity(nsdg_ctx* ctx, double dt, const double* u, const double* v, double* unew,
     double* vnew, int64_t r0, int64_t r1);
+
+int nsdg_mevp_fused(nsdg_ctx* ctx, double dt, const double* u, const double* v, double* unew,
+    double* vnew, double* const* Sold, double* const* Snew, int64_t r0, int64_t r1);
 
 // comm.cu -----------------------------------------------------------------------------------
 // fill ghost rows of the given planes: row nyl -> upper neighbour's row 0, row 1 -> lower

@@ -194,13 +194,13 @@ class GpuDynamics:
     """DG transport (dG0/1/2) + mEVP on one strip of a structured periodic grid."""
 
     def __init__(self, ctx, nx, ny_global, hx, hy, ncomp=6, ny_local=None, j0=0, rk_order=0,
-                 limiter=0, mevp=None):
+                 limiter=0, mevp=None, flags=0):
         self.ctx, self.lib, self.h = ctx, ctx.lib, ctx.h
         self.nx, self.ny_global = int(nx), int(ny_global)
         self.ny = int(ny_local if ny_local is not None else ny_global)
         self.ncomp = int(ncomp)
         self.cfg = DynConfig(self.nx, self.ny_global, self.ny, int(j0), float(hx), float(hy),
-                             self.ncomp, int(rk_order), int(limiter), 0)
+                             self.ncomp, int(rk_order), int(limiter), int(flags))
         check(self.h, self.lib.nsdg_dyn_init(self.h, ctypes.byref(self.cfg)))
         self.set_mevp_params(mevp if mevp is not None else MevpParams.defaults())
 

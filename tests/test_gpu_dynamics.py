@@ -6,7 +6,7 @@ import numpy as np
 import pytest
 
 from nextsimdg_b200 import synthetic as S
-from nextsimdg_b200._abi import BC_BOX, BC_PERIODIC, MevpParams, NsdgError
+from nextsimdg_b200._abi import BC_BOX, BC_PERIODIC, DYN_SPLIT_MEVP, MevpParams, NsdgError
 from nextsimdg_b200.gpu import GpuDynamics
 from oracle import cpu_oracle as O
 
@@ -109,9 +109,10 @@ def test_cone_rotation_dg1_quarter_turn(ctx):
     assert abs(dyn.mass("H") - m0) / m0 < 1e-13
 
 
+@pytest.mark.parametrize("flags", [0, DYN_SPLIT_MEVP], ids=["fused", "split"])
 @pytest.mark.parametrize("bc", [BC_PERIODIC, BC_BOX])
-@pytest.mark.parametrize("shape", [(64, 48), (33, 21)])
-def test_mevp_matches_oracle(ctx, bc, shape):
+@pytest.mark.parametrize("shape", [(64, 48), (33, 21), (130, 19), (64, 8), (65, 9)])
+def test_mevp_matches_oracle(ctx, bc, shape, flags):
     nx, ny = shape
     F, hx, hy = S.box_case(nx, ny, 6)
     rng = np.random.default_rng(5)
@@ -124,7 +125,7 @@ def test_mevp_matches_oracle(ctx, bc, shape):
     mp = MevpParams.defaults()
     mp.bc = bc
     mp.alpha = mp.beta = 300.0
-    dyn = GpuDynamics(ctx, nx, ny, hx, hy, 6, mevp=mp)
+    dyn = GpuDynamics(ctx, nx, ny, hx, hy, 6, mevp=mp, flags=flags)
     dyn.upload_all(F)
     for nsub in (1, 7):  # odd counts exercise the ping-pong pointer swap
         dyn.mevp_step(120.0, nsub)
