@@ -34,7 +34,8 @@ BYTES_VELOCITY = (9 + 2 + 2 + 2 + 2 + 2 + 2) * 8  # r S(9) u,v un,vn tau uo,vo H
 BYTES_FUSED = (9 + 2 + 4 + 2 + 2 + 2 + 2 + 9 + 2) * 8  # one fused sub-iteration kernel
 BYTES_TRANSPORT_STEP = (2 * 8 * NCOMP + 6) * 8  # H and A, SSP-RK3, shared velocity reads
 BYTES_PREPARE = (12 + 4 + 2 + 2 + 2 + 2 + 2 + 2) * 8  # P_g, nodal H/A, wind stress, u^n copy
-BYTES_STEP = BYTES_TRANSPORT_STEP + BYTES_PREPARE + NSUB * (BYTES_STRESS + BYTES_VELOCITY)
+BYTES_STEP_SPLIT = BYTES_TRANSPORT_STEP + BYTES_PREPARE + NSUB * (BYTES_STRESS + BYTES_VELOCITY)
+BYTES_STEP_FUSED = BYTES_TRANSPORT_STEP + BYTES_PREPARE + NSUB * BYTES_FUSED
 
 
 def peaks():
@@ -275,6 +276,7 @@ def run_gpu(args):
         kbytes = per_kernel_bytes.get(kname, 0) * cells_local
         kavg_ms = ktot / kcnt
         achieved = kbytes / (kavg_ms * 1e-3) / 1e9
+        BYTES_STEP = BYTES_STEP_FUSED if "mevp_fused_kernel" in prof else BYTES_STEP_SPLIT
         step_gbs = BYTES_STEP * cells_local * args.steps / (ms * 1e-3) / 1e9
         roof = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak,
                 "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,

@@ -343,8 +343,8 @@ __global__ void __launch_bounds__(FusedCfg<TX, TY>::NT, FusedCfg<TX, TY>::MINB) 
                 const double g12 = e12_0 + e12_1 * xa + e12_2 * yb;
                 const double pp = pr[2 * b + a];
                 const double tr = g11 + g22, df = g11 - g22;
-                const double delta = sqrt(dmin2 + tr * tr + ie2 * (df * df + 4. * g12 * g12));
-                const double zeta = pp / (2. * delta);
+                // zeta = P/(2 Delta) with one reciprocal square root instead of sqrt + divide
+                const double zeta = 0.5 * pp * rsqrt(dmin2 + tr * tr + ie2 * (df * df + 4. * g12 * g12));
                 const double eta = zeta * ie2;
                 const double s11 = 2. * eta * g11 + (zeta - eta) * tr - 0.5 * pp;
                 const double s22 = 2. * eta * g22 + (zeta - eta) * tr - 0.5 * pp;
@@ -394,21 +394,19 @@ __global__ void __launch_bounds__(FusedCfg<TX, TY>::NT, FusedCfg<TX, TY>::MINB) 
             return;
         }
     }
-    double dx = 0., dy = 0.;
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-        const double sa = (q & 1) ? -1. : 1.;
-        const double sb = (q & 2) ? -1. : 1.;
-        // local cell (tx-1 + (q&1), ty-1 + (q>>1)) -> shared index +1
-        const int t = (ty + (q >> 1)) * CXS + tx + (q & 1);
-        const double ix11 = sa * A.hy * (0.5 * ss[0][t] + sb * ss[1][t] / 12.);
-        const double iy12 = sb * A.hx * (0.5 * ss[2][t] + sa * ss[3][t] / 12.);
-        const double ix12 = sa * A.hy * (0.5 * ss[2][t] + sb * ss[4][t] / 12.);
-        const double iy22 = sb * A.hx * (0.5 * ss[5][t] + sa * ss[6][t] / 12.);
-        dx -= ix11 + iy12;
-        dy -= ix12 + iy22;
-    }
-    const double iarea = 1. / (A.hx * A.hy);
+    // -(S, grad phi_n)/(hx hy) from the 4 adjacent cells; with sa = +,-,+,- and sb = +,+,-,- for
+    // the cells (tx-1,ty-1), (tx,ty-1), (tx-1,ty), (tx,ty) the analytic integrals collapse to
+    // signed sums of shared-memory values times four constants
+    const int t00 = ty * CXS + tx, t10 = t00 + 1, t01 = t00 + CXS, t11 = t01 + 1;
+    const double c1 = 0.5 * ihx, c2 = ihx * (1. / 12.), c3 = 0.5 * ihy, c4 = ihy * (1. / 12.);
+#define SUM_A(c) (ss[c][t00] - ss[c][t10] + ss[c][t01] - ss[c][t11]) /* sum sa X */
+#define SUM_B(c) (ss[c][t00] + ss[c][t10] - ss[c][t01] - ss[c][t11]) /* sum sb X */
+#define SUM_AB(c) (ss[c][t00] - ss[c][t10] - ss[c][t01] + ss[c][t11]) /* sum sa sb X */
+    const double dxa = -(c1 * SUM_A(0) + c2 * SUM_AB(1) + c3 * SUM_B(2) + c4 * SUM_AB(3));
+    const double dya = -(c1 * SUM_A(2) + c2 * SUM_AB(4) + c3 * SUM_B(5) + c4 * SUM_AB(6));
+#undef SUM_A
+#undef SUM_B
+#undef SUM_AB
     const double u = __ldg(A.u + n), v = __ldg(A.v + n);
     const double uo = __ldg(A.uo + n), vo = __ldg(A.vo + n);
     const double m = A.P.rho_ice * fmax(__ldg(A.hn + n), A.P.h_min);
@@ -418,11 +416,12 @@ __global__ void __launch_bounds__(FusedCfg<TX, TY>::NT, FusedCfg<TX, TY>::MINB) 
     const double mdt = m / A.dt;
     const double denom = mdt * (1. + A.P.beta) + cd;
     const double rx = mdt * (A.P.beta * u + __ldg(A.un + n)) + a * __ldg(A.taux + n) + cd * uo
-        + m * A.P.f_coriolis * (v - vo) + dx * iarea;
+        + m * A.P.f_coriolis * (v - vo) + dxa;
     const double ry = mdt * (A.P.beta * v + __ldg(A.vn + n)) + a * __ldg(A.tauy + n) + cd * vo
-        - m * A.P.f_coriolis * (u - uo) + dy * iarea;
-    A.out0[n] = rx / denom;
-    A.out1[n] = ry / denom;
+        - m * A.P.f_coriolis * (u - uo) + dya;
+    const double inv = 1. / denom;
+    A.out0[n] = rx * inv;
+    A.out1[n] = ry * inv;
 }
 
 MevpArgs base_args(DynState* d)
