@@ -135,8 +135,11 @@ int mevp_cycle(nsdg_ctx* ctx, double dt, int nsub)
 {
     DynState* d = ctx->dyn;
     const bool multi = nsdg_comm_active(ctx);
+    // ghost-row mode: strips, or a single rank running the bulk-copy fused kernel (the ring
+    // exchange is then a local row copy, see comm.cu)
+    const bool ghost = multi || d->ghost_single;
     int rc;
-    if (multi) {
+    if (ghost) {
         // lower ghost rows of H, A (strength and nodal means), both ghost rows of u, v, lower
         // ghost row of S (it then evolves redundantly, bit-identical to the owner's copy)
         PlaneSet ps = planes_of(d, d->f[NSDG_DF_H], d->nc);
@@ -154,7 +157,7 @@ int mevp_cycle(nsdg_ctx* ctx, double dt, int nsub)
         if ((rc = nsdg_halo_exchange(ctx, ps, 3)))
             return rc;
     }
-    if ((rc = nsdg_mevp_prepare(ctx)))
+    if ((rc = nsdg_mevp_prepare(ctx, ghost)))
         return rc;
     double *u = d->f[NSDG_DF_U], *v = d->f[NSDG_DF_V], *u2 = d->u2, *v2 = d->v2;
     const int64_t s0 = multi ? 0 : 1;
@@ -163,7 +166,7 @@ int mevp_cycle(nsdg_ctx* ctx, double dt, int nsub)
     double* sb[3] = { d->s2[0], d->s2[1], d->s2[2] };
     for (int p = 0; p < nsub; ++p) {
         if (fused) {
-            if ((rc = nsdg_mevp_fused(ctx, dt, u, v, u2, v2, sa, sb, 1, d->nyl + 1)))
+            if ((rc = nsdg_mevp_fused(ctx, dt, u, v, u2, v2, sa, sb, 1, d->nyl + 1, ghost)))
                 return rc;
             for (int q = 0; q < 3; ++q)
                 std::swap(sa[q], sb[q]);
@@ -272,6 +275,7 @@ int nsdg_dyn_init(nsdg_ctx* ctx, const nsdg_dyn_config* cfg)
     d->nc = cfg->ncomp;
     d->rk = cfg->rk_order ? cfg->rk_order : (d->nc == 1 ? 1 : (d->nc == 3 ? 2 : 3));
     d->wrap = !multi;
+    d->ghost_single = !multi && !(cfg->flags & NSDG_DYN_SPLIT_MEVP) && nsdg_mevp_tma_eligible(d->nx);
     int rc;
     for (int q = 0; q < NSDG_DF_COUNT; ++q) {
         d->ncomp[q] = field_ncomp(d, q);

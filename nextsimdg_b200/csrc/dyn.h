@@ -15,6 +15,10 @@ struct DynState {
     int nc = 0; // tracer components
     int rk = 0; // RK order actually used
     bool wrap = true; // single rank: periodic wrap in y inside the kernels
+    // single rank, bulk-copy fused mEVP kernel: the sub-cycle runs in ghost-row mode (as a strip
+    // would) with the ring exchange replaced by local row copies, so that every tile footprint
+    // is a plain box of the plane (no wrap in y)
+    bool ghost_single = false;
     double* f[NSDG_DF_COUNT] = {};
     int ncomp[NSDG_DF_COUNT] = {};
     // RK stage buffers for H and A
@@ -54,13 +58,16 @@ int nsdg_transport_stage(nsdg_ctx* ctx, int nfields, double* const* src, double*
 int nsdg_transport_limit(nsdg_ctx* ctx, double* phi, double lo, double hi);
 
 // mevp.cu -----------------------------------------------------------------------------------
-int nsdg_mevp_prepare(nsdg_ctx* ctx); // pg, hn, an, tau, un/vn from the current H, A, U, V
+// pg, hn, an, tau, un/vn from the current H, A, U, V; ghost: ghost rows are current (no wrap)
+int nsdg_mevp_prepare(nsdg_ctx* ctx, bool ghost);
+// the bulk-copy (TMA) fused kernel handles this row length
+bool nsdg_mevp_tma_eligible(int64_t nx);
 int nsdg_mevp_stress(nsdg_ctx* ctx, const double* u, const double* v, int64_t r0, int64_t r1);
 int nsdg_mevp_velocity(nsdg_ctx* ctx, double dt, const double* u, const double* v, double* unew,
     double* vnew, int64_t r0, int64_t r1);
 
 int nsdg_mevp_fused(nsdg_ctx* ctx, double dt, const double* u, const double* v, double* unew,
-    double* vnew, double* const* Sold, double* const* Snew, int64_t r0, int64_t r1);
+    double* vnew, double* const* Sold, double* const* Snew, int64_t r0, int64_t r1, bool ghost);
 
 // comm.cu -----------------------------------------------------------------------------------
 // fill ghost rows of the given planes: row nyl -> upper neighbour's row 0, row 1 -> lower
