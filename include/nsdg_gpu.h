@@ -154,6 +154,8 @@ typedef struct nsdg_dyn_config {
 
 /* use the two-kernel (stress, velocity) sub-iteration instead of the fused kernel */
 #define NSDG_DYN_SPLIT_MEVP 1
+/* one sub-iteration per launch: do not use the pair-fused (two sub-iterations per launch) kernel */
+#define NSDG_DYN_SINGLE_MEVP 2
 
 /* ---- context ---- */
 int nsdg_abi_version(void);

@@ -61,6 +61,7 @@ class DynConfig(ctypes.Structure):
 
 
 DYN_SPLIT_MEVP = 1
+DYN_SINGLE_MEVP = 2
 
 
 # every symbol include/nsdg_gpu.h declares: name -> (restype, argtypes)

@@ -76,23 +76,6 @@ __global__ void unpack_rows(const __grid_constant__ PackArgs A)
     }
 }
 
-// single rank in ghost-row mode: the ring neighbour is the rank itself
-// blockIdx.y = plane, blockIdx.z = 0 (row nyl -> row 0) / 1 (row 1 -> row nyl+1)
-__global__ void self_halo_rows(const __grid_constant__ PackArgs A, int64_t nyl, int which)
-{
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= A.nx)
-        return;
-    double* p = A.plane[blockIdx.y];
-    if (blockIdx.z == 0) {
-        if (which & 1)
-            p[i] = p[nyl * A.nx + i];
-    } else {
-        if (which & 2)
-            p[(nyl + 1) * A.nx + i] = p[A.nx + i];
-    }
-}
-
 } // namespace
 
 #define NSDG_NCCL(ctx, c, expr)                                                                   \
@@ -118,21 +101,9 @@ void nsdg_comm_free(nsdg_ctx* ctx)
 
 int nsdg_halo_exchange(nsdg_ctx* ctx, const PlaneSet& planes, int which)
 {
-    if (planes.n == 0)
+    if (!nsdg_comm_active(ctx) || planes.n == 0)
         return NSDG_OK;
     DynState* d = ctx->dyn;
-    if (!nsdg_comm_active(ctx)) {
-        if (!d->ghost_single)
-            return NSDG_OK;
-        PackArgs A = {};
-        for (int q = 0; q < planes.n; ++q)
-            A.plane[q] = planes.p[q];
-        A.n = planes.n;
-        A.nx = d->nx;
-        dim3 block(256), grid((unsigned)((d->nx + 255) / 256), (unsigned)planes.n, 2);
-        NSDG_KERNEL(ctx, NSDG_K_PACK, self_halo_rows<<<grid, block, 0, ctx->stream>>>(A, d->nyl, which));
-        return NSDG_OK;
-    }
     CommState* c = ctx->comm;
     NSDG_REQUIRE(ctx, (size_t)planes.n * d->nx <= d->halo_capacity, NSDG_EINVAL, "too many planes in one halo exchange");
     const int up = (c->rank + 1) % c->nranks, down = (c->rank + c->nranks - 1) % c->nranks;

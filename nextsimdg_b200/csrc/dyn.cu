@@ -2,6 +2,7 @@
 // halo exchanges of the strip decomposition).  See include/nsdg_gpu.h and dyn.h.
 #include "dyn.h"
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 namespace {
@@ -135,11 +136,8 @@ int mevp_cycle(nsdg_ctx* ctx, double dt, int nsub)
 {
     DynState* d = ctx->dyn;
     const bool multi = nsdg_comm_active(ctx);
-    // ghost-row mode: strips, or a single rank running the bulk-copy fused kernel (the ring
-    // exchange is then a local row copy, see comm.cu)
-    const bool ghost = multi || d->ghost_single;
     int rc;
-    if (ghost) {
+    if (multi) {
         // lower ghost rows of H, A (strength and nodal means), both ghost rows of u, v, lower
         // ghost row of S (it then evolves redundantly, bit-identical to the owner's copy)
         PlaneSet ps = planes_of(d, d->f[NSDG_DF_H], d->nc);
@@ -157,23 +155,36 @@ int mevp_cycle(nsdg_ctx* ctx, double dt, int nsub)
         if ((rc = nsdg_halo_exchange(ctx, ps, 3)))
             return rc;
     }
-    if ((rc = nsdg_mevp_prepare(ctx, ghost)))
+    if ((rc = nsdg_mevp_prepare(ctx, dt)))
         return rc;
     double *u = d->f[NSDG_DF_U], *v = d->f[NSDG_DF_V], *u2 = d->u2, *v2 = d->v2;
     const int64_t s0 = multi ? 0 : 1;
     const bool fused = !(d->cfg.flags & NSDG_DYN_SPLIT_MEVP);
+    static int pair_env = -1; // NSDG_MEVP_PAIR=0/1 overrides the default (tuning / A-B tests)
+    if (pair_env < 0) {
+        const char* e = getenv("NSDG_MEVP_PAIR");
+        pair_env = e ? (atoi(e) != 0) : 1;
+    }
+    // single rank: two sub-iterations per launch while at least two remain
+    const bool pair = pair_env && fused && !multi && !(d->cfg.flags & NSDG_DYN_SINGLE_MEVP);
     double* sa[3] = { d->f[NSDG_DF_S11], d->f[NSDG_DF_S12], d->f[NSDG_DF_S22] };
     double* sb[3] = { d->s2[0], d->s2[1], d->s2[2] };
     for (int p = 0; p < nsub; ++p) {
-        if (fused) {
-            if ((rc = nsdg_mevp_fused(ctx, dt, u, v, u2, v2, sa, sb, 1, d->nyl + 1, ghost)))
+        if (pair && p + 1 < nsub) {
+            if ((rc = nsdg_mevp_pair(ctx, dt, u, v, u2, v2, sa, sb)))
+                return rc;
+            for (int q = 0; q < 3; ++q)
+                std::swap(sa[q], sb[q]);
+            ++p;
+        } else if (fused) {
+            if ((rc = nsdg_mevp_fused(ctx, dt, u, v, u2, v2, sa, sb, 1, d->nyl + 1)))
                 return rc;
             for (int q = 0; q < 3; ++q)
                 std::swap(sa[q], sb[q]);
         } else {
-            if ((rc = nsdg_mevp_stress(ctx, u, v, s0, d->nyl + 1)))
+            if ((rc = nsdg_mevp_stress(ctx, dt, u, v, sa, s0, d->nyl + 1)))
                 return rc;
-            if ((rc = nsdg_mevp_velocity(ctx, dt, u, v, u2, v2, 1, d->nyl + 1)))
+            if ((rc = nsdg_mevp_velocity(ctx, dt, u, v, u2, v2, sa, 1, d->nyl + 1)))
                 return rc;
         }
         if (multi) {
@@ -214,7 +225,7 @@ void nsdg_dyn_free(nsdg_ctx* ctx)
     }
     for (int q = 0; q < 3; ++q)
         cudaFree(d->s2[q]);
-    double* w[] = { d->pg, d->hn, d->an, d->un, d->vn, d->u2, d->v2, d->taux, d->tauy, d->scratch,
+    double* w[] = { d->pg, d->nd, d->u2, d->v2, d->scratch,
         d->send_lo, d->send_hi, d->recv_lo, d->recv_hi };
     for (double* p : w)
         cudaFree(p);
@@ -259,7 +270,12 @@ int nsdg_dyn_init(nsdg_ctx* ctx, const nsdg_dyn_config* cfg)
     NSDG_REQUIRE(ctx, cfg->ncomp == 1 || cfg->ncomp == 3 || cfg->ncomp == 6, NSDG_EINVAL,
         "ncomp must be 1 (dG0), 3 (dG1) or 6 (dG2), got %d", cfg->ncomp);
     NSDG_REQUIRE(ctx, cfg->rk_order >= 0 && cfg->rk_order <= 3, NSDG_EINVAL, "rk_order in 0..3");
-    NSDG_REQUIRE(ctx, (cfg->flags & ~NSDG_DYN_SPLIT_MEVP) == 0, NSDG_EINVAL, "unknown flags 0x%x", cfg->flags);
+    NSDG_REQUIRE(ctx, (cfg->flags & ~(NSDG_DYN_SPLIT_MEVP | NSDG_DYN_SINGLE_MEVP)) == 0, NSDG_EINVAL,
+        "unknown flags 0x%x", cfg->flags);
+    // the kernels index every array with 32-bit integers
+    NSDG_REQUIRE(ctx, (cfg->ny_local + 2) * cfg->nx * (cfg->ncomp > 4 ? cfg->ncomp : 4) < (int64_t)1 << 31,
+        NSDG_EINVAL, "strip too large for 32-bit indexing: %lld x %lld cells, %d components",
+        (long long)cfg->nx, (long long)cfg->ny_local, cfg->ncomp);
     const bool multi = nsdg_comm_active(ctx);
     NSDG_REQUIRE(ctx, multi || cfg->ny_local == cfg->ny_global, NSDG_EINVAL,
         "a strip (ny_local < ny_global) needs nsdg_comm_init before nsdg_dyn_init");
@@ -275,7 +291,6 @@ int nsdg_dyn_init(nsdg_ctx* ctx, const nsdg_dyn_config* cfg)
     d->nc = cfg->ncomp;
     d->rk = cfg->rk_order ? cfg->rk_order : (d->nc == 1 ? 1 : (d->nc == 3 ? 2 : 3));
     d->wrap = !multi;
-    d->ghost_single = !multi && !(cfg->flags & NSDG_DYN_SPLIT_MEVP) && nsdg_mevp_tma_eligible(d->nx);
     int rc;
     for (int q = 0; q < NSDG_DF_COUNT; ++q) {
         d->ncomp[q] = field_ncomp(d, q);
@@ -288,11 +303,11 @@ int nsdg_dyn_init(nsdg_ctx* ctx, const nsdg_dyn_config* cfg)
         if (d->rk == 3 && (rc = alloc_planes(ctx, &d->stage2[f], d->nc)))
             return rc;
     }
-    double** one[] = { &d->hn, &d->an, &d->un, &d->vn, &d->u2, &d->v2, &d->taux, &d->tauy };
+    double** one[] = { &d->u2, &d->v2 };
     for (double** p : one)
         if ((rc = alloc_planes(ctx, p, 1)))
             return rc;
-    if ((rc = alloc_planes(ctx, &d->pg, 4)))
+    if ((rc = alloc_planes(ctx, &d->pg, 4)) || (rc = alloc_planes(ctx, &d->nd, 4)))
         return rc;
     if (!(cfg->flags & NSDG_DYN_SPLIT_MEVP))
         for (int q = 0; q < 3; ++q)

@@ -15,10 +15,6 @@ struct DynState {
     int nc = 0; // tracer components
     int rk = 0; // RK order actually used
     bool wrap = true; // single rank: periodic wrap in y inside the kernels
-    // single rank, bulk-copy fused mEVP kernel: the sub-cycle runs in ghost-row mode (as a strip
-    // would) with the ring exchange replaced by local row copies, so that every tile footprint
-    // is a plain box of the plane (no wrap in y)
-    bool ghost_single = false;
     double* f[NSDG_DF_COUNT] = {};
     int ncomp[NSDG_DF_COUNT] = {};
     // RK stage buffers for H and A
@@ -26,15 +22,10 @@ struct DynState {
     double* stage2[2] = {};
     // per-step mEVP work arrays
     double* pg = nullptr; // ice strength at the 2x2 Gauss points, 4 planes
-    double* hn = nullptr; // nodal thickness
-    double* an = nullptr; // nodal concentration
-    double* un = nullptr; // velocity at the start of the momentum step
-    double* vn = nullptr;
+    double* nd = nullptr; // per-node constants of the sub-cycle, 4 planes: cx0, cy0, mdt, acd
     double* s2[3] = {}; // ping-pong partners of S11, S12, S22 (fused sub-iteration)
     double* u2 = nullptr; // ping-pong partner of U,V
     double* v2 = nullptr;
-    double* taux = nullptr; // C_a rho_a |u_a| u_a
-    double* tauy = nullptr;
     double* scratch = nullptr; // reductions
     double* host_stage = nullptr; // pinned staging for upload/download
     size_t host_stage_bytes = 0;
@@ -58,16 +49,19 @@ int nsdg_transport_stage(nsdg_ctx* ctx, int nfields, double* const* src, double*
 int nsdg_transport_limit(nsdg_ctx* ctx, double* phi, double lo, double hi);
 
 // mevp.cu -----------------------------------------------------------------------------------
-// pg, hn, an, tau, un/vn from the current H, A, U, V; ghost: ghost rows are current (no wrap)
-int nsdg_mevp_prepare(nsdg_ctx* ctx, bool ghost);
-// the bulk-copy (TMA) fused kernel handles this row length
-bool nsdg_mevp_tma_eligible(int64_t nx);
-int nsdg_mevp_stress(nsdg_ctx* ctx, const double* u, const double* v, int64_t r0, int64_t r1);
+// pg and the per-node constants from the current H, A, U, V for a momentum step of length dt
+int nsdg_mevp_prepare(nsdg_ctx* ctx, double dt);
+// split variant: stress in place on cell rows [r0,r1), then velocity on node rows [r0,r1)
+int nsdg_mevp_stress(nsdg_ctx* ctx, double dt, const double* u, const double* v, double* const* S,
+    int64_t r0, int64_t r1);
 int nsdg_mevp_velocity(nsdg_ctx* ctx, double dt, const double* u, const double* v, double* unew,
-    double* vnew, int64_t r0, int64_t r1);
-
+    double* vnew, double* const* S, int64_t r0, int64_t r1);
+// one fused sub-iteration: (u,v,Sold) -> (unew,vnew,Snew) on node rows [r0,r1)
 int nsdg_mevp_fused(nsdg_ctx* ctx, double dt, const double* u, const double* v, double* unew,
-    double* vnew, double* const* Sold, double* const* Snew, int64_t r0, int64_t r1, bool ghost);
+    double* vnew, double* const* Sold, double* const* Snew, int64_t r0, int64_t r1);
+// two sub-iterations in one launch (temporal blocking), single rank in wrap mode only
+int nsdg_mevp_pair(nsdg_ctx* ctx, double dt, const double* u, const double* v, double* unew,
+    double* vnew, double* const* Sold, double* const* Snew);
 
 // comm.cu -----------------------------------------------------------------------------------
 // fill ghost rows of the given planes: row nyl -> upper neighbour's row 0, row 1 -> lower

@@ -6,7 +6,8 @@ import numpy as np
 import pytest
 
 from nextsimdg_b200 import synthetic as S
-from nextsimdg_b200._abi import BC_BOX, BC_PERIODIC, DYN_SPLIT_MEVP, MevpParams, NsdgError
+from nextsimdg_b200._abi import (BC_BOX, BC_PERIODIC, DYN_SINGLE_MEVP, DYN_SPLIT_MEVP, MevpParams,
+                                   NsdgError)
 from nextsimdg_b200.gpu import GpuDynamics
 from oracle import cpu_oracle as O
 
@@ -109,7 +110,7 @@ def test_cone_rotation_dg1_quarter_turn(ctx):
     assert abs(dyn.mass("H") - m0) / m0 < 1e-13
 
 
-@pytest.mark.parametrize("flags", [0, DYN_SPLIT_MEVP], ids=["fused", "split"])
+@pytest.mark.parametrize("flags", [0, DYN_SINGLE_MEVP, DYN_SPLIT_MEVP], ids=["pair", "fused", "split"])
 @pytest.mark.parametrize("bc", [BC_PERIODIC, BC_BOX])
 @pytest.mark.parametrize("shape", [(64, 48), (33, 21), (130, 19), (64, 8), (65, 9), (128, 21), (96, 16), (2400 // 25 * 3 + 32, 11)])
 def test_mevp_matches_oracle(ctx, bc, shape, flags):
@@ -137,30 +138,6 @@ def test_mevp_matches_oracle(ctx, bc, shape, flags):
     if bc == BC_BOX:
         u = dyn.download("U")
         assert np.all(u[0] == 0) and np.all(u[:, 0] == 0)
-
-
-@pytest.mark.parametrize("shape", [(128, 21), (96, 16), (320, 11)])
-def test_mevp_bulk_copy_kernel_matches_oracle(ctx, shape, monkeypatch):
-    """The opt-in TMA (tensor-box / bulk-copy, mbarrier-pipelined) fused kernel: single rank in
-    ghost-row mode with local ring copies."""
-    monkeypatch.setenv("NSDG_FUSED_TMA", "1")
-    nx, ny = shape
-    F, hx, hy = S.box_case(nx, ny, 6)
-    rng = np.random.default_rng(6)
-    F["U"] = 0.05 * rng.standard_normal((ny, nx))
-    F["V"] = 0.05 * rng.standard_normal((ny, nx))
-    for k in ("S11", "S12", "S22"):
-        F[k] = 100 * rng.standard_normal((3, ny, nx))
-    mp = MevpParams.defaults()
-    mp.bc = BC_PERIODIC
-    mp.alpha = mp.beta = 300.0
-    dyn = GpuDynamics(ctx, nx, ny, hx, hy, 6, mevp=mp)
-    dyn.upload_all(F)
-    dyn.mevp_step(120.0, 5)
-    ref = O.mevp_step(mp, F["H"], F["A"], F["U"], F["V"], F["S11"], F["S12"], F["S22"],
-                      F["UATM"], F["VATM"], F["UOCN"], F["VOCN"], hx, hy, 120.0, 5)
-    for name, r in zip(("U", "V", "S11", "S12", "S22"), ref):
-        assert maxrel(dyn.download(name), r) < RTOL, name
 
 
 def test_north_star_step_box_100_substeps(ctx):

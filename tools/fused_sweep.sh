@@ -1,8 +1,11 @@
 #!/bin/bash
-# scratch: fused-kernel sweep at 4096^2 (per-launch average from the event profiler)
+# scratch: mEVP kernel sweep at 4096^2 (per-launch average from the event profiler)
 run() { echo -n "$* : "; env "$@" python bench.py --steps 2 --warmup 1 --no-cpu --e2e-steps 1 | python -c "
 import json,sys; d=json.loads(sys.stdin.read()); r=d['roofline']; print(round(d['ms_per_step'],2), r['kernel'], round(r['avg_launch_ms'],4), round(r['frac'],3))"; }
-run NSDG_FUSED_TMA=0
-run NSDG_FUSED_TMA=1
-run NSDG_FUSED_TMA=1 NSDG_FUSED_CTAS=1
-run NSDG_FUSED_TMA=1 NSDG_FUSED_CTAS=4
+run NSDG_MEVP_PAIR=0
+run NSDG_MEVP_PAIR=0 NSDG_FUSED_TILE=64x4
+run NSDG_MEVP_PAIR=0 NSDG_FUSED_TILE=32x16
+run NSDG_MEVP_PAIR=1 NSDG_PAIR_TILE=16x16
+run NSDG_MEVP_PAIR=1 NSDG_PAIR_TILE=32x8
+run NSDG_MEVP_PAIR=1 NSDG_PAIR_TILE=32x12
+run NSDG_MEVP_PAIR=1 NSDG_PAIR_TILE=32x16
