@@ -28,12 +28,16 @@ sys.path.insert(0, ROOT)
 NSUB = 100
 DT = 120.0
 NCOMP = 6
-# algorithmic bytes per cell (DESIGN.md "Roofline accounting"; counting rule of SURVEY.md 8d)
+# algorithmic bytes per cell (counting rule of SURVEY.md 8d: every distinct
+# array element one cell-update must read or write counts once, neighbour re-reads are free)
 BYTES_STRESS = (9 + 2 + 4 + 9) * 8  # r S(9) u,v(2) P_g(4)  w S(9)
-BYTES_VELOCITY = (9 + 2 + 2 + 2 + 2 + 2 + 2) * 8  # r S(9) u,v un,vn tau uo,vo Hn,An  w u,v
-BYTES_FUSED = (9 + 2 + 4 + 2 + 2 + 2 + 2 + 9 + 2) * 8  # one fused sub-iteration kernel
+BYTES_VELOCITY = (7 + 2 + 2 + 4 + 2) * 8  # r S(7 of 9) u,v u_o,v_o node constants(4)  w u,v
+BYTES_FUSED = (9 + 2 + 4 + 2 + 4 + 9 + 2) * 8  # one fused sub-iteration: 32 doubles
 BYTES_TRANSPORT_STEP = (2 * 8 * NCOMP + 6) * 8  # H and A, SSP-RK3, shared velocity reads
-BYTES_PREPARE = (12 + 4 + 2 + 2 + 2 + 2 + 2 + 2) * 8  # P_g, nodal H/A, wind stress, u^n copy
+BYTES_PREPARE = (12 + 4 + 8 + 4) * 8  # P_g from H,A; node constants from H0,A0,u_a,u,u_o
+# the pair kernel runs TWO sub-iterations per launch: its units per launch are 2 x cells, its
+# compulsory DRAM bytes per launch (temporal blocking) are those of ONE fused sub-iteration
+SUBITS_PER_LAUNCH = {"mevp_pair_kernel": 2}
 BYTES_STEP_SPLIT = BYTES_TRANSPORT_STEP + BYTES_PREPARE + NSUB * (BYTES_STRESS + BYTES_VELOCITY)
 BYTES_STEP_FUSED = BYTES_TRANSPORT_STEP + BYTES_PREPARE + NSUB * BYTES_FUSED
 
@@ -270,23 +274,37 @@ def run_gpu(args):
         # dominant kernel of the step by measured share
         dom = max(prof.items(), key=lambda kv: kv[1][0])
         per_kernel_bytes = {"stress_kernel": BYTES_STRESS, "velocity_kernel": BYTES_VELOCITY,
-                            "mevp_fused_kernel": BYTES_FUSED,
+                            "mevp_fused_kernel": BYTES_FUSED, "mevp_pair_kernel": BYTES_FUSED,
                             "transport_stage_kernel": BYTES_TRANSPORT_STEP / 3.0}
         kname, (ktot, kcnt) = dom
-        kbytes = per_kernel_bytes.get(kname, 0) * cells_local
+        units = SUBITS_PER_LAUNCH.get(kname, 1)
+        kbytes = per_kernel_bytes.get(kname, 0) * units * cells_local
         kavg_ms = ktot / kcnt
         achieved = kbytes / (kavg_ms * 1e-3) / 1e9
-        BYTES_STEP = BYTES_STEP_FUSED if "mevp_fused_kernel" in prof else BYTES_STEP_SPLIT
+        split = "stress_kernel" in prof
+        BYTES_STEP = BYTES_STEP_SPLIT if split else BYTES_STEP_FUSED
         step_gbs = BYTES_STEP * cells_local * args.steps / (ms * 1e-3) / 1e9
         roof = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak,
                 "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
                 "traffic": args.traffic,
-                "algorithmic_bytes_per_launch": kbytes, "avg_launch_ms": kavg_ms,
+                "algorithmic_bytes_per_launch": kbytes,
+                "units_per_launch": f"{units} sub-iteration(s) x {cells_local} cells x "
+                                    f"{per_kernel_bytes.get(kname, 0)} B",
+                "avg_launch_ms": kavg_ms,
                 "launches": kcnt, "share_of_step": ktot / ms,
                 "whole_step": {"bytes_per_cell": BYTES_STEP, "achieved": step_gbs,
                                "frac": step_gbs / peak},
                 "kernels": {k: {"ms_total": v[0], "launches": v[1], "share": v[0] / ms}
                             for k, v in sorted(prof.items(), key=lambda kv: -kv[1][0])}}
+        if units > 1:
+            # temporal blocking: the launch must move only one sub-iteration's bytes; its own
+            # DRAM-bound time is therefore half of what `frac` is measured against
+            roof["temporal_blocking"] = {
+                "compulsory_dram_bytes_per_launch": kbytes // units,
+                "dram_gbs": kbytes / units / (kavg_ms * 1e-3) / 1e9,
+                "dram_frac_of_peak": kbytes / units / (kavg_ms * 1e-3) / 1e9 / peak,
+                "note": "frac > dram_frac_of_peak because two sub-iterations share one pass "
+                        "over HBM; the kernel is FP64-pipe/issue bound (profiles/)"}
         cpu = None
         if args.gpus == 1 and not args.no_cpu:
             n = args.cpu_sample

@@ -90,6 +90,21 @@ __device__ __forceinline__ double rcp_pos(double d)
     return fma(r, e, r);
 }
 
+__device__ __forceinline__ void prefetch_l1(const double* p)
+{
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+}
+// pull the six node streams of node_update towards L1 ahead of their use (no registers held)
+template <typename Args> __device__ __forceinline__ void prefetch_node(const Args& A, int n)
+{
+    prefetch_l1(A.uo + n);
+    prefetch_l1(A.vo + n);
+    prefetch_l1(A.nd + n);
+    prefetch_l1(A.nd + A.plane + n);
+    prefetch_l1(A.nd + 2 * A.plane + n);
+    prefetch_l1(A.nd + 3 * A.plane + n);
+}
+
 __device__ __forceinline__ double eval_dg(const double* f, int plane, int k, int nc, double a, double b)
 {
     double s = __ldg(f + k);
@@ -368,6 +383,11 @@ __global__ void __launch_bounds__(FusedCfg<TX, TY>::NT, FusedCfg<TX, TY>::MINB) 
     const int tid = threadIdx.x;
     const int i0 = blockIdx.x * TX;
     const int r0 = A.r0 + blockIdx.y * TY;
+    {
+        const int ni = i0 + tid % TX, nr = r0 + tid / TX;
+        if (tid < TX * TY && ni < A.nx && nr < A.r1)
+            prefetch_node(A, nr * A.nx + ni);
+    }
 
     // ---- new stress of the (TX+1) x (TY+1) cells touching this tile's nodes
     if (tid < NCELL) {
@@ -466,11 +486,10 @@ template <int TX, int TY> struct PairCfg {
     static constexpr int BX = TX + 2, BY = TY + 2; // nodes of phase B
     static constexpr int NA = AX * AY, NB = BX * BY;
     static constexpr int NT = (NA + 31) / 32 * 32;
-    static constexpr int MINB = NT <= 448 ? 2 : 1;
 };
 
-template <int TX, int TY>
-__global__ void __launch_bounds__(PairCfg<TX, TY>::NT, PairCfg<TX, TY>::MINB) mevp_pair_kernel(const __grid_constant__ MevpArgs A)
+template <int TX, int TY, int MINB>
+__global__ void __launch_bounds__(PairCfg<TX, TY>::NT, MINB) mevp_pair_kernel(const __grid_constant__ MevpArgs A)
 {
     using C = PairCfg<TX, TY>;
     constexpr int AX = C::AX, BX = C::BX, NA = C::NA, NB = C::NB;
@@ -479,6 +498,8 @@ __global__ void __launch_bounds__(PairCfg<TX, TY>::NT, PairCfg<TX, TY>::MINB) me
     const int tid = threadIdx.x;
     const int i0 = blockIdx.x * TX;
     const int r0 = A.r0 + blockIdx.y * TY; // plane row of the first owned node row
+    // (an L1 prefetch of the node streams of phases B and D, as in mevp_fused_kernel, was measured
+    // to cost 5 % at 16x16: profiles/r1p_prefetch_occupancy_sweep.txt)
 
     // ---- A: stress p+1 of cell (ax, ay) = global column i0-2+ax, interior row index r0-3+ay
     const int ax = tid % AX, ay = tid / AX;
@@ -744,26 +765,32 @@ int nsdg_mevp_pair(nsdg_ctx* ctx, double dt, const double* u, const double* v, d
     if (tile < 0) {
         const char* e = getenv("NSDG_PAIR_TILE");
         std::string t = e ? e : "16x16";
-        tile = t == "32x8" ? 1 : t == "32x16" ? 2 : t == "32x12" ? 3 : 0;
+        tile = t == "32x8" ? 1 : t == "32x16" ? 2 : t == "16x16m3" ? 3 : t == "16x8" ? 4 : t == "16x12" ? 5 : 0;
     }
-#define NSDG_PAIR_LAUNCH(TX, TY)                                                                  \
+#define NSDG_PAIR_LAUNCH(TX, TY, MINB)                                                            \
     do {                                                                                          \
         dim3 block(PairCfg<TX, TY>::NT),                                                          \
             grid((unsigned)((d->nx + TX - 1) / TX), (unsigned)((d->nyl + TY - 1) / TY));          \
-        NSDG_KERNEL(ctx, NSDG_K_MEVP_PAIR, (mevp_pair_kernel<TX, TY><<<grid, block, 0, ctx->stream>>>(A))); \
+        NSDG_KERNEL(ctx, NSDG_K_MEVP_PAIR, (mevp_pair_kernel<TX, TY, MINB><<<grid, block, 0, ctx->stream>>>(A))); \
     } while (0)
     switch (tile) {
     case 1:
-        NSDG_PAIR_LAUNCH(32, 8);
+        NSDG_PAIR_LAUNCH(32, 8, 2);
         break;
     case 2:
-        NSDG_PAIR_LAUNCH(32, 16);
+        NSDG_PAIR_LAUNCH(32, 16, 1);
         break;
     case 3:
-        NSDG_PAIR_LAUNCH(32, 12);
+        NSDG_PAIR_LAUNCH(16, 16, 3);
+        break;
+    case 4:
+        NSDG_PAIR_LAUNCH(16, 8, 4);
+        break;
+    case 5:
+        NSDG_PAIR_LAUNCH(16, 12, 3);
         break;
     default:
-        NSDG_PAIR_LAUNCH(16, 16);
+        NSDG_PAIR_LAUNCH(16, 16, 2);
     }
 #undef NSDG_PAIR_LAUNCH
     return NSDG_OK;
