@@ -214,8 +214,9 @@ int nsdg_dyn_set_mevp_params(nsdg_ctx* ctx, const nsdg_mevp_params* p);
 int nsdg_dyn_upload(nsdg_ctx* ctx, int32_t field, const double* host);
 int nsdg_dyn_download(nsdg_ctx* ctx, int32_t field, double* host);
 int nsdg_dyn_field_ncomp(const nsdg_ctx* ctx, int32_t field);
-/* device pointer of component 0, row 0 of the padded array (ny_local+2 rows, row 0 and
- * ny_local+1 are ghost rows); pitch_elems = nx, comp_stride = (ny_local+2)*nx */
+/* device pointer of component 0, row 0 of the padded array: ny_local+4 rows, of which rows
+ * 0,1 and ny_local+2, ny_local+3 are ghost rows of the strip decomposition and rows
+ * 2..ny_local+1 the interior; pitch_elems = nx, comp_stride = (ny_local+4)*nx */
 int nsdg_dyn_field_ptr(nsdg_ctx* ctx, int32_t field, void** device_ptr);
 /* advance tracer `field` (NSDG_DF_H or NSDG_DF_A) by dt with the current U,V */
 int nsdg_transport_step(nsdg_ctx* ctx, int32_t field, double dt);

@@ -37,43 +37,30 @@ void* open_nccl(std::string& err)
     return nullptr;
 }
 
-struct PackArgs {
-    double* plane[12];
+// rows to gather into (pack) or scatter from (unpack) a contiguous message buffer, in buffer order
+constexpr int MAX_HALO_ROWS = 64;
+struct RowList {
+    double* plane[MAX_HALO_ROWS];
+    int row[MAX_HALO_ROWS];
     int n;
-    int64_t nx;
-    int64_t row_lo, row_hi; // source (pack) or destination (unpack) rows
-    double* buf_lo; // pack: rows row_lo -> buf_lo ; unpack: buf_lo -> rows row_lo
-    double* buf_hi;
 };
 
-// blockIdx.y = plane, blockIdx.z = 0 (lo) / 1 (hi)
-__global__ void pack_rows(const __grid_constant__ PackArgs A)
+// blockIdx.y = entry of the list
+__global__ void pack_rows(const __grid_constant__ RowList L, double* buf, int64_t nx)
 {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= A.nx)
+    if (i >= nx)
         return;
-    const int p = blockIdx.y;
-    if (blockIdx.z == 0) {
-        if (A.buf_lo)
-            A.buf_lo[p * A.nx + i] = A.plane[p][A.row_lo * A.nx + i];
-    } else {
-        if (A.buf_hi)
-            A.buf_hi[p * A.nx + i] = A.plane[p][A.row_hi * A.nx + i];
-    }
+    const int e = blockIdx.y;
+    buf[e * nx + i] = L.plane[e][L.row[e] * nx + i];
 }
-__global__ void unpack_rows(const __grid_constant__ PackArgs A)
+__global__ void unpack_rows(const __grid_constant__ RowList L, const double* buf, int64_t nx)
 {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= A.nx)
+    if (i >= nx)
         return;
-    const int p = blockIdx.y;
-    if (blockIdx.z == 0) {
-        if (A.buf_lo)
-            A.plane[p][A.row_lo * A.nx + i] = A.buf_lo[p * A.nx + i];
-    } else {
-        if (A.buf_hi)
-            A.plane[p][A.row_hi * A.nx + i] = A.buf_hi[p * A.nx + i];
-    }
+    const int e = blockIdx.y;
+    L.plane[e][L.row[e] * nx + i] = buf[e * nx + i];
 }
 
 } // namespace
@@ -99,47 +86,73 @@ void nsdg_comm_free(nsdg_ctx* ctx)
     ctx->comm = nullptr;
 }
 
-int nsdg_halo_exchange(nsdg_ctx* ctx, const PlaneSet& planes, int which)
+int nsdg_halo_exchange(nsdg_ctx* ctx, const HaloSpec* specs, int nspecs)
 {
-    if (!nsdg_comm_active(ctx) || planes.n == 0)
+    if (!nsdg_comm_active(ctx) || nspecs == 0)
         return NSDG_OK;
-    DynState* d = ctx->dyn;
     CommState* c = ctx->comm;
-    NSDG_REQUIRE(ctx, (size_t)planes.n * d->nx <= d->halo_capacity, NSDG_EINVAL, "too many planes in one halo exchange");
+    DynState* d = ctx->dyn;
+    const int G = NSDG_GHOST;
+    const int nyl = (int)d->nyl;
+    // my top interior rows -> lower ghosts of the rank above; my bottom interior rows -> upper
+    // ghosts of the rank below.  Sender and receiver enumerate (spec, plane, row) identically.
+    RowList send_up = {}, send_dn = {}, recv_lo = {}, recv_hi = {};
+    for (int s = 0; s < nspecs; ++s) {
+        const HaloSpec& h = specs[s];
+        NSDG_REQUIRE(ctx, h.nlo >= 0 && h.nlo <= G && h.nhi >= 0 && h.nhi <= G && h.nlo <= nyl && h.nhi <= nyl,
+            NSDG_EINVAL, "halo width out of range");
+        for (int q = 0; q < h.planes.n; ++q) {
+            for (int r = 0; r < h.nlo; ++r) { // ghost row G-nlo+r <- neighbour's interior row G+nyl-nlo+r
+                NSDG_REQUIRE(ctx, send_up.n < MAX_HALO_ROWS, NSDG_EINVAL, "too many rows in one halo exchange");
+                send_up.plane[send_up.n] = h.planes.p[q];
+                send_up.row[send_up.n++] = G + nyl - h.nlo + r;
+                recv_lo.plane[recv_lo.n] = h.planes.p[q];
+                recv_lo.row[recv_lo.n++] = G - h.nlo + r;
+            }
+            for (int r = 0; r < h.nhi; ++r) { // ghost row G+nyl+r <- neighbour's interior row G+r
+                NSDG_REQUIRE(ctx, send_dn.n < MAX_HALO_ROWS, NSDG_EINVAL, "too many rows in one halo exchange");
+                send_dn.plane[send_dn.n] = h.planes.p[q];
+                send_dn.row[send_dn.n++] = G + r;
+                recv_hi.plane[recv_hi.n] = h.planes.p[q];
+                recv_hi.row[recv_hi.n++] = G + nyl + r;
+            }
+        }
+    }
     const int up = (c->rank + 1) % c->nranks, down = (c->rank + c->nranks - 1) % c->nranks;
-    const bool fill_lo = which & 1, fill_hi = which & 2;
-    const size_t count = (size_t)planes.n * d->nx;
-    PackArgs A;
-    for (int q = 0; q < planes.n; ++q)
-        A.plane[q] = planes.p[q];
-    A.n = planes.n;
-    A.nx = d->nx;
-    // pack: my top owned row feeds the upper neighbour's lower ghost; my bottom owned row feeds
-    // the lower neighbour's upper ghost
-    A.row_hi = d->nyl;
-    A.row_lo = 1;
-    A.buf_hi = fill_lo ? d->send_hi : nullptr;
-    A.buf_lo = fill_hi ? d->send_lo : nullptr;
-    dim3 block(256), grid((unsigned)((d->nx + 255) / 256), (unsigned)planes.n, 2);
-    NSDG_KERNEL(ctx, NSDG_K_PACK, pack_rows<<<grid, block, 0, ctx->stream>>>(A));
+    dim3 block(256);
+    const unsigned gx = (unsigned)((d->nx + 255) / 256);
+    if (send_up.n)
+        NSDG_KERNEL(ctx, NSDG_K_PACK, pack_rows<<<dim3(gx, send_up.n), block, 0, ctx->stream>>>(send_up, d->send_hi, d->nx));
+    if (send_dn.n)
+        NSDG_KERNEL(ctx, NSDG_K_PACK, pack_rows<<<dim3(gx, send_dn.n), block, 0, ctx->stream>>>(send_dn, d->send_lo, d->nx));
     NSDG_NCCL(ctx, c, c->GroupStart());
-    if (fill_lo) {
+    if (send_up.n) {
+        const size_t count = (size_t)send_up.n * d->nx;
         NSDG_NCCL(ctx, c, c->Send(d->send_hi, count, ncclFloat64, up, c->comm, ctx->stream));
         NSDG_NCCL(ctx, c, c->Recv(d->recv_lo, count, ncclFloat64, down, c->comm, ctx->stream));
         c->bytes_sent += (int64_t)count * 8;
     }
-    if (fill_hi) {
+    if (send_dn.n) {
+        const size_t count = (size_t)send_dn.n * d->nx;
         NSDG_NCCL(ctx, c, c->Send(d->send_lo, count, ncclFloat64, down, c->comm, ctx->stream));
         NSDG_NCCL(ctx, c, c->Recv(d->recv_hi, count, ncclFloat64, up, c->comm, ctx->stream));
         c->bytes_sent += (int64_t)count * 8;
     }
     NSDG_NCCL(ctx, c, c->GroupEnd());
-    A.row_lo = 0;
-    A.row_hi = d->nyl + 1;
-    A.buf_lo = fill_lo ? d->recv_lo : nullptr;
-    A.buf_hi = fill_hi ? d->recv_hi : nullptr;
-    NSDG_KERNEL(ctx, NSDG_K_UNPACK, unpack_rows<<<grid, block, 0, ctx->stream>>>(A));
+    if (recv_lo.n)
+        NSDG_KERNEL(ctx, NSDG_K_UNPACK, unpack_rows<<<dim3(gx, recv_lo.n), block, 0, ctx->stream>>>(recv_lo, d->recv_lo, d->nx));
+    if (recv_hi.n)
+        NSDG_KERNEL(ctx, NSDG_K_UNPACK, unpack_rows<<<dim3(gx, recv_hi.n), block, 0, ctx->stream>>>(recv_hi, d->recv_hi, d->nx));
     return NSDG_OK;
+}
+
+int nsdg_halo_exchange(nsdg_ctx* ctx, const PlaneSet& planes, int which)
+{
+    HaloSpec h;
+    h.planes = planes;
+    h.nlo = (which & 1) ? 1 : 0;
+    h.nhi = (which & 2) ? 1 : 0;
+    return nsdg_halo_exchange(ctx, &h, 1);
 }
 
 extern "C" {

@@ -36,7 +36,7 @@ __global__ void mass_kernel(const double* mean, int64_t nx, int64_t nyl, double*
     double s = 0.;
     const int64_t n = nx * nyl;
     for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < n; q += (int64_t)gridDim.x * blockDim.x)
-        s += mean[nx + q]; // interior starts at row 1
+        s += mean[NSDG_GHOST * nx + q]; // interior starts at row NSDG_GHOST
     for (int off = 16; off > 0; off >>= 1)
         s += __shfl_down_sync(0xffffffffu, s, off);
     __shared__ double part[32];
@@ -72,7 +72,7 @@ int transport_fields(nsdg_ctx* ctx, int nfields, double** phi, double** s1, doub
 {
     DynState* d = ctx->dyn;
     const bool multi = nsdg_comm_active(ctx);
-    const int64_t r0 = 1, r1 = d->nyl + 1;
+    const int64_t r0 = NSDG_GHOST, r1 = NSDG_GHOST + d->nyl;
     int rc;
     auto halo = [&](double** arr) -> int {
         if (!multi)
@@ -106,11 +106,11 @@ int transport_fields(nsdg_ctx* ctx, int nfields, double** phi, double** s1, doub
         || (rc = limit(s1)))
         return rc;
     if (d->rk == 1) {
-        // copy the interior of every component (rows 1..nyl are contiguous within a plane)
+        // copy the interior of every component (interior rows are contiguous within a plane)
         for (int f = 0; f < nfields; ++f)
             for (int c = 0; c < d->nc; ++c)
-                NSDG_CUDA(ctx, cudaMemcpyAsync(phi[f] + (size_t)c * d->plane + d->nx,
-                                   s1[f] + (size_t)c * d->plane + d->nx,
+                NSDG_CUDA(ctx, cudaMemcpyAsync(phi[f] + (size_t)c * d->plane + NSDG_GHOST * d->nx,
+                                   s1[f] + (size_t)c * d->plane + NSDG_GHOST * d->nx,
                                    sizeof(double) * (size_t)d->nx * d->nyl, cudaMemcpyDeviceToDevice,
                                    ctx->stream));
         return NSDG_OK;
@@ -137,62 +137,81 @@ int mevp_cycle(nsdg_ctx* ctx, double dt, int nsub)
     DynState* d = ctx->dyn;
     const bool multi = nsdg_comm_active(ctx);
     int rc;
+    const int G = NSDG_GHOST;
     if (multi) {
-        // lower ghost rows of H, A (strength and nodal means), both ghost rows of u, v, lower
-        // ghost row of S (it then evolves redundantly, bit-identical to the owner's copy)
-        PlaneSet ps = planes_of(d, d->f[NSDG_DF_H], d->nc);
-        append(ps, d, d->f[NSDG_DF_A], d->nc);
-        if ((rc = nsdg_halo_exchange(ctx, ps, 1)))
+        // ghost rows the sub-cycle reads: H, A (strength on the recomputed ghost cells, nodal
+        // means), the stress, and every node array (velocity, forcing) -- the pair kernel works
+        // on a two-row halo below and above (one row above for cell data)
+        HaloSpec hs[2];
+        hs[0].planes = planes_of(d, d->f[NSDG_DF_H], d->nc);
+        append(hs[0].planes, d, d->f[NSDG_DF_A], d->nc);
+        hs[0].nlo = 2;
+        hs[0].nhi = 1;
+        if ((rc = nsdg_halo_exchange(ctx, hs, 1)))
             return rc;
-        ps = planes_of(d, d->f[NSDG_DF_S11], 3);
-        append(ps, d, d->f[NSDG_DF_S12], 3);
-        append(ps, d, d->f[NSDG_DF_S22], 3);
-        if ((rc = nsdg_halo_exchange(ctx, ps, 1)))
-            return rc;
-        ps.n = 0;
-        ps.p[ps.n++] = d->f[NSDG_DF_U];
-        ps.p[ps.n++] = d->f[NSDG_DF_V];
-        if ((rc = nsdg_halo_exchange(ctx, ps, 3)))
+        hs[0].planes = planes_of(d, d->f[NSDG_DF_S11], 3);
+        append(hs[0].planes, d, d->f[NSDG_DF_S12], 3);
+        append(hs[0].planes, d, d->f[NSDG_DF_S22], 3);
+        hs[1].planes.n = 0;
+        for (int q : { NSDG_DF_U, NSDG_DF_V, NSDG_DF_UATM, NSDG_DF_VATM, NSDG_DF_UOCN, NSDG_DF_VOCN })
+            hs[1].planes.p[hs[1].planes.n++] = d->f[q];
+        hs[1].nlo = hs[1].nhi = 2;
+        if ((rc = nsdg_halo_exchange(ctx, hs, 2)))
             return rc;
     }
     if ((rc = nsdg_mevp_prepare(ctx, dt)))
         return rc;
     double *u = d->f[NSDG_DF_U], *v = d->f[NSDG_DF_V], *u2 = d->u2, *v2 = d->v2;
-    const int64_t s0 = multi ? 0 : 1;
+    const int64_t s0 = multi ? G - 1 : G, r0 = G, r1 = G + d->nyl;
     const bool fused = !(d->cfg.flags & NSDG_DYN_SPLIT_MEVP);
     static int pair_env = -1; // NSDG_MEVP_PAIR=0/1 overrides the default (tuning / A-B tests)
     if (pair_env < 0) {
         const char* e = getenv("NSDG_MEVP_PAIR");
         pair_env = e ? (atoi(e) != 0) : 1;
     }
-    // single rank: two sub-iterations per launch while at least two remain
-    const bool pair = pair_env && fused && !multi && !(d->cfg.flags & NSDG_DYN_SINGLE_MEVP);
+    // two sub-iterations per launch (and per halo exchange) while at least two remain
+    const bool pair = pair_env && fused && !(d->cfg.flags & NSDG_DYN_SINGLE_MEVP);
     double* sa[3] = { d->f[NSDG_DF_S11], d->f[NSDG_DF_S12], d->f[NSDG_DF_S22] };
     double* sb[3] = { d->s2[0], d->s2[1], d->s2[2] };
     for (int p = 0; p < nsub; ++p) {
+        bool paired = false;
         if (pair && p + 1 < nsub) {
             if ((rc = nsdg_mevp_pair(ctx, dt, u, v, u2, v2, sa, sb)))
                 return rc;
             for (int q = 0; q < 3; ++q)
                 std::swap(sa[q], sb[q]);
             ++p;
+            paired = true;
         } else if (fused) {
-            if ((rc = nsdg_mevp_fused(ctx, dt, u, v, u2, v2, sa, sb, 1, d->nyl + 1)))
+            if ((rc = nsdg_mevp_fused(ctx, dt, u, v, u2, v2, sa, sb, r0, r1)))
                 return rc;
             for (int q = 0; q < 3; ++q)
                 std::swap(sa[q], sb[q]);
         } else {
-            if ((rc = nsdg_mevp_stress(ctx, dt, u, v, sa, s0, d->nyl + 1)))
+            if ((rc = nsdg_mevp_stress(ctx, dt, u, v, sa, s0, r1)))
                 return rc;
-            if ((rc = nsdg_mevp_velocity(ctx, dt, u, v, u2, v2, sa, 1, d->nyl + 1)))
+            if ((rc = nsdg_mevp_velocity(ctx, dt, u, v, u2, v2, sa, r0, r1)))
                 return rc;
         }
         if (multi) {
-            PlaneSet ps;
-            ps.n = 0;
-            ps.p[ps.n++] = u2;
-            ps.p[ps.n++] = v2;
-            if ((rc = nsdg_halo_exchange(ctx, ps, 3)))
+            // after a pair the next pair needs the new stress on its ghost cells as well; a single
+            // sub-iteration keeps the first lower ghost row of S current by itself
+            HaloSpec hs[2];
+            int n = 0;
+            if (paired) {
+                hs[n].planes = planes_of(d, sa[0], 3);
+                append(hs[n].planes, d, sa[1], 3);
+                append(hs[n].planes, d, sa[2], 3);
+                hs[n].nlo = 2;
+                hs[n].nhi = 1;
+                ++n;
+            }
+            hs[n].planes.n = 0;
+            hs[n].planes.p[hs[n].planes.n++] = u2;
+            hs[n].planes.p[hs[n].planes.n++] = v2;
+            hs[n].nlo = hs[n].nhi = paired ? 2 : 1;
+            ++n;
+            if ((rc = nsdg_halo_exchange(ctx, hs, n)))
                 return rc;
         }
         std::swap(u, u2);
@@ -273,7 +292,7 @@ int nsdg_dyn_init(nsdg_ctx* ctx, const nsdg_dyn_config* cfg)
     NSDG_REQUIRE(ctx, (cfg->flags & ~(NSDG_DYN_SPLIT_MEVP | NSDG_DYN_SINGLE_MEVP)) == 0, NSDG_EINVAL,
         "unknown flags 0x%x", cfg->flags);
     // the kernels index every array with 32-bit integers
-    NSDG_REQUIRE(ctx, (cfg->ny_local + 2) * cfg->nx * (cfg->ncomp > 4 ? cfg->ncomp : 4) < (int64_t)1 << 31,
+    NSDG_REQUIRE(ctx, (cfg->ny_local + 2 * NSDG_GHOST) * cfg->nx * (cfg->ncomp > 4 ? cfg->ncomp : 4) < (int64_t)1 << 31,
         NSDG_EINVAL, "strip too large for 32-bit indexing: %lld x %lld cells, %d components",
         (long long)cfg->nx, (long long)cfg->ny_local, cfg->ncomp);
     const bool multi = nsdg_comm_active(ctx);
@@ -286,7 +305,7 @@ int nsdg_dyn_init(nsdg_ctx* ctx, const nsdg_dyn_config* cfg)
     nsdg_mevp_default_params(&d->mp);
     d->nx = cfg->nx;
     d->nyl = cfg->ny_local;
-    d->rows = d->nyl + 2;
+    d->rows = d->nyl + 2 * NSDG_GHOST;
     d->plane = d->rows * d->nx;
     d->nc = cfg->ncomp;
     d->rk = cfg->rk_order ? cfg->rk_order : (d->nc == 1 ? 1 : (d->nc == 3 ? 2 : 3));
@@ -315,7 +334,7 @@ int nsdg_dyn_init(nsdg_ctx* ctx, const nsdg_dyn_config* cfg)
                 return rc;
     NSDG_CUDA(ctx, cudaMalloc(&d->scratch, 64));
     if (multi) {
-        d->halo_capacity = 12 * (size_t)d->nx;
+        d->halo_capacity = 64 * (size_t)d->nx;
         double** hb[] = { &d->send_lo, &d->send_hi, &d->recv_lo, &d->recv_hi };
         for (double** p : hb)
             NSDG_CUDA(ctx, cudaMalloc(p, sizeof(double) * d->halo_capacity));
@@ -352,7 +371,7 @@ int nsdg_dyn_upload(nsdg_ctx* ctx, int32_t field, const double* host)
     NSDG_REQUIRE(ctx, field >= 0 && field < NSDG_DF_COUNT && host, NSDG_EINVAL, "bad field/host");
     const size_t inner = (size_t)d->nx * d->nyl;
     for (int c = 0; c < d->ncomp[field]; ++c)
-        NSDG_CUDA(ctx, cudaMemcpyAsync(d->f[field] + (size_t)c * d->plane + d->nx, host + c * inner,
+        NSDG_CUDA(ctx, cudaMemcpyAsync(d->f[field] + (size_t)c * d->plane + NSDG_GHOST * d->nx, host + c * inner,
                            sizeof(double) * inner, cudaMemcpyHostToDevice, ctx->stream));
     NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return NSDG_OK;
@@ -366,7 +385,7 @@ int nsdg_dyn_download(nsdg_ctx* ctx, int32_t field, double* host)
     NSDG_REQUIRE(ctx, field >= 0 && field < NSDG_DF_COUNT && host, NSDG_EINVAL, "bad field/host");
     const size_t inner = (size_t)d->nx * d->nyl;
     for (int c = 0; c < d->ncomp[field]; ++c)
-        NSDG_CUDA(ctx, cudaMemcpyAsync(host + c * inner, d->f[field] + (size_t)c * d->plane + d->nx,
+        NSDG_CUDA(ctx, cudaMemcpyAsync(host + c * inner, d->f[field] + (size_t)c * d->plane + NSDG_GHOST * d->nx,
                            sizeof(double) * inner, cudaMemcpyDeviceToHost, ctx->stream));
     NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return NSDG_OK;

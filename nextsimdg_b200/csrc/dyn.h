@@ -1,17 +1,21 @@
 // Device-resident state of the dynamics (DG transport + mEVP) and the internal launchers.
 //
-// HBM layout.  Every array is a stack of planes; a plane is (ny_local+2) rows of nx doubles,
-// row 0 and row ny_local+1 being ghost rows of the strip decomposition (unused when one rank
-// owns the whole periodic domain: kernels then wrap row indices instead).  DG fields are
+// HBM layout.  Every array is a stack of planes; a plane is (ny_local + 2*NSDG_GHOST) rows of nx
+// doubles: interior rows are [NSDG_GHOST, NSDG_GHOST + ny_local), the NSDG_GHOST rows on either
+// side are ghost rows of the strip decomposition (unused when one rank owns the whole periodic
+// domain: kernels then wrap row indices instead).  Two ghost rows, because the pair-fused mEVP
+// kernel advances two sub-iterations per halo exchange.  DG fields are
 // component-major, a[c][row][i], so that each coefficient is its own coalesced stream.  Node
 // (CG1) arrays use the same plane shape; node (i,row) is the lower-left corner of cell (i,row).
 #pragma once
 #include "ctx.h"
 
+constexpr int NSDG_GHOST = 2;
+
 struct DynState {
     nsdg_dyn_config cfg;
     nsdg_mevp_params mp;
-    int64_t nx = 0, nyl = 0, rows = 0, plane = 0; // rows = nyl+2, plane = rows*nx
+    int64_t nx = 0, nyl = 0, rows = 0, plane = 0; // rows = nyl + 2*NSDG_GHOST, plane = rows*nx
     int nc = 0; // tracer components
     int rk = 0; // RK order actually used
     bool wrap = true; // single rank: periodic wrap in y inside the kernels
@@ -37,9 +41,16 @@ struct DynState {
     size_t halo_capacity = 0; // doubles per buffer
 };
 
-struct PlaneSet { // up to 12 planes handled by one halo exchange
+struct PlaneSet { // planes handled together by one halo exchange
     double* p[12];
     int n;
+};
+// One group of planes of a halo exchange: fill `nlo` lower ghost rows (from the top interior
+// rows of the rank below) and `nhi` upper ghost rows (from the bottom interior rows of the rank
+// above); 0 <= nlo, nhi <= NSDG_GHOST.
+struct HaloSpec {
+    PlaneSet planes;
+    int nlo, nhi;
 };
 
 // transport.cu ------------------------------------------------------------------------------
@@ -64,8 +75,9 @@ int nsdg_mevp_pair(nsdg_ctx* ctx, double dt, const double* u, const double* v, d
     double* vnew, double* const* Sold, double* const* Snew);
 
 // comm.cu -----------------------------------------------------------------------------------
-// fill ghost rows of the given planes: row nyl -> upper neighbour's row 0, row 1 -> lower
-// neighbour's row nyl+1 (ring).  which: 1 = lower ghost only, 2 = upper ghost only, 3 = both.
-// No-op on a single rank (kernels wrap).
+// Ring halo exchange of up to 3 plane groups in ONE message per neighbour.  No-op on a single
+// rank (kernels wrap).
+int nsdg_halo_exchange(nsdg_ctx* ctx, const HaloSpec* specs, int nspecs);
+// one group: which = 1 lower ghost row only, 2 upper ghost row only, 3 both (one row each)
 int nsdg_halo_exchange(nsdg_ctx* ctx, const PlaneSet& planes, int which);
 bool nsdg_comm_active(const nsdg_ctx* ctx);

@@ -31,7 +31,7 @@ constexpr double GQ = 0.28867513459481287; // 1/(2 sqrt 3)
 
 struct MevpArgs {
     int nx, nyl, plane, r0, r1, j0;
-    int wrap, nc, bc, pad_;
+    int wrap, nc, bc, ny_global;
     double ihx, ihy, ie2, dmin2, ia; // stress: 1/hx, 1/hy, 1/e^2, Delta_min^2, 1/alpha
     double c1, c2, c3, c4; // divergence: 0.5/hx, 1/(12 hx), 0.5/hy, 1/(12 hy)
     double beta, beta1, dtf; // beta, 1+beta, dt*f
@@ -59,15 +59,15 @@ struct MevpArgs {
 __device__ __forceinline__ int row_below(const MevpArgs& A, int r)
 {
     int rm = r - 1;
-    if (A.wrap && rm < 1)
-        rm = A.nyl;
+    if (A.wrap && rm < NSDG_GHOST)
+        rm += A.nyl;
     return rm;
 }
 __device__ __forceinline__ int row_above(const MevpArgs& A, int r)
 {
     int rp = r + 1;
-    if (A.wrap && rp > A.nyl)
-        rp = 1;
+    if (A.wrap && rp >= NSDG_GHOST + A.nyl)
+        rp -= A.nyl;
     return rp;
 }
 
@@ -259,9 +259,12 @@ __device__ __forceinline__ void node_update(const MevpArgs& A, int n, double dx,
     vnew = (mb * v + cy0 + cd * vo - mf * u + dy) * inv;
 }
 
+// closed box: the node lines i == 0 and global j == 0 (jrow = plane row - NSDG_GHOST; a strip's
+// upper ghost rows on the last rank are the ring's row 0 again)
 __device__ __forceinline__ bool dirichlet(const MevpArgs& A, int gi, int jrow)
 {
-    return A.bc == NSDG_BC_BOX && (gi == 0 || A.j0 + jrow == 0);
+    const int j = A.j0 + jrow;
+    return A.bc == NSDG_BC_BOX && (gi == 0 || j == 0 || j == A.ny_global);
 }
 
 // ---- split variant --------------------------------------------------------------------------
@@ -303,7 +306,7 @@ __global__ void __launch_bounds__(256) velocity_kernel(const __grid_constant__ M
         return;
     const int n = r * A.nx + i;
     double un_ = 0., vn_ = 0.;
-    if (!dirichlet(A, i, r - 1)) {
+    if (!dirichlet(A, i, r - NSDG_GHOST)) {
         const int rm = row_below(A, r);
         const int im = (i == 0) ? A.nx - 1 : i - 1;
         Div7 q;
@@ -398,11 +401,11 @@ __global__ void __launch_bounds__(FusedCfg<TX, TY>::NT, FusedCfg<TX, TY>::MINB) 
                 gi += A.nx;
             const int gip = (gi == A.nx - 1) ? 0 : gi + 1;
             bool ghost_row = false;
-            if (gr < 1) {
+            if (gr < NSDG_GHOST) {
                 if (A.wrap)
-                    gr = A.nyl;
+                    gr += A.nyl;
                 else
-                    ghost_row = true; // strip decomposition: row 0 is kept current redundantly
+                    ghost_row = true; // strips: the first lower ghost row is kept current redundantly
             }
             const int k = gr * A.nx + gi;
             const int grp = row_above(A, gr);
@@ -442,7 +445,7 @@ __global__ void __launch_bounds__(FusedCfg<TX, TY>::NT, FusedCfg<TX, TY>::MINB) 
         return;
     const int n = nr * A.nx + ni;
     double un_ = 0., vn_ = 0.;
-    if (!dirichlet(A, ni, nr - 1)) {
+    if (!dirichlet(A, ni, nr - NSDG_GHOST)) {
         double dx, dy;
         div_from_smem(A, ss, NCELL, ty * CXS + tx, CXS, dx, dy);
         node_update(A, n, dx, dy, __ldg(A.u + n), __ldg(A.v + n), un_, vn_);
@@ -465,8 +468,9 @@ __global__ void __launch_bounds__(FusedCfg<TX, TY>::NT, FusedCfg<TX, TY>::MINB) 
 //                   S^{p+1} and P_g in registers, u^{p+1} from shared memory; owned cells -> HBM
 //   D  velocity p+2 on the TX x TY owned nodes -> HBM
 // Every value is computed by the same formulas as in the single sub-iteration kernels, so a
-// redundantly computed halo value is bit-identical to the owner's.  Single rank only (periodic
-// wrap in x and y by index arithmetic); strips use one sub-iteration per exchange.
+// redundantly computed halo value is bit-identical to the owner's.  Single rank: periodic wrap
+// in x and y by index arithmetic.  Strips: the two ghost rows on either side carry S^p, P_g,
+// u^p and the node constants of the neighbours, refreshed once per pair (dyn.cu).
 __device__ __forceinline__ int wrap_idx(int i, int n)
 {
     if (i < 0)
@@ -508,9 +512,17 @@ __global__ void __launch_bounds__(PairCfg<TX, TY>::NT, MINB) mevp_pair_kernel(co
     int k = 0;
     if (in_a) {
         const int gi = wrap_idx(i0 - 2 + ax, A.nx);
-        const int gr = 1 + wrap_idx(r0 - 3 + ay, A.nyl); // plane row (interior rows are 1..nyl)
         const int gip = (gi == A.nx - 1) ? 0 : gi + 1;
-        const int grp = (gr == A.nyl) ? 1 : gr + 1;
+        // plane row: periodic wrap on a single rank, ghost rows of the strip otherwise (rows past
+        // a partial last tile row are clamped to valid memory and never used)
+        int gr = r0 - 2 + ay, grp;
+        if (A.wrap) {
+            gr = NSDG_GHOST + wrap_idx(gr - NSDG_GHOST, A.nyl);
+            grp = (gr == NSDG_GHOST + A.nyl - 1) ? NSDG_GHOST : gr + 1;
+        } else {
+            gr = min(gr, A.nyl + 2 * NSDG_GHOST - 1);
+            grp = min(gr + 1, A.nyl + 2 * NSDG_GHOST - 1);
+        }
         k = gr * A.nx + gi;
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
@@ -534,10 +546,14 @@ __global__ void __launch_bounds__(PairCfg<TX, TY>::NT, MINB) mevp_pair_kernel(co
     if (tid < NB) {
         const int bx = tid % BX, by = tid / BX;
         const int ni = wrap_idx(i0 - 1 + bx, A.nx);
-        const int nj = wrap_idx(r0 - 2 + by, A.nyl); // interior row index 0..nyl-1
+        int nrow = r0 - 1 + by; // plane row
+        if (A.wrap)
+            nrow = NSDG_GHOST + wrap_idx(nrow - NSDG_GHOST, A.nyl);
+        else
+            nrow = min(nrow, A.nyl + 2 * NSDG_GHOST - 1);
         double un_ = 0., vn_ = 0.;
-        if (!dirichlet(A, ni, nj)) {
-            const int n = (1 + nj) * A.nx + ni;
+        if (!dirichlet(A, ni, nrow - NSDG_GHOST)) {
+            const int n = nrow * A.nx + ni;
             double dx, dy;
             div_from_smem(A, ss, NA, by * AX + bx, AX, dx, dy);
             node_update(A, n, dx, dy, __ldg(A.u + n), __ldg(A.v + n), un_, vn_);
@@ -573,7 +589,7 @@ __global__ void __launch_bounds__(PairCfg<TX, TY>::NT, MINB) mevp_pair_kernel(co
         if (ni < A.nx && nr < A.r1) {
             const int n = nr * A.nx + ni;
             double un_ = 0., vn_ = 0.;
-            if (!dirichlet(A, ni, nr - 1)) {
+            if (!dirichlet(A, ni, nr - NSDG_GHOST)) {
                 const int b = (ty + 1) * BX + tx + 1;
                 double dx, dy;
                 div_from_smem(A, ss, NA, (ty + 1) * AX + tx + 1, AX, dx, dy);
@@ -593,6 +609,7 @@ MevpArgs base_args(DynState* d, double dt)
     A.nyl = (int)d->nyl;
     A.plane = (int)d->plane;
     A.j0 = (int)d->cfg.j0;
+    A.ny_global = (int)d->cfg.ny_global;
     A.wrap = d->wrap ? 1 : 0;
     A.nc = d->nc;
     A.bc = P.bc;
@@ -644,20 +661,24 @@ void set_stress(MevpArgs& A, double* const* Sold, double* const* Snew)
 
 } // namespace
 
-// Requires (multi-rank): ghost rows of H, A current.  Single rank: kernels wrap.
+// Requires (strips): two lower and one upper ghost row of H, A current.  Single rank: kernels wrap.
 int nsdg_mevp_prepare(nsdg_ctx* ctx, double dt)
 {
     DynState* d = ctx->dyn;
     MevpArgs A = base_args(d, dt);
-    // strength on rows 0..nyl when the lower ghost row's stress is computed redundantly
-    A.r0 = d->wrap ? 1 : 0;
-    A.r1 = (int)d->nyl + 1;
+    const int G = NSDG_GHOST;
+    // strips: strength also on the ghost cell rows the (pair-)fused kernels recompute
+    A.r0 = d->wrap ? G : 0;
+    A.r1 = G + (int)d->nyl + (d->wrap ? 0 : 1);
     A.out0 = d->pg;
     dim3 block(256), grid((unsigned)((d->nx + 255) / 256), (unsigned)(A.r1 - A.r0));
     NSDG_KERNEL(ctx, NSDG_K_PRESSURE, pressure_kernel<<<grid, block, 0, ctx->stream>>>(A));
-    A.r0 = 1;
+    // node constants on the owned node rows, plus (strips) the first ghost node row on either
+    // side, which phase B of the pair kernel updates redundantly
+    A.r0 = d->wrap ? G : G - 1;
+    A.r1 = G + (int)d->nyl + (d->wrap ? 0 : 1);
     A.out0 = d->nd;
-    grid = dim3((unsigned)((d->nx + 255) / 256), (unsigned)d->nyl);
+    grid = dim3((unsigned)((d->nx + 255) / 256), (unsigned)(A.r1 - A.r0));
     NSDG_KERNEL(ctx, NSDG_K_NODAL, nodal_kernel<<<grid, block, 0, ctx->stream>>>(A));
     return NSDG_OK;
 }
@@ -752,15 +773,14 @@ int nsdg_mevp_pair(nsdg_ctx* ctx, double dt, const double* u, const double* v, d
     double* vnew, double* const* Sold, double* const* Snew)
 {
     DynState* d = ctx->dyn;
-    NSDG_REQUIRE(ctx, d->wrap, NSDG_ESTATE, "pair-fused mEVP kernel needs a single rank (wrap mode)");
     MevpArgs A = base_args(d, dt);
     A.u = u;
     A.v = v;
     A.out0 = unew;
     A.out1 = vnew;
     set_stress(A, Sold, Snew);
-    A.r0 = 1;
-    A.r1 = (int)d->nyl + 1;
+    A.r0 = NSDG_GHOST;
+    A.r1 = NSDG_GHOST + (int)d->nyl;
     static int tile = -1;
     if (tile < 0) {
         const char* e = getenv("NSDG_PAIR_TILE");

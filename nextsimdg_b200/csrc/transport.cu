@@ -90,11 +90,11 @@ __global__ void __launch_bounds__(256) transport_stage_kernel(const __grid_const
     if (i >= A.nx || r >= A.r1)
         return;
     int64_t rm = r - 1, rp = r + 1;
-    if (A.wrap) {
-        if (rm < 1)
-            rm = A.nyl;
-        if (rp > A.nyl)
-            rp = 1;
+    if (A.wrap) { // interior rows are [NSDG_GHOST, NSDG_GHOST + nyl)
+        if (rm < NSDG_GHOST)
+            rm += A.nyl;
+        if (rp >= NSDG_GHOST + A.nyl)
+            rp -= A.nyl;
     }
     const int64_t im = (i == 0) ? A.nx - 1 : i - 1;
     const int64_t ip = (i == A.nx - 1) ? 0 : i + 1;
@@ -199,8 +199,8 @@ template <int NC>
 __global__ void limit_kernel(double* phi, int64_t nx, int64_t nyl, int64_t plane, double lo, double hi)
 {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const int64_t r = 1 + (int64_t)blockIdx.y;
-    if (i >= nx || r > nyl)
+    const int64_t r = NSDG_GHOST + (int64_t)blockIdx.y;
+    if (i >= nx || (int64_t)blockIdx.y >= nyl)
         return;
     const int64_t k = r * nx + i;
     double c[NC];

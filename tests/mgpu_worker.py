@@ -10,7 +10,8 @@ import torch.distributed as dist
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from nextsimdg_b200 import strips, synthetic as S  # noqa: E402
-from nextsimdg_b200._abi import BC_BOX, BC_PERIODIC, DYN_SPLIT_MEVP, MevpParams  # noqa: E402
+from nextsimdg_b200._abi import (BC_BOX, BC_PERIODIC, DYN_SINGLE_MEVP, DYN_SPLIT_MEVP,  # noqa: E402
+                                   MevpParams)
 from nextsimdg_b200.gpu import Context, GpuDynamics  # noqa: E402
 
 
@@ -26,7 +27,9 @@ def main():
     ok = True
     for (nx, ny, bc, flags, nsub) in ((64, 16 * world + 3, BC_BOX, 0, 7),
                                       (45, 9 * world, BC_PERIODIC, 0, 4),
-                                      (64, 16 * world, BC_BOX, DYN_SPLIT_MEVP, 5)):
+                                      (64, 16 * world, BC_BOX, DYN_SPLIT_MEVP, 5),
+                                      (96, 5 * world + 1, BC_BOX, DYN_SINGLE_MEVP, 3),
+                                      (40, 2 * world, BC_PERIODIC, 0, 6)):
         F, hx, hy = S.box_case(nx, ny, 6)
         rng = np.random.default_rng(11)
         F["U"] = 0.05 * rng.standard_normal((ny, nx))
