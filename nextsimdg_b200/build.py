@@ -15,11 +15,10 @@ OBJDIR = os.path.join(CSRC, "build")
 
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-std=c++17", "-O3", "-lineinfo", "-Xcompiler", "-fPIC"]
-# per-file extras. thermo.cu keeps the reference's operation order (no FMA contraction) so that
-# its data-dependent branches resolve as on the CPU; see the header of that file.
+# per-file extras
 SOURCES = {
     "ctx.cu": [],
-    "thermo.cu": ["-fmad=false"],
+    "thermo.cu": [],
     "transport.cu": [],
     "mevp.cu": [],
     "dyn.cu": [],

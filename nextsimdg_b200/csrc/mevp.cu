@@ -22,6 +22,7 @@
 // All index arithmetic is 32-bit (validated by the host: every array of the sub-cycle has fewer
 // than 2^31 elements) and every quotient that does not depend on the cell is taken on the host.
 #include "dyn.h"
+#include "fp64_fast.cuh"
 #include <cstdlib>
 #include <string>
 
@@ -69,25 +70,6 @@ __device__ __forceinline__ int row_above(const MevpArgs& A, int r)
     if (A.wrap && rp >= NSDG_GHOST + A.nyl)
         rp -= A.nyl;
     return rp;
-}
-
-// ---- FP64 helpers for strictly positive, normal-range arguments (no special-case paths):
-// MUFU seed + one cubically convergent (rsqrt) / two quadratic (rcp) corrections, <= 1 ulp
-__device__ __forceinline__ double rsqrt_pos(double x)
-{
-    double y;
-    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
-    const double e = fma(x, -(y * y), 1.0);
-    return fma(fma(e, 0.375, 0.5), y * e, y);
-}
-__device__ __forceinline__ double rcp_pos(double d)
-{
-    double r;
-    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
-    double e = fma(-d, r, 1.0);
-    r = fma(r, e, r);
-    e = fma(-d, r, 1.0);
-    return fma(r, e, r);
 }
 
 __device__ __forceinline__ void prefetch_l1(const double* p)

@@ -11,10 +11,14 @@
 //
 // Layout: 15 structure-of-arrays FP64 streams of length ncells (14 inputs + the hidden
 // persistent newice); 5 are written back.  160 algorithmic bytes per
-// cell-update, HBM-bound; two cells per thread so every access is a 16-byte vector.
-// This file is compiled with -fmad=false: the operation order of the reference is kept so
-// that data-dependent branches (t1<tf, hi<minh, draught>hi, c<minc) resolve identically.
+// cell-update.  The reference's ~38 per-cell divisions are the cost centre on the FP64 pipe, so
+// quotients by constants and by dt are multiplications by reciprocals taken at compile time / on
+// the host, quotients with a common denominator share one reciprocal, and the remaining 14 are
+// Newton reciprocals (fp64_fast.cuh); exact zeros stay exact zeros (0*r == 0/d), so the
+// data-dependent branches (t1<tf, hi<minh, draught>hi, c<minc, hs>0) resolve as on the CPU and
+// the state agrees with the compiled reference to <= 1e-10 (tests/test_gpu_thermo.py).
 #include "ctx.h"
+#include "fp64_fast.cuh"
 
 namespace {
 
@@ -54,11 +58,11 @@ __device__ __forceinline__ double sph_f(const SphCoef& k, double t, double pPa)
     double pmb = pPa * 0.01;
     return 1 + k.bigA + pmb * (k.bigB + k.bigC * t * t);
 }
-// NextsimPhysics.cpp:377-381
-__device__ __forceinline__ double sph_est(const SphCoef& k, double t, double sal)
+// NextsimPhysics.cpp:377-381; rtc = 1/(t + c)
+__device__ __forceinline__ double sph_est(const SphCoef& k, double t, double sal, double rtc)
 {
     double salFactor = 1 - 5.37e-4 * sal;
-    return k.a * exp((k.b - t / k.d) * t / (t + k.c)) * salFactor;
+    return k.a * exp((k.b - t * (1. / k.d)) * t * rtc) * salFactor;
 }
 // NextsimPhysics.cpp:383-386; pow(x,4) as two squarings
 __device__ __forceinline__ double stefan_boltzmann(double tC)
@@ -84,41 +88,50 @@ struct CellOut {
     double hice, cice, hsnow, tice0, newice;
 };
 
+// idt = 1/dt
 template <bool DIAG>
 __device__ __forceinline__ CellOut thermo_cell(
-    const nsdg_thermo_params& P, double dt, const CellIn& in, double* diag)
+    const nsdg_thermo_params& P, double dt, double idt, const CellIn& in, double* diag)
 {
     const double hice = in.hice, cice = in.cice, hsnow = in.hsnow, tice0 = in.tice0;
     const double sst = in.sst, sss = in.sss, slp = in.slp, wind = in.wind;
     double newice = in.newice;
 
     // ---- updateDerivedData: IPhysics1d.hpp:33-45, NextsimPhysics.cpp:85-114 ----
-    // specific humidities (NextsimPhysics.cpp:333-343); est/f of the ice surface are reused
-    // by dq_dT below (the reference recomputes them, :356-369)
-    double estA = sph_est(SPH_WATER, in.tdew, 0.), fA = sph_f(SPH_WATER, in.tdew, slp);
-    double sphuma = SPH_ALPHA * fA * estA / (slp - SPH_BETA * fA * estA);
-    double estW = sph_est(SPH_WATER, sst, sss), fW = sph_f(SPH_WATER, sst, slp);
-    double sphumw = SPH_ALPHA * fW * estW / (slp - SPH_BETA * fW * estW);
-    double estI = sph_est(SPH_ICE, tice0, 0.), fI = sph_f(SPH_ICE, tice0, slp);
-    double sphumi = SPH_ALPHA * fI * estI / (slp - SPH_BETA * fI * estI);
-    double Ra_wet = AIR_RA / (1 - sphuma * (1 - VAPOUR_RA / AIR_RA));
-    double rho = slp / (Ra_wet * kelvin(in.tair));
-    double cspec = AIR_CP + sphuma * VAPOUR_CP;
-    const double hiTrue = (cice != 0) ? hice / cice : 0; // PrognosticData.hpp:56
-    const double hsTrue = (cice != 0) ? hsnow / cice : 0; // PrognosticData.hpp:75
+    // specific humidities (NextsimPhysics.cpp:333-343): q = alpha f est / (p - beta f est); est, f
+    // and the reciprocals of the ice surface are reused by dq_dT below (the reference recomputes
+    // them, :356-369)
+    const double estA = sph_est(SPH_WATER, in.tdew, 0., rcp_pos(in.tdew + SPH_WATER.c));
+    const double fA = sph_f(SPH_WATER, in.tdew, slp);
+    const double sphuma = SPH_ALPHA * fA * estA * rcp_pos(slp - SPH_BETA * fA * estA);
+    const double estW = sph_est(SPH_WATER, sst, sss, rcp_pos(sst + SPH_WATER.c));
+    const double fW = sph_f(SPH_WATER, sst, slp);
+    const double sphumw = SPH_ALPHA * fW * estW * rcp_pos(slp - SPH_BETA * fW * estW);
+    const double rtcI = rcp_pos(tice0 + SPH_ICE.c);
+    const double estI = sph_est(SPH_ICE, tice0, 0., rtcI);
+    const double fI = sph_f(SPH_ICE, tice0, slp);
+    const double rqI = rcp_pos(slp - SPH_BETA * fI * estI);
+    const double sphumi = SPH_ALPHA * fI * estI * rqI;
+    // rho = p / (R_wet T), R_wet = R_a / (1 - q_a (1 - R_v/R_a))   (:104-109)
+    const double rho = slp * (1 - sphuma * (1 - VAPOUR_RA / AIR_RA)) * rcp_pos(AIR_RA * kelvin(in.tair));
+    const double cspec = AIR_CP + sphuma * VAPOUR_CP;
+    const double icice = (cice != 0) ? rcp_pos(cice) : 0.;
+    const double hiTrue = hice * icice; // PrognosticData.hpp:56
+    const double hsTrue = hsnow * icice; // PrognosticData.hpp:75
     double hs_new = hsTrue, hi_new = hiTrue;
 
     // ---- NextsimPhysics::calculate :116-131 ----
-    double evap = P.drag_ocean_q * rho * wind * (sphumw - sphuma); // :133-137
+    const double rw = rho * wind;
+    double evap = P.drag_ocean_q * rw * (sphumw - sphuma); // :133-137
     double tau = rho * (1e-3 * fmax(1.0, fmin(2.0, 0.61 + 0.063 * wind))); // :139-142,291-295
     // heatFluxOpenWater :144-162
     double Qlhow = evap * latent_heat_water(sst);
-    double Qshow = P.drag_ocean_t * rho * cspec * wind * (sst - in.tair);
+    double Qshow = P.drag_ocean_t * rw * cspec * (sst - in.tair);
     double Qswow = -in.qsw * (1 - P.albedo_w);
     double Qlwow = stefan_boltzmann(sst) - in.qlw;
     double Qow = Qlhow + Qshow + Qlwow + Qswow;
     // massFluxIceAtmosphere :164-168
-    double subl = P.drag_ice_t * rho * wind * (sphumi - sphuma);
+    double subl = P.drag_ice_t * rw * (sphumi - sphuma);
     // heatFluxIceAtmosphere :170-198
     double lhi = latent_heat_ice(tice0);
     double Qlhi = subl * lhi;
@@ -127,38 +140,37 @@ __device__ __forceinline__ CellOut thermo_cell(
         const SphCoef& k = SPH_ICE;
         double df_dT = 2 * k.bigC * k.bigB * tice0;
         double numerator = k.b * k.c * k.d - tice0 * (2 * k.c + tice0);
-        double denominator = k.d * sq(k.c + tice0);
-        double dest_dT = numerator / denominator * estI;
-        numerator = SPH_ALPHA * slp * (fI * dest_dT + estI * df_dT);
-        denominator = sq(slp - SPH_BETA * estI * fI);
-        dq_dT = numerator / denominator;
+        double dest_dT = numerator * (sq(rtcI) * (1. / k.d)) * estI; // / (d (c + T)^2)
+        dq_dT = SPH_ALPHA * slp * (fI * dest_dT + estI * df_dT) * sq(rqI); // / (p - beta est f)^2
     }
-    double dmdot_dT = P.drag_ice_t * rho * wind * dq_dT;
-    double dQlh_dT = lhi * dmdot_dT;
-    double Qshi = P.drag_ice_t * rho * cspec * wind * (tice0 - in.tair);
-    double dQsh_dT = P.drag_ice_t * rho * cspec * wind;
+    const double dsh = P.drag_ice_t * rw * cspec;
+    double dQlh_dT = lhi * (P.drag_ice_t * rw * dq_dT);
+    double Qshi = dsh * (tice0 - in.tair);
+    double dQsh_dT = dsh;
     double albedoValue;
-    { // IIceAlbedo::albedo, argument as NextsimPhysics.cpp:185-186
-        const double hsArg = (cice > 0) ? (hsnow / cice) : 0.;
+    { // IIceAlbedo::albedo, argument as NextsimPhysics.cpp:185-186 (hsnow/cice if cice > 0 else 0)
+        const double hsArg = (cice > 0) ? hsTrue : 0.;
         const double ICE_ALBEDO = 0.64, SNOW_ALBEDO = 0.85;
         if (P.albedo_kind == NSDG_ALBEDO_CCSM) { // CCSMIceAlbedo.cpp:28-36
             double iceAlbedoT = P.ccsm_ice_albedo - fmax(0., 0.075 * (tice0 - (-1.)));
             double snowAlbedoT = P.ccsm_snow_albedo - fmax(0., 0.124 * (tice0 - (-1.)));
-            double snowCoverFraction = hsArg / (hsArg + 0.02);
+            double snowCoverFraction = hsArg * rcp_pos(hsArg + 0.02);
             albedoValue = snowCoverFraction * snowAlbedoT + (1 - snowCoverFraction) * iceAlbedoT;
         } else if (hsArg > 0.) {
             albedoValue = (P.albedo_kind == NSDG_ALBEDO_SMU) // SMUIceAlbedo.cpp:19-26
                 ? SNOW_ALBEDO
                 : fmin(SNOW_ALBEDO, // SMU2IceAlbedo.cpp:21-29
-                    ICE_ALBEDO + (SNOW_ALBEDO - ICE_ALBEDO) * hsArg / 0.2);
+                    ICE_ALBEDO + (SNOW_ALBEDO - ICE_ALBEDO) * hsArg * (1. / 0.2));
         } else {
             albedoValue = ICE_ALBEDO + 0.4 * (1 - ICE_ALBEDO) * P.i0;
         }
     }
     double Qswi = -in.qsw * (1. - P.i0) * (1 - albedoValue);
-    double sbI = stefan_boltzmann(tice0);
+    const double kI = kelvin(tice0);
+    const double sb3 = ICE_EPSILON * SIGMA_SB * kI * sq(kI);
+    double sbI = sb3 * kI;
     double Qlwi = sbI - in.qlw;
-    double dQlw_dT = 4 / kelvin(tice0) * sbI;
+    double dQlw_dT = 4 * sb3; // 4/T * eps sigma T^4
     double Qia = Qlhi + Qshi + Qlwi + Qswi;
     double dQ_dT = dQlh_dT + dQsh_dT + dQlw_dT;
     // heatFluxIceOcean :222-226 -> BasicIceOceanHeatFlux.cpp:16-25, ExternalData.hpp:60
@@ -169,7 +181,8 @@ __device__ __forceinline__ CellOut thermo_cell(
         tf = -WATER_MU * sss;
     }
     const double mlBulkCp = in.mld * WATER_RHOOCEAN * WATER_CP;
-    double Qio = (sst - tf) * mlBulkCp / dt;
+    const double Qio0 = (sst - tf) * mlBulkCp * idt;
+    double Qio = Qio0;
 
     // ---- massFluxIceOcean :200-220 ----
     double hifroms = 0;
@@ -183,31 +196,31 @@ __device__ __forceinline__ CellOut thermo_cell(
             hs_new = 0;
             t_new = freezingPointIce;
         } else {
-            double k_lSlab = P.ks * ICE_KAPPA / (P.ks * hiTrue + ICE_KAPPA * hsTrue);
+            double k_lSlab = P.ks * ICE_KAPPA * rcp_pos(P.ks * hiTrue + ICE_KAPPA * hsTrue);
             double QIceConduction = k_lSlab * (tf - tice0);
             double remainingFlux = QIceConduction - Qia;
-            t_new = tice0 + remainingFlux / (k_lSlab + dQ_dT);
+            t_new = tice0 + remainingFlux * rcp_pos(k_lSlab + dQ_dT);
             double meltingLimit = (hsTrue > 0.) ? 0 : freezingPointIce;
             t_new = fmin(meltingLimit, t_new);
-            double snowMeltRate = fmin(-remainingFlux, 0.) / bulkLHFusionSnow;
-            double snowSublRate = subl / ICE_RHOSNOW;
+            double snowMeltRate = fmin(-remainingFlux, 0.) * (1. / bulkLHFusionSnow);
+            double snowSublRate = subl * (1. / ICE_RHOSNOW);
             hs_new += (snowMeltRate - snowSublRate) * dt;
-            double excessIceMelt = fmin(hs_new, 0.) * bulkLHFusionSnow / bulkLHFusionIce;
+            double excessIceMelt = fmin(hs_new, 0.) * (bulkLHFusionSnow / bulkLHFusionIce);
             hs_new = fmax(hs_new, 0.);
-            hs_new += in.snowfall * dt / ICE_RHOSNOW;
-            double iceBottomChange = (QIceConduction - Qio) * dt / bulkLHFusionIce;
+            hs_new += in.snowfall * dt * (1. / ICE_RHOSNOW);
+            double iceBottomChange = (QIceConduction - Qio) * dt * (1. / bulkLHFusionIce);
             double iceThicknessChange = excessIceMelt + iceBottomChange;
             hi_new += iceThicknessChange;
-            double iceDraught = (hi_new * ICE_RHO + hs_new * ICE_RHOSNOW) / WATER_RHOOCEAN;
+            double iceDraught = (hi_new * ICE_RHO + hs_new * ICE_RHOSNOW) * (1. / WATER_RHOOCEAN);
             if (P.flooding && iceDraught > hi_new) { // :95-106
                 double newIce = iceDraught - hi_new;
                 hifroms += newIce;
                 hi_new = iceDraught;
-                hs_new -= newIce * ICE_RHO / ICE_RHOSNOW;
+                hs_new -= newIce * (ICE_RHO / ICE_RHOSNOW);
             }
             if (hi_new < P.min_thick) { // :108-132
                 hifroms = 0;
-                double deltaQio = hi_new * bulkLHFusionIce / dt + hs_new * bulkLHFusionSnow / dt;
+                double deltaQio = (hi_new * bulkLHFusionIce + hs_new * bulkLHFusionSnow) * idt;
                 Qio += deltaQio;
                 hi_new = 0;
                 hs_new = 0;
@@ -217,13 +230,15 @@ __device__ __forceinline__ CellOut thermo_cell(
     }
     { // newIceFormation :228-254
         double coolingFlux = Qow;
-        double deltaTml = -coolingFlux / mlBulkCp * dt;
+        double deltaTml = -coolingFlux * rcp_pos(mlBulkCp) * dt;
         double t1 = sst + deltaTml;
         if (t1 < tf) {
-            double sensibleFlux = (tf - sst) / deltaTml * coolingFlux;
+            // (tf - sst)/deltaTml * coolingFlux == (sst - tf) mlBulkCp / dt: the flux that takes
+            // the mixed layer exactly to the freezing point
+            double sensibleFlux = Qio0;
             double latentFlux = coolingFlux - sensibleFlux;
             Qow = sensibleFlux;
-            newice = latentFlux * dt * (1 - cice) / (ICE_LF * ICE_RHO);
+            newice = latentFlux * dt * (1 - cice) * (1. / (ICE_LF * ICE_RHO));
         }
     }
     double c_new;
@@ -233,22 +248,23 @@ __device__ __forceinline__ CellOut thermo_cell(
             double m = 0;
             if (!(cice >= 1)) {
                 double del_hi = hi_new - hiTrue;
-                m = del_hi * cice * P.phi_m / hiTrue;
+                m = del_hi * cice * P.phi_m * rcp_pos(hiTrue);
             }
             del_c += m;
         }
         c_new = cice + del_c;
         if (c_new >= P.min_conc) {
-            hi_new += (newice - hi_new * del_c) / (cice + del_c);
+            const double rc = rcp_pos(c_new);
+            hi_new += (newice - hi_new * del_c) * rc;
             if (del_c < 0) {
-                Qow -= del_c * hs_new * ICE_LF * ICE_RHOSNOW / dt;
+                Qow -= del_c * hs_new * ICE_LF * ICE_RHOSNOW * idt;
             } else {
-                hs_new += (0. - hs_new * del_c) / (cice + del_c);
+                hs_new += (0. - hs_new * del_c) * rc;
             }
         }
     }
     if (c_new < P.min_conc || hi_new < P.min_thick) { // NextsimPhysics.cpp:210-219
-        Qow += c_new * ICE_LF * (hi_new * ICE_RHO + hs_new * ICE_RHOSNOW) / dt;
+        Qow += c_new * ICE_LF * (hi_new * ICE_RHO + hs_new * ICE_RHOSNOW) * idt;
         c_new = 0;
         hi_new = 0;
         hs_new = 0;
@@ -283,57 +299,30 @@ struct ThermoPtrs {
     double* diag;
 };
 
-__device__ __forceinline__ double2 ldg2(const double* p, int64_t k2)
-{
-    return __ldg(reinterpret_cast<const double2*>(p) + k2);
-}
-
-// two cells per thread: every global access is a 16-byte vector, fully coalesced
+// one cell per thread: 15 coalesced 8-byte loads issued up front, 5 stores
 template <bool DIAG>
 __global__ void __launch_bounds__(256) thermo_kernel(const __grid_constant__ nsdg_thermo_params P,
-    const __grid_constant__ ThermoPtrs ptr, double dt, int64_t n)
+    const __grid_constant__ ThermoPtrs ptr, double dt, double idt, int64_t n)
 {
-    const int64_t npair = n >> 1;
-    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (int64_t k2 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k2 < npair; k2 += stride) {
-        double2 v[NSDG_TF_COUNT];
+    const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n)
+        return;
+    double v[NSDG_TF_COUNT];
 #pragma unroll
-        for (int q = 0; q < NSDG_TF_COUNT; ++q)
-            v[q] = ldg2(ptr.f[q], k2);
-        CellIn a = { v[0].x, v[1].x, v[2].x, v[3].x, v[4].x, v[5].x, v[6].x, v[7].x, v[8].x,
-            v[9].x, v[10].x, v[11].x, v[12].x, v[13].x, v[14].x };
-        CellIn b = { v[0].y, v[1].y, v[2].y, v[3].y, v[4].y, v[5].y, v[6].y, v[7].y, v[8].y,
-            v[9].y, v[10].y, v[11].y, v[12].y, v[13].y, v[14].y };
-        double da[NSDG_THERMO_NDIAG], db[NSDG_THERMO_NDIAG];
-        CellOut oa = thermo_cell<DIAG>(P, dt, a, da);
-        CellOut ob = thermo_cell<DIAG>(P, dt, b, db);
-        reinterpret_cast<double2*>(ptr.f[NSDG_TF_HICE])[k2] = make_double2(oa.hice, ob.hice);
-        reinterpret_cast<double2*>(ptr.f[NSDG_TF_CICE])[k2] = make_double2(oa.cice, ob.cice);
-        reinterpret_cast<double2*>(ptr.f[NSDG_TF_HSNOW])[k2] = make_double2(oa.hsnow, ob.hsnow);
-        reinterpret_cast<double2*>(ptr.f[NSDG_TF_TICE0])[k2] = make_double2(oa.tice0, ob.tice0);
-        reinterpret_cast<double2*>(ptr.f[NSDG_TF_NEWICE])[k2] = make_double2(oa.newice, ob.newice);
-        if (DIAG) {
+    for (int q = 0; q < NSDG_TF_COUNT; ++q)
+        v[q] = __ldg(ptr.f[q] + k);
+    const CellIn a = { v[0], v[1], v[2], v[3], v[4], v[5], v[6], v[7], v[8], v[9], v[10], v[11], v[12], v[13], v[14] };
+    double da[NSDG_THERMO_NDIAG];
+    const CellOut o = thermo_cell<DIAG>(P, dt, idt, a, da);
+    ptr.f[NSDG_TF_HICE][k] = o.hice;
+    ptr.f[NSDG_TF_CICE][k] = o.cice;
+    ptr.f[NSDG_TF_HSNOW][k] = o.hsnow;
+    ptr.f[NSDG_TF_TICE0][k] = o.tice0;
+    ptr.f[NSDG_TF_NEWICE][k] = o.newice;
+    if (DIAG) {
 #pragma unroll
-            for (int q = 0; q < NSDG_THERMO_NDIAG; ++q)
-                reinterpret_cast<double2*>(ptr.diag + (size_t)q * n)[k2] = make_double2(da[q], db[q]);
-        }
-    }
-    // odd tail cell
-    if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
-        const int64_t k = n - 1;
-        CellIn a = { ptr.f[0][k], ptr.f[1][k], ptr.f[2][k], ptr.f[3][k], ptr.f[4][k], ptr.f[5][k],
-            ptr.f[6][k], ptr.f[7][k], ptr.f[8][k], ptr.f[9][k], ptr.f[10][k], ptr.f[11][k],
-            ptr.f[12][k], ptr.f[13][k], ptr.f[14][k] };
-        double da[NSDG_THERMO_NDIAG];
-        CellOut oa = thermo_cell<DIAG>(P, dt, a, da);
-        ptr.f[NSDG_TF_HICE][k] = oa.hice;
-        ptr.f[NSDG_TF_CICE][k] = oa.cice;
-        ptr.f[NSDG_TF_HSNOW][k] = oa.hsnow;
-        ptr.f[NSDG_TF_TICE0][k] = oa.tice0;
-        ptr.f[NSDG_TF_NEWICE][k] = oa.newice;
-        if (DIAG)
-            for (int q = 0; q < NSDG_THERMO_NDIAG; ++q)
-                ptr.diag[(size_t)q * n + k] = da[q];
+        for (int q = 0; q < NSDG_THERMO_NDIAG; ++q)
+            ptr.diag[(size_t)q * n + k] = da[q];
     }
 }
 
@@ -368,15 +357,14 @@ int thermo_launch(nsdg_ctx* ctx, double dt, int nsteps, bool diag)
         p.f[q] = t->fields[q];
     p.diag = t->diag;
     const int block = 256;
-    int64_t npair = (t->n + 1) / 2;
-    int64_t want = (npair + block - 1) / block;
-    int64_t cap = (int64_t)ctx->sm_count * 16; // grid-stride beyond 16 CTAs/SM worth of work
-    int grid = (int)(want < cap ? (want > 0 ? want : 1) : cap);
+    NSDG_REQUIRE(ctx, (t->n + block - 1) / block < ((int64_t)1 << 31), NSDG_EINVAL, "too many cells for one launch");
+    const unsigned grid = (unsigned)((t->n + block - 1) / block);
+    const double idt = 1. / dt;
     for (int s = 0; s < nsteps; ++s) {
         if (diag && s == nsteps - 1)
-            NSDG_KERNEL(ctx, NSDG_K_THERMO, thermo_kernel<true><<<grid, block, 0, ctx->stream>>>(t->params, p, dt, t->n));
+            NSDG_KERNEL(ctx, NSDG_K_THERMO, thermo_kernel<true><<<grid, block, 0, ctx->stream>>>(t->params, p, dt, idt, t->n));
         else
-            NSDG_KERNEL(ctx, NSDG_K_THERMO, thermo_kernel<false><<<grid, block, 0, ctx->stream>>>(t->params, p, dt, t->n));
+            NSDG_KERNEL(ctx, NSDG_K_THERMO, thermo_kernel<false><<<grid, block, 0, ctx->stream>>>(t->params, p, dt, idt, t->n));
     }
     return NSDG_OK;
 }
