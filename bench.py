@@ -233,8 +233,11 @@ def run_gpu(args):
     if not np.isfinite(umax):
         raise SystemExit("bench.py: non-finite velocity after the timed steps")
 
-    # ---- e2e: host (pinned) buffers in and out through the C ABI every step
+    # ---- e2e: one C-ABI call per step with HOST (pinned) buffers, nsdg_dyn_step_host: this
+    # step's forcing goes up, the full prognostic state comes down, copies overlap the compute;
+    # the model state itself stays resident between steps (as DevStep's state stays in memory)
     names = ("H", "A", "U", "V", "S11", "S12", "S22", "UATM", "VATM", "UOCN", "VOCN")
+    forcing = ("UATM", "VATM", "UOCN", "VOCN")
     outs = ("H", "A", "U", "V", "S11", "S12", "S22")
     host = {}
     for k in names:
@@ -242,32 +245,28 @@ def run_gpu(args):
         tpin = torch.empty(a.shape, dtype=torch.float64).pin_memory()
         tpin.numpy()[...] = a
         host[k] = tpin
-    h2d = sum(host[k].numel() * 8 for k in names)
-    d2h = sum(host[k].numel() * 8 for k in outs)
-    import ctypes
-    from nextsimdg_b200._abi import DYN_FIELDS, c_double_p, check
 
-    def ptr(tn):
-        return ctypes.cast(tn.data_ptr(), c_double_p)
-
-    def e2e_step():
-        for k in names:
-            check(ctx.h, ctx.lib.nsdg_dyn_upload(ctx.h, DYN_FIELDS.index(k), ptr(host[k])))
-        check(ctx.h, ctx.lib.nsdg_dyn_step(ctx.h, DT, NSUB))
-        for k in outs:
-            check(ctx.h, ctx.lib.nsdg_dyn_download(ctx.h, DYN_FIELDS.index(k), ptr(host[k])))
+    def e2e_run(in_names, nsteps):
+        ins = {k: host[k].data_ptr() for k in in_names}
+        outp = {k: host[k].data_ptr() for k in outs}
+        dyn.step_host(DT, NSUB, ins, outp)  # untimed first call
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(nsteps):
+            dyn.step_host(DT, NSUB, ins, outp)
+        barrier()
+        te = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        return cells_total * nsteps / float(te.item())
 
     e2e_steps = max(1, min(args.steps, args.e2e_steps))
-    e2e_step()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        e2e_step()
-    barrier()
-    te = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(te, op=dist.ReduceOp.MAX)
-    e2e_value = cells_total * e2e_steps / float(te.item())
+    h2d = sum(host[k].numel() * 8 for k in forcing)
+    d2h = sum(host[k].numel() * 8 for k in outs)
+    e2e_value = e2e_run(forcing, e2e_steps)
+    # for transparency: the same call with the WHOLE state uploaded every step as well
+    h2d_full = sum(host[k].numel() * 8 for k in names)
+    e2e_full = e2e_run(names, 1)
 
     if rank == 0:
         peak, peak_src = peaks()
@@ -324,8 +323,13 @@ def run_gpu(args):
                 "config": workload_config(args, world), "clocks": clocks,
                 "e2e": {"value": e2e_value, "unit": "cell-updates/s", "h2d_bytes_per_step": h2d,
                         "d2h_bytes_per_step": d2h, "steps": e2e_steps,
-                        "what": "full state + forcing uploaded from pinned host memory, one "
-                                "nsdg_dyn_step, full state downloaded, every step"},
+                        "what": "nsdg_dyn_step_host per step: this step's forcing (wind, ocean "
+                                "current) uploaded from pinned host memory, full prognostic state "
+                                "(H, A, U, V, S) downloaded, copies overlapped with compute; the "
+                                "state stays resident between steps",
+                        "full_roundtrip": {"value": e2e_full, "h2d_bytes_per_step": h2d_full,
+                                           "d2h_bytes_per_step": d2h,
+                                           "what": "same call, whole state uploaded every step too"}},
                 "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu,
                 "max_abs_u": umax,
                 "halo_bytes_sent_per_rank": ctx.comm_bytes_sent if world > 1 else 0}

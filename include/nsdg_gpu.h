@@ -226,6 +226,16 @@ int nsdg_transport_step_HA(nsdg_ctx* ctx, double dt);
 int nsdg_mevp_step(nsdg_ctx* ctx, double dt, int32_t nsub);
 /* the north-star unit: transport of H,A with the current velocity, then the mEVP sub-cycle */
 int nsdg_dyn_step(nsdg_ctx* ctx, double dt, int32_t nsub);
+/* One model step with HOST buffers, copies overlapped with compute on separate streams:
+ *   in[f]  (f = nsdg_dyn_field, NSDG_DF_COUNT entries, NULL = keep the resident device copy):
+ *          U, V, H, A go up first and the transport starts as soon as they have arrived, while
+ *          the stress and the forcing are still in flight;
+ *   out[f] (NULL = not wanted): H and A come down while the mEVP sub-cycle runs, U, V and the
+ *          stress after it.
+ * Host layout as nsdg_dyn_upload/download.  Buffers should be page-locked (pinned) for the
+ * copies to be asynchronous.  Returns after everything has completed. */
+int nsdg_dyn_step_host(nsdg_ctx* ctx, double dt, int32_t nsub, const double* const* in,
+    double* const* out);
 /* sum over this rank's cells of the mean coefficient times cell area (mass diagnostic) */
 int nsdg_dyn_mass(nsdg_ctx* ctx, int32_t field, double* mass);
 

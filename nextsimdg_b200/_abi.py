@@ -104,6 +104,8 @@ SYMBOLS = {
     "nsdg_transport_step_HA": (ctypes.c_int, [_ctx, _dbl]),
     "nsdg_mevp_step": (ctypes.c_int, [_ctx, _dbl, _i32]),
     "nsdg_dyn_step": (ctypes.c_int, [_ctx, _dbl, _i32]),
+    "nsdg_dyn_step_host": (ctypes.c_int, [_ctx, _dbl, _i32, ctypes.POINTER(c_double_p),
+                                          ctypes.POINTER(c_double_p)]),
     "nsdg_dyn_mass": (ctypes.c_int, [_ctx, _i32, c_double_p]),
     "nsdg_comm_get_unique_id": (ctypes.c_int, [ctypes.c_void_p]),
     "nsdg_comm_init": (ctypes.c_int, [_ctx, ctypes.c_void_p, _i32, _i32]),

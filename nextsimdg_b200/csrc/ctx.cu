@@ -121,6 +121,12 @@ int nsdg_create(nsdg_ctx** out, int device)
     if (cudaSetDevice(device) != cudaSuccess
         || cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess
         || cudaStreamCreateWithFlags(&ctx->comm_stream, cudaStreamNonBlocking) != cudaSuccess
+        || cudaStreamCreateWithFlags(&ctx->h2d_stream, cudaStreamNonBlocking) != cudaSuccess
+        || cudaStreamCreateWithFlags(&ctx->d2h_stream, cudaStreamNonBlocking) != cudaSuccess
+        || cudaEventCreateWithFlags(&ctx->ev_pipe[0], cudaEventDisableTiming) != cudaSuccess
+        || cudaEventCreateWithFlags(&ctx->ev_pipe[1], cudaEventDisableTiming) != cudaSuccess
+        || cudaEventCreateWithFlags(&ctx->ev_pipe[2], cudaEventDisableTiming) != cudaSuccess
+        || cudaEventCreateWithFlags(&ctx->ev_pipe[3], cudaEventDisableTiming) != cudaSuccess
         || cudaEventCreate(&ctx->ev_start) != cudaSuccess
         || cudaEventCreate(&ctx->ev_stop) != cudaSuccess) {
         fprintf(stderr, "nsdg_create: %s\n", cudaGetErrorString(cudaGetLastError()));
@@ -151,6 +157,13 @@ int nsdg_destroy(nsdg_ctx* ctx)
         cudaStreamDestroy(ctx->stream);
     if (ctx->comm_stream)
         cudaStreamDestroy(ctx->comm_stream);
+    if (ctx->h2d_stream)
+        cudaStreamDestroy(ctx->h2d_stream);
+    if (ctx->d2h_stream)
+        cudaStreamDestroy(ctx->d2h_stream);
+    for (cudaEvent_t e : ctx->ev_pipe)
+        if (e)
+            cudaEventDestroy(e);
     delete ctx;
     return NSDG_OK;
 }

@@ -440,6 +440,66 @@ int nsdg_dyn_step(nsdg_ctx* ctx, double dt, int32_t nsub)
     return nsdg_mevp_step(ctx, dt, nsub);
 }
 
+int nsdg_dyn_step_host(nsdg_ctx* ctx, double dt, int32_t nsub, const double* const* in,
+    double* const* out)
+{
+    NSDG_ENTER(ctx);
+    DynState* d = ctx->dyn;
+    NSDG_REQUIRE(ctx, d, NSDG_ESTATE, "nsdg_dyn_init has not been called");
+    NSDG_REQUIRE(ctx, dt > 0 && nsub >= 0, NSDG_EINVAL, "dt > 0 and nsub >= 0 required");
+    const size_t inner = (size_t)d->nx * d->nyl;
+    auto copy = [&](int f, bool up, cudaStream_t st) -> cudaError_t {
+        for (int c = 0; c < d->ncomp[f]; ++c) {
+            double* dev = d->f[f] + (size_t)c * d->plane + NSDG_GHOST * d->nx;
+            cudaError_t e = up
+                ? cudaMemcpyAsync(dev, in[f] + c * inner, sizeof(double) * inner, cudaMemcpyHostToDevice, st)
+                : cudaMemcpyAsync(out[f] + c * inner, dev, sizeof(double) * inner, cudaMemcpyDeviceToHost, st);
+            if (e != cudaSuccess)
+                return e;
+        }
+        return cudaSuccess;
+    };
+    // ---- uploads: what the transport needs first
+    const int first[] = { NSDG_DF_U, NSDG_DF_V, NSDG_DF_H, NSDG_DF_A };
+    const int second[] = { NSDG_DF_S11, NSDG_DF_S12, NSDG_DF_S22, NSDG_DF_UATM, NSDG_DF_VATM, NSDG_DF_UOCN, NSDG_DF_VOCN };
+    if (in) {
+        for (int f : first)
+            if (in[f])
+                NSDG_CUDA(ctx, copy(f, true, ctx->h2d_stream));
+        NSDG_CUDA(ctx, cudaEventRecord(ctx->ev_pipe[0], ctx->h2d_stream));
+        for (int f : second)
+            if (in[f])
+                NSDG_CUDA(ctx, copy(f, true, ctx->h2d_stream));
+        NSDG_CUDA(ctx, cudaEventRecord(ctx->ev_pipe[1], ctx->h2d_stream));
+        NSDG_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_pipe[0], 0));
+    }
+    int rc = nsdg_transport_step_HA(ctx, dt);
+    if (rc)
+        return rc;
+    NSDG_CUDA(ctx, cudaEventRecord(ctx->ev_pipe[2], ctx->stream));
+    // ---- H, A are final after the transport: they come down while the sub-cycle runs
+    if (out) {
+        NSDG_CUDA(ctx, cudaStreamWaitEvent(ctx->d2h_stream, ctx->ev_pipe[2], 0));
+        for (int f : { NSDG_DF_H, NSDG_DF_A })
+            if (out[f])
+                NSDG_CUDA(ctx, copy(f, false, ctx->d2h_stream));
+    }
+    if (in)
+        NSDG_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_pipe[1], 0));
+    if ((rc = nsdg_mevp_step(ctx, dt, nsub)))
+        return rc;
+    NSDG_CUDA(ctx, cudaEventRecord(ctx->ev_pipe[3], ctx->stream));
+    if (out) {
+        NSDG_CUDA(ctx, cudaStreamWaitEvent(ctx->d2h_stream, ctx->ev_pipe[3], 0));
+        for (int f : { NSDG_DF_U, NSDG_DF_V, NSDG_DF_S11, NSDG_DF_S12, NSDG_DF_S22 })
+            if (out[f]) // d->f[] already points at the buffers that hold the new state
+                NSDG_CUDA(ctx, copy(f, false, ctx->d2h_stream));
+        NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->d2h_stream));
+    }
+    NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return NSDG_OK;
+}
+
 int nsdg_dyn_mass(nsdg_ctx* ctx, int32_t field, double* mass)
 {
     NSDG_ENTER(ctx);

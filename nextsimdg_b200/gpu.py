@@ -238,6 +238,30 @@ class GpuDynamics:
     def step(self, dt, nsub=100):
         check(self.h, self.lib.nsdg_dyn_step(self.h, float(dt), int(nsub)))
 
+    def step_host(self, dt, nsub, inputs=None, outputs=None):
+        """One step with host buffers (nsdg_dyn_step_host): `inputs` maps field names to arrays
+        (or raw addresses of pinned buffers) uploaded for this step, `outputs` maps field names
+        to writable buffers; copies overlap the compute.  Missing names stay resident / are
+        not downloaded."""
+        def table(m, writable):
+            t = (c_double_p * len(DYN_FIELDS))()
+            keep = []
+            for k, a in (m or {}).items():
+                if isinstance(a, int):
+                    t[DYN_FIELDS.index(k)] = ctypes.cast(a, c_double_p)
+                    continue
+                if a.dtype != np.float64 or not a.flags.c_contiguous or a.size != int(np.prod(self.field_shape(k))):
+                    raise ValueError(f"{k}: need a contiguous float64 array of shape {self.field_shape(k)}")
+                if writable and not a.flags.writeable:
+                    raise ValueError(f"{k}: output buffer is read-only")
+                keep.append(a)
+                t[DYN_FIELDS.index(k)] = _p(a)
+            return t, keep
+        tin, k1 = table(inputs, False)
+        tout, k2 = table(outputs, True)
+        check(self.h, self.lib.nsdg_dyn_step_host(self.h, float(dt), int(nsub),
+                                                  tin if inputs else None, tout if outputs else None))
+
     def mass(self, name):
         m = ctypes.c_double()
         check(self.h, self.lib.nsdg_dyn_mass(self.h, DYN_FIELDS.index(name), ctypes.byref(m)))

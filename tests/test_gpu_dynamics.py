@@ -159,6 +159,30 @@ def test_north_star_step_box_100_substeps(ctx):
     assert 1e-4 < np.abs(st[2]).max() < 0.1  # the ice actually moves
 
 
+def test_step_host_equals_resident_path(ctx):
+    """nsdg_dyn_step_host (host buffers, copies overlapped with compute) == upload, step, download."""
+    nx, ny = 96, 40
+    F, hx, hy = S.box_case(nx, ny, 6)
+    F["U"], F["V"] = random_velocity(nx, ny, 3, 0.05)
+    mp = MevpParams.defaults()
+    mp.bc = BC_PERIODIC
+    a = GpuDynamics(ctx, nx, ny, hx, hy, 6, mevp=mp)
+    a.upload_all(F)
+    a.step(120.0, 9)
+    a.step(120.0, 9)
+    names = ("H", "A", "U", "V", "S11", "S12", "S22")
+    ref = {k: a.download(k) for k in names}
+    b = GpuDynamics(ctx, nx, ny, hx, hy, 6, mevp=mp)
+    out = {k: np.empty(b.field_shape(k)) for k in names}
+    b.step_host(120.0, 9, {k: np.ascontiguousarray(v, dtype=np.float64) for k, v in F.items()}, out)
+    # second step: state stays resident, only the forcing goes up again
+    b.step_host(120.0, 9, {k: np.ascontiguousarray(F[k]) for k in ("UATM", "VATM", "UOCN", "VOCN")}, out)
+    for k in names:
+        assert np.array_equal(out[k], ref[k]), k
+    with pytest.raises(ValueError):
+        b.step_host(120.0, 1, {"H": np.zeros((3, 3))}, None)
+
+
 def test_size_independent_properties_large_grid(ctx):
     """2048^2 dG2 (too large for the oracle in seconds): constants are preserved, mass is
     conserved to round-off, zero forcing keeps a state of rest."""
