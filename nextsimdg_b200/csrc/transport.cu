@@ -6,12 +6,14 @@
 // One thread owns one cell and gathers everything it needs (no atomics, deterministic):
 //   volume term + the four edge upwind fluxes + inverse mass + the RK stage combination
 //     dst = a*base + b*(src + dt*L(src))
-// for NF tracers that share the velocity reads.  Each thread computes both fluxes of its own
+// for one tracer (blockIdx.z selects it).  Each thread computes both fluxes of its own
 // edges (the neighbour recomputes the shared one): 2x redundant flops, zero extra DRAM bytes.
 // Coefficients are component-major planes, so every load below is a fully coalesced stream;
 // the +-1 neighbours in x and y hit L1/L2 (counting rule of SURVEY.md 8d: neighbour re-reads
-// are free).  Algorithmic bytes per cell per stage: (NC src + NC base + NC dst)*NF*8 + 2*8.
+// are free).  Algorithmic bytes per cell per stage: (NC src + NC base + NC dst)*NF*8 + 2*8
+// (the velocity reads of the second tracer's CTAs hit L2).
 #include "dyn.h"
+#include <cstdlib>
 
 namespace {
 
@@ -62,7 +64,7 @@ template <int NC> __device__ __forceinline__ void add_psi(double (&r)[NC], doubl
     }
 }
 
-template <int NC> __device__ __forceinline__ void load_cell(double (&c)[NC], const double* p, int64_t plane, int64_t k)
+template <int NC> __device__ __forceinline__ void load_cell(double (&c)[NC], const double* p, int plane, int k)
 {
 #pragma unroll
     for (int q = 0; q < NC; ++q)
@@ -76,56 +78,51 @@ struct StageArgs {
     const double* u;
     const double* v;
     double a, b, dt, ihx, ihy;
-    int64_t nx, nyl, plane, r0, r1;
+    int nx, nyl, plane, r0, r1;
     int wrap;
 };
 
-template <int NC, int NF, bool HAS_BASE>
-__global__ void __launch_bounds__(256) transport_stage_kernel(const __grid_constant__ StageArgs A)
+// one tracer per blockIdx.z (the velocity reads of the second tracer hit L2): half the registers
+// of a two-tracer thread, so three CTAs instead of one fit an SM
+template <int NC, bool HAS_BASE, int MINB>
+__global__ void __launch_bounds__(256, MINB) transport_stage_kernel(const __grid_constant__ StageArgs A)
 {
     constexpr int NQ = (NC == 1) ? 1 : (NC == 3 ? 2 : 3);
     using G = Gauss<NQ>;
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const int64_t r = A.r0 + (int64_t)blockIdx.y * blockDim.y + threadIdx.y;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int r = A.r0 + blockIdx.y * blockDim.y + threadIdx.y;
     if (i >= A.nx || r >= A.r1)
         return;
-    int64_t rm = r - 1, rp = r + 1;
+    int rm = r - 1, rp = r + 1;
     if (A.wrap) { // interior rows are [NSDG_GHOST, NSDG_GHOST + nyl)
         if (rm < NSDG_GHOST)
             rm += A.nyl;
         if (rp >= NSDG_GHOST + A.nyl)
             rp -= A.nyl;
     }
-    const int64_t im = (i == 0) ? A.nx - 1 : i - 1;
-    const int64_t ip = (i == A.nx - 1) ? 0 : i + 1;
-    const int64_t k = r * A.nx + i;
+    const int im = (i == 0) ? A.nx - 1 : i - 1;
+    const int ip = (i == A.nx - 1) ? 0 : i + 1;
+    const int k = r * A.nx + i;
+    const int f = blockIdx.z;
 
     const double u00 = __ldg(A.u + r * A.nx + i), u10 = __ldg(A.u + r * A.nx + ip);
     const double u01 = __ldg(A.u + rp * A.nx + i), u11 = __ldg(A.u + rp * A.nx + ip);
     const double v00 = __ldg(A.v + r * A.nx + i), v10 = __ldg(A.v + r * A.nx + ip);
     const double v01 = __ldg(A.v + rp * A.nx + i), v11 = __ldg(A.v + rp * A.nx + ip);
 
-    // edge-normal velocities at the edge Gauss points, split into outflow/inflow parts
-    double uLp[NQ], uLm[NQ], uRp[NQ], uRm[NQ], vBp[NQ], vBm[NQ], vTp[NQ], vTm[NQ];
+    // edge-normal velocities (times weight / cell size) at the edge Gauss points; the upwind
+    // trace is selected by their sign: max(vn,0)*minus + min(vn,0)*plus == vn*(vn > 0 ? minus : plus)
+    double uL[NQ], uR[NQ], vB[NQ], vT[NQ];
 #pragma unroll
     for (int g = 0; g < NQ; ++g) {
         const double s = G::x(g), w = G::w(g);
-        double uL = (u00 * (1 - s) + u01 * s) * A.ihx * w;
-        double uR = (u10 * (1 - s) + u11 * s) * A.ihx * w;
-        double vB = (v00 * (1 - s) + v10 * s) * A.ihy * w;
-        double vT = (v01 * (1 - s) + v11 * s) * A.ihy * w;
-        uLp[g] = fmax(uL, 0.);
-        uLm[g] = fmin(uL, 0.);
-        uRp[g] = fmax(uR, 0.);
-        uRm[g] = fmin(uR, 0.);
-        vBp[g] = fmax(vB, 0.);
-        vBm[g] = fmin(vB, 0.);
-        vTp[g] = fmax(vT, 0.);
-        vTm[g] = fmin(vT, 0.);
+        uL[g] = (u00 * (1 - s) + u01 * s) * A.ihx * w;
+        uR[g] = (u10 * (1 - s) + u11 * s) * A.ihx * w;
+        vB[g] = (v00 * (1 - s) + v10 * s) * A.ihy * w;
+        vT[g] = (v01 * (1 - s) + v11 * s) * A.ihy * w;
     }
 
-#pragma unroll
-    for (int f = 0; f < NF; ++f) {
+    {
         double c[NC], cn[NC], rr[NC];
         load_cell<NC>(c, A.src[f], A.plane, k);
 #pragma unroll
@@ -156,7 +153,7 @@ __global__ void __launch_bounds__(256) transport_stage_kernel(const __grid_const
 #pragma unroll
         for (int g = 0; g < NQ; ++g) {
             const double s = G::x(g);
-            double F = uLp[g] * eval<NC>(cn, 1., s) + uLm[g] * eval<NC>(c, 0., s);
+            double F = uL[g] * (uL[g] > 0. ? eval<NC>(cn, 1., s) : eval<NC>(c, 0., s));
             add_psi<NC>(rr, F, 0., s);
         }
         // right edge (xi = 1)
@@ -164,7 +161,7 @@ __global__ void __launch_bounds__(256) transport_stage_kernel(const __grid_const
 #pragma unroll
         for (int g = 0; g < NQ; ++g) {
             const double s = G::x(g);
-            double F = uRp[g] * eval<NC>(c, 1., s) + uRm[g] * eval<NC>(cn, 0., s);
+            double F = uR[g] * (uR[g] > 0. ? eval<NC>(c, 1., s) : eval<NC>(cn, 0., s));
             add_psi<NC>(rr, -F, 1., s);
         }
         // bottom edge (eta = 0)
@@ -172,7 +169,7 @@ __global__ void __launch_bounds__(256) transport_stage_kernel(const __grid_const
 #pragma unroll
         for (int g = 0; g < NQ; ++g) {
             const double s = G::x(g);
-            double F = vBp[g] * eval<NC>(cn, s, 1.) + vBm[g] * eval<NC>(c, s, 0.);
+            double F = vB[g] * (vB[g] > 0. ? eval<NC>(cn, s, 1.) : eval<NC>(c, s, 0.));
             add_psi<NC>(rr, F, s, 0.);
         }
         // top edge (eta = 1)
@@ -180,7 +177,7 @@ __global__ void __launch_bounds__(256) transport_stage_kernel(const __grid_const
 #pragma unroll
         for (int g = 0; g < NQ; ++g) {
             const double s = G::x(g);
-            double F = vTp[g] * eval<NC>(c, s, 1.) + vTm[g] * eval<NC>(cn, s, 0.);
+            double F = vT[g] * (vT[g] > 0. ? eval<NC>(c, s, 1.) : eval<NC>(cn, s, 0.));
             add_psi<NC>(rr, -F, s, 1.);
         }
         constexpr double IM[6] = { 1., 12., 12., 180., 180., 144. };
@@ -228,13 +225,13 @@ __global__ void limit_kernel(double* phi, int64_t nx, int64_t nyl, int64_t plane
     }
 }
 
-template <int NC, int NF>
+template <int NC, int MINB>
 void launch_stage(const StageArgs& A, bool has_base, dim3 grid, dim3 block, cudaStream_t s)
 {
     if (has_base)
-        transport_stage_kernel<NC, NF, true><<<grid, block, 0, s>>>(A);
+        transport_stage_kernel<NC, true, MINB><<<grid, block, 0, s>>>(A);
     else
-        transport_stage_kernel<NC, NF, false><<<grid, block, 0, s>>>(A);
+        transport_stage_kernel<NC, false, MINB><<<grid, block, 0, s>>>(A);
 }
 
 } // namespace
@@ -258,32 +255,31 @@ int nsdg_transport_stage(nsdg_ctx* ctx, int nfields, double* const* src, double*
     A.dt = dt;
     A.ihx = 1. / d->cfg.hx;
     A.ihy = 1. / d->cfg.hy;
-    A.nx = d->nx;
-    A.nyl = d->nyl;
-    A.plane = d->plane;
-    A.r0 = r0;
-    A.r1 = r1;
+    A.nx = (int)d->nx;
+    A.nyl = (int)d->nyl;
+    A.plane = (int)d->plane;
+    A.r0 = (int)r0;
+    A.r1 = (int)r1;
     A.wrap = d->wrap ? 1 : 0;
     dim3 block(64, 4);
-    dim3 grid((unsigned)((d->nx + 63) / 64), (unsigned)((r1 - r0 + 3) / 4));
+    dim3 grid((unsigned)((d->nx + 63) / 64), (unsigned)((r1 - r0 + 3) / 4), (unsigned)nfields);
     const bool hb = base != nullptr;
     nsdg_prof_begin(ctx, NSDG_K_TRANSPORT);
-    if (d->nc == 1) {
-        if (nfields == 1)
-            launch_stage<1, 1>(A, hb, grid, block, ctx->stream);
-        else
-            launch_stage<1, 2>(A, hb, grid, block, ctx->stream);
-    } else if (d->nc == 3) {
-        if (nfields == 1)
-            launch_stage<3, 1>(A, hb, grid, block, ctx->stream);
-        else
-            launch_stage<3, 2>(A, hb, grid, block, ctx->stream);
-    } else {
-        if (nfields == 1)
-            launch_stage<6, 1>(A, hb, grid, block, ctx->stream);
-        else
-            launch_stage<6, 2>(A, hb, grid, block, ctx->stream);
+    static int minb = 0; // NSDG_TRANSPORT_MINB: resident-CTA target of the dG2 register budget (tuning)
+    if (!minb) {
+        const char* e = getenv("NSDG_TRANSPORT_MINB");
+        minb = e ? atoi(e) : 2;
     }
+    if (d->nc == 1)
+        launch_stage<1, 4>(A, hb, grid, block, ctx->stream);
+    else if (d->nc == 3)
+        launch_stage<3, 4>(A, hb, grid, block, ctx->stream);
+    else if (minb == 1)
+        launch_stage<6, 1>(A, hb, grid, block, ctx->stream);
+    else if (minb == 3)
+        launch_stage<6, 3>(A, hb, grid, block, ctx->stream);
+    else
+        launch_stage<6, 2>(A, hb, grid, block, ctx->stream);
     nsdg_prof_end(ctx);
     NSDG_LAUNCHED(ctx);
     return NSDG_OK;
