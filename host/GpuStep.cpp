@@ -34,16 +34,20 @@ template <> const std::map<int, std::string> Configured<GpuStepConfig>::keyMap =
 
 GpuStep::GpuStep(int device)
     : pStructure(nullptr)
+    , device(device)
     , ctx(nullptr)
     , n(0)
     , nLayers(1)
     , dirty(false)
 {
     nsdg_thermo_default_params(&params);
-    int rc = nsdg_create(&ctx, device);
-    if (rc != NSDG_OK)
-        throw std::runtime_error("GpuStep: no CUDA device (nsdg_create failed); there is no CPU "
-                                 "fallback - use DevStep");
+}
+
+void GpuStep::setDevice(int dev)
+{
+    if (ctx)
+        throw std::logic_error("GpuStep::setDevice after setInitialData");
+    device = dev;
 }
 
 GpuStep::~GpuStep()
@@ -105,6 +109,11 @@ nsdg_thermo_params GpuStep::queryConfiguration()
 
 void GpuStep::setInitialData(IStructure& dataStructure)
 {
+    if (!ctx && nsdg_create(&ctx, device) != NSDG_OK) {
+        ctx = nullptr;
+        throw std::runtime_error("GpuStep: no CUDA device (nsdg_create failed); there is no CPU "
+                                 "fallback - select Nextsim::DevStep");
+    }
     pStructure = &dataStructure;
     params = queryConfiguration();
 

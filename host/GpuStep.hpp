@@ -26,7 +26,11 @@ namespace Nextsim {
 
 class GpuStep : public IModelStep {
 public:
+    //! Trivial: the CUDA context is created by setInitialData, so that the reference's
+    //! ModuleLoader can hold a static instance next to DevStep on a box without a GPU.
     explicit GpuStep(int device = 0);
+    //! Selects the CUDA device; only before setInitialData.
+    void setDevice(int device);
     virtual ~GpuStep();
     GpuStep(const GpuStep&) = delete;
     GpuStep& operator=(const GpuStep&) = delete;
@@ -53,6 +57,7 @@ private:
     static nsdg_thermo_params queryConfiguration();
 
     IStructure* pStructure;
+    int device;
     nsdg_ctx* ctx;
     nsdg_thermo_params params;
     size_t n;

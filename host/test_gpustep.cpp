@@ -161,6 +161,50 @@ int main(int argc, char** argv)
             ++failures;
         gpuStep.writeRestartFile("/tmp/gpustep_restart.txt");
     }
+    // ---- the step chosen like every other plug-in: [Modules] Nextsim::IModelStep = Nextsim::GpuStep
+    {
+        Configurator::clear();
+        Configurator::addStream(std::unique_ptr<std::istream>(
+            new std::stringstream("[Modules]\nNextsim::IModelStep = Nextsim::GpuStep\n")));
+        ModuleLoader::getLoader().setAllDefaults();
+        IModelStep& dflt = ModuleLoader::getLoader().getImplementation<IModelStep>();
+        if (!dynamic_cast<DevStep*>(&dflt)) {
+            printf("default IModelStep is not DevStep\n");
+            ++failures;
+        }
+        ConfiguredModule::parseConfigurator();
+        {
+            ElementData probe;
+            probe.configure();
+        }
+        IModelStep& chosen = ModuleLoader::getLoader().getImplementation<IModelStep>();
+        if (!dynamic_cast<GpuStep*>(&chosen)) {
+            printf("[Modules] did not select GpuStep\n");
+            ++failures;
+        }
+        size_t m = n < 5000 ? n : 5000;
+        VectorGrid cpuGrid(m, layers), gpuGrid(m, layers);
+        fill(cpuGrid, layers, false);
+        fill(gpuGrid, layers, false);
+        DevStep cpuStep;
+        cpuStep.setInitialData(cpuGrid);
+        Iterator cpuIt(&cpuStep);
+        cpuIt.setStartStopStep(0, dt, dt);
+        cpuIt.run();
+        chosen.setInitialData(gpuGrid);
+        Iterator gpuIt(&chosen);
+        gpuIt.setStartStopStep(0, dt, dt);
+        gpuIt.run();
+        size_t bad = 0;
+        for (size_t k = 0; k < m; ++k) {
+            double a = cpuGrid.data[k].iceThickness(), b = gpuGrid.data[k].iceThickness();
+            if (std::fabs(a - b) > 1e-10 * std::fmax(std::fabs(a), 1e-3))
+                ++bad;
+        }
+        printf("module-loader selected step: cells=%zu out_of_tolerance=%zu\n", m, bad);
+        if (bad)
+            ++failures;
+    }
     printf(failures ? "FAIL\n" : "PASS\n");
     return failures ? 1 : 0;
 }
