@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define NSDG_ABI_VERSION 1
+#define NSDG_ABI_VERSION 2
 
 typedef struct nsdg_ctx nsdg_ctx;
 
@@ -187,6 +187,19 @@ int nsdg_thermo_upload_prognostic(nsdg_ctx* ctx, const double* hice, const doubl
 int nsdg_thermo_upload_forcing(nsdg_ctx* ctx, const double* tair, const double* tdew,
     const double* slp, const double* qsw, const double* qlw, const double* mld,
     const double* snowfall, const double* wind);
+/* Forcing ingestion with time interpolation on the device (replaces the
+ * constant fill of core/src/include/DummyExternalData.hpp:22-34): two time levels of the 8
+ * forcing streams stay resident, nsdg_thermo_blend_forcing sets the active forcing to
+ * f0 + w (f1 - f0), 0 <= w <= 1, without touching the host. */
+int nsdg_thermo_upload_forcing_level(nsdg_ctx* ctx, int32_t level, const double* tair,
+    const double* tdew, const double* slp, const double* qsw, const double* qlw,
+    const double* mld, const double* snowfall, const double* wind);
+int nsdg_thermo_blend_forcing(nsdg_ctx* ctx, double w);
+/* Slab-ocean closure, off by default = the reference's behaviour, which
+ * computes Qow and Qio and drops them (core/src/PrognosticData.cpp:63-71, quirk Q5).  When on,
+ * every sweep also integrates them into the mixed layer:
+ *   sst <- sst - dt ((1 - cice) Qow + cice Qio) / (mld rho_ocean c_p),  cice before the sweep. */
+int nsdg_thermo_set_slab_ocean(nsdg_ctx* ctx, int32_t enable);
 /* newice is zeroed by init; these two exist for checkpoint/resume of the hidden state */
 int nsdg_thermo_upload_newice(nsdg_ctx* ctx, const double* newice);
 int nsdg_thermo_download_newice(nsdg_ctx* ctx, double* newice);
@@ -236,6 +249,11 @@ int nsdg_dyn_step(nsdg_ctx* ctx, double dt, int32_t nsub);
  * copies to be asynchronous.  Returns after everything has completed. */
 int nsdg_dyn_step_host(nsdg_ctx* ctx, double dt, int32_t nsub, const double* const* in,
     double* const* out);
+/* forcing ingestion for the dynamics: two resident time levels of (UATM, VATM, UOCN, VOCN),
+ * host layout [ny_local][nx] each; blend sets the active forcing to f0 + w (f1 - f0) */
+int nsdg_dyn_upload_forcing_level(nsdg_ctx* ctx, int32_t level, const double* uatm,
+    const double* vatm, const double* uocn, const double* vocn);
+int nsdg_dyn_blend_forcing(nsdg_ctx* ctx, double w);
 /* sum over this rank's cells of the mean coefficient times cell area (mass diagnostic) */
 int nsdg_dyn_mass(nsdg_ctx* ctx, int32_t field, double* mass);
 

@@ -85,6 +85,9 @@ SYMBOLS = {
     "nsdg_thermo_set_params": (ctypes.c_int, [_ctx, ctypes.POINTER(ThermoParams)]),
     "nsdg_thermo_upload_prognostic": (ctypes.c_int, [_ctx] + [c_double_p] * 6),
     "nsdg_thermo_upload_forcing": (ctypes.c_int, [_ctx] + [c_double_p] * 8),
+    "nsdg_thermo_upload_forcing_level": (ctypes.c_int, [_ctx, _i32] + [c_double_p] * 8),
+    "nsdg_thermo_blend_forcing": (ctypes.c_int, [_ctx, _dbl]),
+    "nsdg_thermo_set_slab_ocean": (ctypes.c_int, [_ctx, _i32]),
     "nsdg_thermo_upload_newice": (ctypes.c_int, [_ctx, c_double_p]),
     "nsdg_thermo_download_newice": (ctypes.c_int, [_ctx, c_double_p]),
     "nsdg_thermo_step": (ctypes.c_int, [_ctx, _dbl, _i32]),
@@ -106,6 +109,8 @@ SYMBOLS = {
     "nsdg_dyn_step": (ctypes.c_int, [_ctx, _dbl, _i32]),
     "nsdg_dyn_step_host": (ctypes.c_int, [_ctx, _dbl, _i32, ctypes.POINTER(c_double_p),
                                           ctypes.POINTER(c_double_p)]),
+    "nsdg_dyn_upload_forcing_level": (ctypes.c_int, [_ctx, _i32] + [c_double_p] * 4),
+    "nsdg_dyn_blend_forcing": (ctypes.c_int, [_ctx, _dbl]),
     "nsdg_dyn_mass": (ctypes.c_int, [_ctx, _i32, c_double_p]),
     "nsdg_comm_get_unique_id": (ctypes.c_int, [ctypes.c_void_p]),
     "nsdg_comm_init": (ctypes.c_int, [_ctx, ctypes.c_void_p, _i32, _i32]),

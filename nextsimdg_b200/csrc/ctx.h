@@ -18,6 +18,9 @@ struct ThermoState {
     double* stage = nullptr; // device staging for tice upload/download [n*nlayers]
     nsdg_thermo_params params;
     bool have_prog = false, have_forcing = false;
+    double* level[2] = {}; // forcing time levels, [8][n] each, allocated on first use
+    bool have_level[2] = { false, false };
+    bool slab_ocean = false;
 };
 
 // kernel classes for the per-launch event profiler (nsdg_profile_*)
@@ -33,6 +36,7 @@ enum NsdgKernelId {
     NSDG_K_MEVP_PAIR,
     NSDG_K_PACK,
     NSDG_K_UNPACK,
+    NSDG_K_BLEND,
     NSDG_K_OTHER,
     NSDG_K_COUNT
 };

@@ -52,6 +52,21 @@ __global__ void mass_kernel(const double* mean, int64_t nx, int64_t nyl, double*
     }
 }
 
+// interior rows of 4 node planes: out[q] = f0[q] + w (f1[q] - f0[q])   (blockIdx.z = q)
+struct Blend4 {
+    double* out[4];
+};
+__global__ void dyn_blend_kernel(const __grid_constant__ Blend4 o, const double* f0, const double* f1, double w,
+    int64_t nx, int64_t nyl, int64_t plane)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nx || (int64_t)blockIdx.y >= nyl)
+        return;
+    const int64_t k = (NSDG_GHOST + (int64_t)blockIdx.y) * nx + i;
+    const double a = f0[blockIdx.z * plane + k];
+    o.out[blockIdx.z][k] = a + w * (f1[blockIdx.z * plane + k] - a);
+}
+
 PlaneSet planes_of(DynState* d, double* base, int ncomp)
 {
     PlaneSet ps;
@@ -244,7 +259,7 @@ void nsdg_dyn_free(nsdg_ctx* ctx)
     }
     for (int q = 0; q < 3; ++q)
         cudaFree(d->s2[q]);
-    double* w[] = { d->pg, d->nd, d->u2, d->v2, d->scratch,
+    double* w[] = { d->pg, d->nd, d->u2, d->v2, d->scratch, d->flevel[0], d->flevel[1],
         d->send_lo, d->send_hi, d->recv_lo, d->recv_hi };
     for (double* p : w)
         cudaFree(p);
@@ -497,6 +512,40 @@ int nsdg_dyn_step_host(nsdg_ctx* ctx, double dt, int32_t nsub, const double* con
         NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->d2h_stream));
     }
     NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return NSDG_OK;
+}
+
+int nsdg_dyn_upload_forcing_level(nsdg_ctx* ctx, int32_t level, const double* uatm,
+    const double* vatm, const double* uocn, const double* vocn)
+{
+    NSDG_ENTER(ctx);
+    DynState* d = ctx->dyn;
+    NSDG_REQUIRE(ctx, d, NSDG_ESTATE, "nsdg_dyn_init has not been called");
+    NSDG_REQUIRE(ctx, level == 0 || level == 1, NSDG_EINVAL, "forcing level must be 0 or 1");
+    NSDG_REQUIRE(ctx, uatm && vatm && uocn && vocn, NSDG_EINVAL, "null forcing array");
+    int rc;
+    if (!d->flevel[level] && (rc = alloc_planes(ctx, &d->flevel[level], 4)))
+        return rc;
+    const double* src[4] = { uatm, vatm, uocn, vocn };
+    const size_t inner = (size_t)d->nx * d->nyl;
+    for (int q = 0; q < 4; ++q)
+        NSDG_CUDA(ctx, cudaMemcpyAsync(d->flevel[level] + (size_t)q * d->plane + NSDG_GHOST * d->nx, src[q],
+                           sizeof(double) * inner, cudaMemcpyHostToDevice, ctx->stream));
+    NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    d->have_flevel[level] = true;
+    return NSDG_OK;
+}
+
+int nsdg_dyn_blend_forcing(nsdg_ctx* ctx, double w)
+{
+    NSDG_ENTER(ctx);
+    DynState* d = ctx->dyn;
+    NSDG_REQUIRE(ctx, d, NSDG_ESTATE, "nsdg_dyn_init has not been called");
+    NSDG_REQUIRE(ctx, d->have_flevel[0] && d->have_flevel[1], NSDG_ESTATE, "both forcing levels must be uploaded first");
+    NSDG_REQUIRE(ctx, w >= 0. && w <= 1., NSDG_EINVAL, "interpolation weight %g outside [0,1]", w);
+    Blend4 o = { { d->f[NSDG_DF_UATM], d->f[NSDG_DF_VATM], d->f[NSDG_DF_UOCN], d->f[NSDG_DF_VOCN] } };
+    dim3 block(256), grid((unsigned)((d->nx + 255) / 256), (unsigned)d->nyl, 4);
+    NSDG_KERNEL(ctx, NSDG_K_BLEND, dyn_blend_kernel<<<grid, block, 0, ctx->stream>>>(o, d->flevel[0], d->flevel[1], w, d->nx, d->nyl, d->plane));
     return NSDG_OK;
 }
 

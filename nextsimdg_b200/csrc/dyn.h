@@ -30,6 +30,8 @@ struct DynState {
     double* s2[3] = {}; // ping-pong partners of S11, S12, S22 (fused sub-iteration)
     double* u2 = nullptr; // ping-pong partner of U,V
     double* v2 = nullptr;
+    double* flevel[2] = {}; // forcing time levels: 4 planes each (UATM, VATM, UOCN, VOCN)
+    bool have_flevel[2] = { false, false };
     double* scratch = nullptr; // reductions
     double* host_stage = nullptr; // pinned staging for upload/download
     size_t host_stage_bytes = 0;

@@ -86,6 +86,7 @@ struct CellIn {
 };
 struct CellOut {
     double hice, cice, hsnow, tice0, newice;
+    double sst; // only meaningful with the slab-ocean closure
 };
 
 // idt = 1/dt
@@ -291,6 +292,8 @@ __device__ __forceinline__ CellOut thermo_cell(
     o.hsnow = hs_new * c_new;
     o.tice0 = t_new;
     o.newice = newice;
+    // slab-ocean closure (opt-in): the two fluxes the reference drops
+    o.sst = sst - dt * ((1 - cice) * Qow + cice * Qio) * rcp_pos(mlBulkCp);
     return o;
 }
 
@@ -300,7 +303,7 @@ struct ThermoPtrs {
 };
 
 // one cell per thread: 15 coalesced 8-byte loads issued up front, 5 stores
-template <bool DIAG>
+template <bool DIAG, bool SLAB>
 __global__ void __launch_bounds__(256) thermo_kernel(const __grid_constant__ nsdg_thermo_params P,
     const __grid_constant__ ThermoPtrs ptr, double dt, double idt, int64_t n)
 {
@@ -319,6 +322,8 @@ __global__ void __launch_bounds__(256) thermo_kernel(const __grid_constant__ nsd
     ptr.f[NSDG_TF_HSNOW][k] = o.hsnow;
     ptr.f[NSDG_TF_TICE0][k] = o.tice0;
     ptr.f[NSDG_TF_NEWICE][k] = o.newice;
+    if (SLAB)
+        ptr.f[NSDG_TF_SST][k] = o.sst;
     if (DIAG) {
 #pragma unroll
         for (int q = 0; q < NSDG_THERMO_NDIAG; ++q)
@@ -341,6 +346,20 @@ __global__ void broadcast_layers(const double* tice0, double* tice, int64_t n, i
         tice[q] = tice0[q / nlayers];
 }
 
+// out[q][k] = f0[q][k] + w (f1[q][k] - f0[q][k]) for the 8 forcing streams (blockIdx.y = q)
+struct BlendPtrs {
+    double* out[8];
+};
+__global__ void blend_kernel(const __grid_constant__ BlendPtrs o, const double* f0, const double* f1, double w, int64_t n)
+{
+    const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n)
+        return;
+    const size_t q = blockIdx.y;
+    const double a = f0[q * n + k];
+    o.out[q][k] = a + w * (f1[q * n + k] - a);
+}
+
 int thermo_launch(nsdg_ctx* ctx, double dt, int nsteps, bool diag)
 {
     ThermoState* t = ctx->thermo;
@@ -361,10 +380,18 @@ int thermo_launch(nsdg_ctx* ctx, double dt, int nsteps, bool diag)
     const unsigned grid = (unsigned)((t->n + block - 1) / block);
     const double idt = 1. / dt;
     for (int s = 0; s < nsteps; ++s) {
-        if (diag && s == nsteps - 1)
-            NSDG_KERNEL(ctx, NSDG_K_THERMO, thermo_kernel<true><<<grid, block, 0, ctx->stream>>>(t->params, p, dt, idt, t->n));
+        const bool dg = diag && s == nsteps - 1;
+        nsdg_prof_begin(ctx, NSDG_K_THERMO);
+        if (dg && t->slab_ocean)
+            thermo_kernel<true, true><<<grid, block, 0, ctx->stream>>>(t->params, p, dt, idt, t->n);
+        else if (dg)
+            thermo_kernel<true, false><<<grid, block, 0, ctx->stream>>>(t->params, p, dt, idt, t->n);
+        else if (t->slab_ocean)
+            thermo_kernel<false, true><<<grid, block, 0, ctx->stream>>>(t->params, p, dt, idt, t->n);
         else
-            NSDG_KERNEL(ctx, NSDG_K_THERMO, thermo_kernel<false><<<grid, block, 0, ctx->stream>>>(t->params, p, dt, idt, t->n));
+            thermo_kernel<false, false><<<grid, block, 0, ctx->stream>>>(t->params, p, dt, idt, t->n);
+        nsdg_prof_end(ctx);
+        NSDG_LAUNCHED(ctx);
     }
     return NSDG_OK;
 }
@@ -380,6 +407,8 @@ void nsdg_thermo_free(nsdg_ctx* ctx)
         cudaFree(t->fields[q]);
     cudaFree(t->diag);
     cudaFree(t->stage);
+    cudaFree(t->level[0]);
+    cudaFree(t->level[1]);
     delete t;
     ctx->thermo = nullptr;
 }
@@ -507,6 +536,53 @@ int nsdg_thermo_upload_forcing(nsdg_ctx* ctx, const double* tair, const double* 
     }
     NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     t->have_forcing = true;
+    return NSDG_OK;
+}
+
+int nsdg_thermo_upload_forcing_level(nsdg_ctx* ctx, int32_t level, const double* tair,
+    const double* tdew, const double* slp, const double* qsw, const double* qlw,
+    const double* mld, const double* snowfall, const double* wind)
+{
+    NSDG_ENTER(ctx);
+    ThermoState* t = ctx->thermo;
+    NSDG_REQUIRE(ctx, t, NSDG_ESTATE, "nsdg_thermo_init has not been called");
+    NSDG_REQUIRE(ctx, level == 0 || level == 1, NSDG_EINVAL, "forcing level must be 0 or 1");
+    const double* src[8] = { tair, tdew, slp, qsw, qlw, mld, snowfall, wind };
+    for (const double* p : src)
+        NSDG_REQUIRE(ctx, p || t->n == 0, NSDG_EINVAL, "null forcing array");
+    if (!t->level[level])
+        NSDG_CUDA(ctx, cudaMalloc(&t->level[level], sizeof(double) * 8 * (size_t)(t->n + 1)));
+    for (int q = 0; q < 8 && t->n > 0; ++q)
+        NSDG_CUDA(ctx, cudaMemcpyAsync(t->level[level] + (size_t)q * t->n, src[q], sizeof(double) * (size_t)t->n,
+                           cudaMemcpyHostToDevice, ctx->stream));
+    NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    t->have_level[level] = true;
+    return NSDG_OK;
+}
+
+int nsdg_thermo_blend_forcing(nsdg_ctx* ctx, double w)
+{
+    NSDG_ENTER(ctx);
+    ThermoState* t = ctx->thermo;
+    NSDG_REQUIRE(ctx, t, NSDG_ESTATE, "nsdg_thermo_init has not been called");
+    NSDG_REQUIRE(ctx, t->have_level[0] && t->have_level[1], NSDG_ESTATE, "both forcing levels must be uploaded first");
+    NSDG_REQUIRE(ctx, w >= 0. && w <= 1., NSDG_EINVAL, "interpolation weight %g outside [0,1]", w);
+    if (t->n > 0) {
+        BlendPtrs o;
+        for (int q = 0; q < 8; ++q)
+            o.out[q] = t->fields[NSDG_TF_TAIR + q];
+        dim3 block(256), grid((unsigned)((t->n + 255) / 256), 8);
+        NSDG_KERNEL(ctx, NSDG_K_BLEND, blend_kernel<<<grid, block, 0, ctx->stream>>>(o, t->level[0], t->level[1], w, t->n));
+    }
+    t->have_forcing = true;
+    return NSDG_OK;
+}
+
+int nsdg_thermo_set_slab_ocean(nsdg_ctx* ctx, int32_t enable)
+{
+    NSDG_ENTER(ctx);
+    NSDG_REQUIRE(ctx, ctx->thermo, NSDG_ESTATE, "nsdg_thermo_init has not been called");
+    ctx->thermo->slab_ocean = enable != 0;
     return NSDG_OK;
 }
 

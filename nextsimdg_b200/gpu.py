@@ -132,6 +132,19 @@ class GpuStep:
         fo = [_f64(forcing[k], self.n) for k in FORCING]
         check(self.h, self.lib.nsdg_thermo_upload_forcing(self.h, *[_p(a) for a in fo]))
 
+    def setForcingLevels(self, forcing0, forcing1):
+        """Two time levels of the forcing stay on the device (nsdg_thermo_upload_forcing_level)."""
+        for lvl, fo in enumerate((forcing0, forcing1)):
+            a = [_f64(fo[k], self.n) for k in FORCING]
+            check(self.h, self.lib.nsdg_thermo_upload_forcing_level(self.h, lvl, *[_p(x) for x in a]))
+
+    def blendForcing(self, w):
+        """active forcing = f0 + w (f1 - f0), interpolated on the device"""
+        check(self.h, self.lib.nsdg_thermo_blend_forcing(self.h, float(w)))
+
+    def setSlabOcean(self, enable=True):
+        check(self.h, self.lib.nsdg_thermo_set_slab_ocean(self.h, int(bool(enable))))
+
     def init(self):
         pass
 
@@ -237,6 +250,14 @@ class GpuDynamics:
 
     def step(self, dt, nsub=100):
         check(self.h, self.lib.nsdg_dyn_step(self.h, float(dt), int(nsub)))
+
+    def set_forcing_levels(self, f0, f1):
+        for lvl, fo in enumerate((f0, f1)):
+            a = [_f64(fo[k], self.nx * self.ny) for k in ("UATM", "VATM", "UOCN", "VOCN")]
+            check(self.h, self.lib.nsdg_dyn_upload_forcing_level(self.h, lvl, *[_p(x) for x in a]))
+
+    def blend_forcing(self, w):
+        check(self.h, self.lib.nsdg_dyn_blend_forcing(self.h, float(w)))
 
     def step_host(self, dt, nsub, inputs=None, outputs=None):
         """One step with host buffers (nsdg_dyn_step_host): `inputs` maps field names to arrays

@@ -183,6 +183,23 @@ def test_step_host_equals_resident_path(ctx):
         b.step_host(120.0, 1, {"H": np.zeros((3, 3))}, None)
 
 
+def test_dynamics_forcing_levels_blend(ctx):
+    nx, ny = 48, 20
+    F, hx, hy = S.box_case(nx, ny, 3)
+    dyn = GpuDynamics(ctx, nx, ny, hx, hy, 3)
+    dyn.upload_all(F)
+    r = np.random.default_rng(4)
+    f0 = {k: r.standard_normal((ny, nx)) for k in ("UATM", "VATM", "UOCN", "VOCN")}
+    f1 = {k: r.standard_normal((ny, nx)) for k in f0}
+    with pytest.raises(NsdgError):
+        dyn.blend_forcing(0.5)
+    dyn.set_forcing_levels(f0, f1)
+    dyn.blend_forcing(0.3)
+    for k in f0:
+        want = f0[k] + 0.3 * (f1[k] - f0[k])
+        assert np.abs(dyn.download(k) - want).max() < 1e-15
+
+
 def test_size_independent_properties_large_grid(ctx):
     """2048^2 dG2 (too large for the oracle in seconds): constants are preserved, mass is
     conserved to round-off, zero forcing keeps a state of rest."""
