@@ -158,11 +158,28 @@ class GpuStep:
     def stop(self, stop_time=0):
         self.ctx.synchronize()
 
-    def writeRestartFile(self, path):
-        """Minimal restart: the 6 prognostic fields + the hidden newice state, as .npz."""
+    def writeRestartFile(self, path, nx=None):
+        """SoA restart (nextsimdg_b200/restart.py; the reference's structure/data layout of
+        core/src/DevGridIO.cpp:160-201) straight from the device mirror, plus the hidden newice
+        state.  nx: edge of the square DevGrid (default: sqrt(ncells), else a 1 x n grid)."""
+        from . import restart
         d = self.get_prognostic()
         d["newice"] = self.get_newice()
-        np.savez(path, **d)
+        if nx is None:
+            r = int(round(self.n ** 0.5))
+            nx = r if r * r == self.n else 1
+        restart.write_restart(path, d, nx, self.n // nx, self.nlayers)
+
+    @classmethod
+    def from_restart(cls, ctx, path, forcing, params=None):
+        """Model::configure's restart read (core/src/Model.cpp:62-73) without ElementData."""
+        from . import restart
+        st, meta = restart.read_restart(path)
+        step = cls(ctx, meta["nx"] * meta["ny"], meta["nlayers"], params)
+        step.setInitialData(st, forcing)
+        if "newice" in st:
+            step.set_newice(st["newice"])
+        return step
 
     # accessors -----------------------------------------------------------------------------
     def get_prognostic(self):

@@ -158,3 +158,33 @@ def test_two_rank_strips_reproduce_single_domain_gloo(tmp_path):
     outs = [p.communicate(timeout=240)[0] for p in procs]
     for r, (p, o) in enumerate(zip(procs, outs)):
         assert p.returncode == 0 and f"rank {r} ok" in o, o
+
+
+def test_soa_restart_roundtrip_and_layout(tmp_path):
+    """the reference's restart content (run/dev_res.py:9-20, layout of
+    core/src/DevGridIO.cpp:160-201) in the HDF5-free container."""
+    from nextsimdg_b200 import restart as R
+    st = R.dev_restart(10, 1)
+    assert st["cice"].size == 100 and np.all(st["cice"] == 0.5) and np.all(st["hice"] == 0.1)
+    assert np.all(st["sst"] == -1) and np.all(st["sss"] == 32) and np.all(st["tice"] == -1)
+    nx, ny, nl = 4, 3, 2
+    rng = np.random.default_rng(0)
+    full = {k: rng.standard_normal(nx * ny * (nl if k == "tice" else 1)) for k in R.PROGNOSTIC}
+    full["newice"] = rng.standard_normal(nx * ny)
+    p = str(tmp_path / "r.nsdgr")
+    R.write_restart(p, full, nx, ny, nl)
+    got, meta = R.read_restart(p)
+    assert meta == {"nx": nx, "ny": ny, "nlayers": nl, "structure": "devgrid"}
+    for k, v in full.items():
+        assert np.array_equal(got[k], v), k
+    # cell (i, j) sits at i*ny + j (x outer), its layers are contiguous
+    i, j = 2, 1
+    assert got["tice"][(i * ny + j) * nl + 1] == full["tice"].reshape(nx, ny, nl)[i, j, 1]
+    with pytest.raises(ValueError):
+        R.write_restart(p, {"hice": np.zeros(3)}, nx, ny, nl)
+    with open(p, "r+b") as f:
+        f.write(b"XXXX")
+    with pytest.raises(ValueError):
+        R.read_restart(p)
+    with pytest.raises(RuntimeError):
+        R.from_netcdf("/nonexistent.nc", p)
