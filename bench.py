@@ -38,6 +38,10 @@ BYTES_PREPARE = (12 + 4 + 8 + 4) * 8  # P_g from H,A; node constants from H0,A0,
 # the pair kernel runs TWO sub-iterations per launch: its units per launch are 2 x cells, its
 # compulsory DRAM bytes per launch (temporal blocking) are those of ONE fused sub-iteration
 SUBITS_PER_LAUNCH = {"mevp_pair_kernel": 2}
+# dram__bytes_read.sum + dram__bytes_write.sum per launch at 4096^2 cells from the ncu --set full
+# captures summarised in profiles/r1t_ncu_full_summary.txt (r1d_... for the fused kernel)
+NCU_TRAFFIC_4096SQ = {"mevp_pair_kernel": 4.2719e9, "mevp_fused_kernel": 4.5397e9,
+                      "transport_stage_kernel": 3.7266e9}
 BYTES_STEP_SPLIT = BYTES_TRANSPORT_STEP + BYTES_PREPARE + NSUB * (BYTES_STRESS + BYTES_VELOCITY)
 BYTES_STEP_FUSED = BYTES_TRANSPORT_STEP + BYTES_PREPARE + NSUB * BYTES_FUSED
 
@@ -285,7 +289,8 @@ def run_gpu(args):
         step_gbs = BYTES_STEP * cells_local * args.steps / (ms * 1e-3) / 1e9
         roof = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak,
                 "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
-                "traffic": args.traffic,
+                "traffic": args.traffic if args.traffic is not None else (
+                    NCU_TRAFFIC_4096SQ.get(kname) if cells_local == 4096 * 4096 else None),
                 "algorithmic_bytes_per_launch": kbytes,
                 "units_per_launch": f"{units} sub-iteration(s) x {cells_local} cells x "
                                     f"{per_kernel_bytes.get(kname, 0)} B",
