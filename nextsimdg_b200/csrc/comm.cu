@@ -86,7 +86,7 @@ void nsdg_comm_free(nsdg_ctx* ctx)
     ctx->comm = nullptr;
 }
 
-int nsdg_halo_exchange(nsdg_ctx* ctx, const HaloSpec* specs, int nspecs)
+int nsdg_halo_exchange(nsdg_ctx* ctx, const HaloSpec* specs, int nspecs, cudaStream_t st)
 {
     if (!nsdg_comm_active(ctx) || nspecs == 0)
         return NSDG_OK;
@@ -121,28 +121,41 @@ int nsdg_halo_exchange(nsdg_ctx* ctx, const HaloSpec* specs, int nspecs)
     const int up = (c->rank + 1) % c->nranks, down = (c->rank + c->nranks - 1) % c->nranks;
     dim3 block(256);
     const unsigned gx = (unsigned)((d->nx + 255) / 256);
+    if (!st)
+        st = ctx->stream;
+    // the per-kernel profiler brackets launches on the compute stream only
+#define NSDG_HALO_KERNEL(kid, ...)                                                                \
+    do {                                                                                          \
+        if (st == ctx->stream) {                                                                  \
+            NSDG_KERNEL(ctx, kid, __VA_ARGS__);                                                   \
+        } else {                                                                                  \
+            __VA_ARGS__;                                                                          \
+            NSDG_LAUNCHED(ctx);                                                                   \
+        }                                                                                         \
+    } while (0)
     if (send_up.n)
-        NSDG_KERNEL(ctx, NSDG_K_PACK, pack_rows<<<dim3(gx, send_up.n), block, 0, ctx->stream>>>(send_up, d->send_hi, d->nx));
+        NSDG_HALO_KERNEL(NSDG_K_PACK, pack_rows<<<dim3(gx, send_up.n), block, 0, st>>>(send_up, d->send_hi, d->nx));
     if (send_dn.n)
-        NSDG_KERNEL(ctx, NSDG_K_PACK, pack_rows<<<dim3(gx, send_dn.n), block, 0, ctx->stream>>>(send_dn, d->send_lo, d->nx));
+        NSDG_HALO_KERNEL(NSDG_K_PACK, pack_rows<<<dim3(gx, send_dn.n), block, 0, st>>>(send_dn, d->send_lo, d->nx));
     NSDG_NCCL(ctx, c, c->GroupStart());
     if (send_up.n) {
         const size_t count = (size_t)send_up.n * d->nx;
-        NSDG_NCCL(ctx, c, c->Send(d->send_hi, count, ncclFloat64, up, c->comm, ctx->stream));
-        NSDG_NCCL(ctx, c, c->Recv(d->recv_lo, count, ncclFloat64, down, c->comm, ctx->stream));
+        NSDG_NCCL(ctx, c, c->Send(d->send_hi, count, ncclFloat64, up, c->comm, st));
+        NSDG_NCCL(ctx, c, c->Recv(d->recv_lo, count, ncclFloat64, down, c->comm, st));
         c->bytes_sent += (int64_t)count * 8;
     }
     if (send_dn.n) {
         const size_t count = (size_t)send_dn.n * d->nx;
-        NSDG_NCCL(ctx, c, c->Send(d->send_lo, count, ncclFloat64, down, c->comm, ctx->stream));
-        NSDG_NCCL(ctx, c, c->Recv(d->recv_hi, count, ncclFloat64, up, c->comm, ctx->stream));
+        NSDG_NCCL(ctx, c, c->Send(d->send_lo, count, ncclFloat64, down, c->comm, st));
+        NSDG_NCCL(ctx, c, c->Recv(d->recv_hi, count, ncclFloat64, up, c->comm, st));
         c->bytes_sent += (int64_t)count * 8;
     }
     NSDG_NCCL(ctx, c, c->GroupEnd());
     if (recv_lo.n)
-        NSDG_KERNEL(ctx, NSDG_K_UNPACK, unpack_rows<<<dim3(gx, recv_lo.n), block, 0, ctx->stream>>>(recv_lo, d->recv_lo, d->nx));
+        NSDG_HALO_KERNEL(NSDG_K_UNPACK, unpack_rows<<<dim3(gx, recv_lo.n), block, 0, st>>>(recv_lo, d->recv_lo, d->nx));
     if (recv_hi.n)
-        NSDG_KERNEL(ctx, NSDG_K_UNPACK, unpack_rows<<<dim3(gx, recv_hi.n), block, 0, ctx->stream>>>(recv_hi, d->recv_hi, d->nx));
+        NSDG_HALO_KERNEL(NSDG_K_UNPACK, unpack_rows<<<dim3(gx, recv_hi.n), block, 0, st>>>(recv_hi, d->recv_hi, d->nx));
+#undef NSDG_HALO_KERNEL
     return NSDG_OK;
 }
 

@@ -118,15 +118,22 @@ int nsdg_create(nsdg_ctx** out, int device)
     }
     nsdg_ctx* ctx = new nsdg_ctx;
     ctx->device = device;
+    // boundary tiles and halo messages run at the highest priority so that they are scheduled
+    // ahead of the interior tiles they overlap with
+    int prio_lo = 0, prio_hi = 0;
+    cudaSetDevice(device);
+    cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
     if (cudaSetDevice(device) != cudaSuccess
         || cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess
-        || cudaStreamCreateWithFlags(&ctx->comm_stream, cudaStreamNonBlocking) != cudaSuccess
+        || cudaStreamCreateWithPriority(&ctx->comm_stream, cudaStreamNonBlocking, prio_hi) != cudaSuccess
         || cudaStreamCreateWithFlags(&ctx->h2d_stream, cudaStreamNonBlocking) != cudaSuccess
         || cudaStreamCreateWithFlags(&ctx->d2h_stream, cudaStreamNonBlocking) != cudaSuccess
         || cudaEventCreateWithFlags(&ctx->ev_pipe[0], cudaEventDisableTiming) != cudaSuccess
         || cudaEventCreateWithFlags(&ctx->ev_pipe[1], cudaEventDisableTiming) != cudaSuccess
         || cudaEventCreateWithFlags(&ctx->ev_pipe[2], cudaEventDisableTiming) != cudaSuccess
         || cudaEventCreateWithFlags(&ctx->ev_pipe[3], cudaEventDisableTiming) != cudaSuccess
+        || cudaEventCreateWithFlags(&ctx->ev_halo[0], cudaEventDisableTiming) != cudaSuccess
+        || cudaEventCreateWithFlags(&ctx->ev_halo[1], cudaEventDisableTiming) != cudaSuccess
         || cudaEventCreate(&ctx->ev_start) != cudaSuccess
         || cudaEventCreate(&ctx->ev_stop) != cudaSuccess) {
         fprintf(stderr, "nsdg_create: %s\n", cudaGetErrorString(cudaGetLastError()));
@@ -162,6 +169,9 @@ int nsdg_destroy(nsdg_ctx* ctx)
     if (ctx->d2h_stream)
         cudaStreamDestroy(ctx->d2h_stream);
     for (cudaEvent_t e : ctx->ev_pipe)
+        if (e)
+            cudaEventDestroy(e);
+    for (cudaEvent_t e : ctx->ev_halo)
         if (e)
             cudaEventDestroy(e);
     delete ctx;

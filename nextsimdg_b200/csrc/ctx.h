@@ -56,6 +56,7 @@ struct nsdg_ctx {
     cudaStream_t comm_stream = nullptr; // halo exchange
     cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr; // nsdg_dyn_step_host copies
     cudaEvent_t ev_pipe[4] = {};
+    cudaEvent_t ev_halo[2] = {}; // boundary tiles done -> exchange; exchange done -> next launch
     cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
     int64_t launches = 0;
     int sm_count = 148;

@@ -188,10 +188,34 @@ int mevp_cycle(nsdg_ctx* ctx, double dt, int nsub)
     const bool pair = pair_env && fused && !(d->cfg.flags & NSDG_DYN_SINGLE_MEVP);
     double* sa[3] = { d->f[NSDG_DF_S11], d->f[NSDG_DF_S12], d->f[NSDG_DF_S22] };
     double* sb[3] = { d->s2[0], d->s2[1], d->s2[2] };
+    // Strips: the tile rows next to the ghost rows go first; their halo messages travel on the
+    // communication stream while the interior tile rows compute (NSDG_HALO_OVERLAP=0 disables).
+    static int overlap_env = -1;
+    if (overlap_env < 0) {
+        const char* e = getenv("NSDG_HALO_OVERLAP");
+        overlap_env = e ? (atoi(e) != 0) : 1;
+    }
+    const int ty = nsdg_mevp_pair_tile_rows();
+    const int64_t ntr = (d->nyl + ty - 1) / ty; // tile rows of the strip
+    // the two top interior rows are sent up: they must lie inside the last boundary launch
+    const int64_t ntop = (d->nyl - (ntr - 1) * ty >= 2) ? 1 : 2;
+    const bool overlap = multi && pair && overlap_env && ntr >= ntop + 2 && ty >= 2;
     for (int p = 0; p < nsub; ++p) {
         bool paired = false;
+        int64_t rest0 = r0, rest1 = r0; // interior rows that run beside the exchange
         if (pair && p + 1 < nsub) {
-            if ((rc = nsdg_mevp_pair(ctx, dt, u, v, u2, v2, sa, sb)))
+            if (overlap) {
+                // boundary tile rows on the (high-priority) communication stream, behind
+                // everything issued so far
+                rest0 = r0 + ty;
+                rest1 = r0 + (ntr - ntop) * ty;
+                NSDG_CUDA(ctx, cudaEventRecord(ctx->ev_halo[0], ctx->stream));
+                NSDG_CUDA(ctx, cudaStreamWaitEvent(ctx->comm_stream, ctx->ev_halo[0], 0));
+                if ((rc = nsdg_mevp_pair(ctx, dt, u, v, u2, v2, sa, sb, r0, rest0, ctx->comm_stream))
+                    || (rc = nsdg_mevp_pair(ctx, dt, u, v, u2, v2, sa, sb, rest1, r1, ctx->comm_stream))
+                    || (rc = nsdg_mevp_pair(ctx, dt, u, v, u2, v2, sa, sb, rest0, rest1)))
+                    return rc;
+            } else if ((rc = nsdg_mevp_pair(ctx, dt, u, v, u2, v2, sa, sb, r0, r1)))
                 return rc;
             for (int q = 0; q < 3; ++q)
                 std::swap(sa[q], sb[q]);
@@ -226,7 +250,13 @@ int mevp_cycle(nsdg_ctx* ctx, double dt, int nsub)
             hs[n].planes.p[hs[n].planes.n++] = v2;
             hs[n].nlo = hs[n].nhi = paired ? 2 : 1;
             ++n;
-            if ((rc = nsdg_halo_exchange(ctx, hs, n)))
+            if (rest1 > rest0) {
+                // behind the boundary tiles on the communication stream, beside the interior tiles
+                if ((rc = nsdg_halo_exchange(ctx, hs, n, ctx->comm_stream)))
+                    return rc;
+                NSDG_CUDA(ctx, cudaEventRecord(ctx->ev_halo[1], ctx->comm_stream));
+                NSDG_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_halo[1], 0));
+            } else if ((rc = nsdg_halo_exchange(ctx, hs, n)))
                 return rc;
         }
         std::swap(u, u2);

@@ -72,14 +72,18 @@ int nsdg_mevp_velocity(nsdg_ctx* ctx, double dt, const double* u, const double* 
 // one fused sub-iteration: (u,v,Sold) -> (unew,vnew,Snew) on node rows [r0,r1)
 int nsdg_mevp_fused(nsdg_ctx* ctx, double dt, const double* u, const double* v, double* unew,
     double* vnew, double* const* Sold, double* const* Snew, int64_t r0, int64_t r1);
-// two sub-iterations in one launch (temporal blocking), single rank in wrap mode only
+// two sub-iterations in one launch (temporal blocking) on the owned rows [r0,r1); r0 must sit on
+// a tile-row boundary (NSDG_GHOST + k * nsdg_mevp_pair_tile_rows())
 int nsdg_mevp_pair(nsdg_ctx* ctx, double dt, const double* u, const double* v, double* unew,
-    double* vnew, double* const* Sold, double* const* Snew);
+    double* vnew, double* const* Sold, double* const* Snew, int64_t r0, int64_t r1,
+    cudaStream_t st = nullptr);
+int nsdg_mevp_pair_tile_rows();
 
 // comm.cu -----------------------------------------------------------------------------------
 // Ring halo exchange of up to 3 plane groups in ONE message per neighbour.  No-op on a single
 // rank (kernels wrap).
-int nsdg_halo_exchange(nsdg_ctx* ctx, const HaloSpec* specs, int nspecs);
+// st: stream to run pack / send+recv / unpack on (nullptr = the compute stream).
+int nsdg_halo_exchange(nsdg_ctx* ctx, const HaloSpec* specs, int nspecs, cudaStream_t st = nullptr);
 // one group: which = 1 lower ghost row only, 2 upper ghost row only, 3 both (one row each)
 int nsdg_halo_exchange(nsdg_ctx* ctx, const PlaneSet& planes, int which);
 bool nsdg_comm_active(const nsdg_ctx* ctx);

@@ -14,11 +14,11 @@
 //             (the oracle's formula with the p-independent terms summed once)
 // Per sub-iteration, three interchangeable implementations (all HBM streams over component-
 // major planes, coalesced; neighbours via L1/L2):
-//   split   stress_kernel + velocity_kernel                          24 + 19 = 43 doubles/cell
+//   split   stress_kernel + velocity_kernel                          24 + 17 = 41 doubles/cell
 //   fused   mevp_fused_kernel: stress + velocity in one launch, the new stress goes to the
 //           velocity phase through shared memory                     32 doubles/cell
 //   pair    mevp_pair_kernel: TWO sub-iterations per launch (temporal blocking on a 2-cell
-//           halo), single rank only                                  32 doubles/cell per PAIR
+//           halo; periodic wrap or the strip's ghost rows)           32 doubles/cell per PAIR
 // All index arithmetic is 32-bit (validated by the host: every array of the sub-cycle has fewer
 // than 2^31 elements) and every quotient that does not depend on the cell is taken on the host.
 #include "dyn.h"
@@ -452,7 +452,9 @@ __global__ void __launch_bounds__(FusedCfg<TX, TY>::NT, FusedCfg<TX, TY>::MINB) 
 // Every value is computed by the same formulas as in the single sub-iteration kernels, so a
 // redundantly computed halo value is bit-identical to the owner's.  Single rank: periodic wrap
 // in x and y by index arithmetic.  Strips: the two ghost rows on either side carry S^p, P_g,
-// u^p and the node constants of the neighbours, refreshed once per pair (dyn.cu).
+// u^p and the node constants of the neighbours, refreshed once per pair (dyn.cu); the launch can
+// be restricted to a range of tile rows so that the tiles next to the ghost rows run first and
+// their halo messages travel while the interior tiles compute.
 __device__ __forceinline__ int wrap_idx(int i, int n)
 {
     if (i < 0)
@@ -751,29 +753,53 @@ int nsdg_mevp_fused(nsdg_ctx* ctx, double dt, const double* u, const double* v, 
 }
 
 // two fused sub-iterations: (u,v,S) at p -> (unew,vnew,Snew) at p+2; single rank (wrap) only
-int nsdg_mevp_pair(nsdg_ctx* ctx, double dt, const double* u, const double* v, double* unew,
-    double* vnew, double* const* Sold, double* const* Snew)
+namespace {
+int pair_tile()
 {
-    DynState* d = ctx->dyn;
-    MevpArgs A = base_args(d, dt);
-    A.u = u;
-    A.v = v;
-    A.out0 = unew;
-    A.out1 = vnew;
-    set_stress(A, Sold, Snew);
-    A.r0 = NSDG_GHOST;
-    A.r1 = NSDG_GHOST + (int)d->nyl;
     static int tile = -1;
     if (tile < 0) {
         const char* e = getenv("NSDG_PAIR_TILE");
         std::string t = e ? e : "16x16";
         tile = t == "32x8" ? 1 : t == "32x16" ? 2 : t == "16x16m3" ? 3 : t == "16x8" ? 4 : t == "16x12" ? 5 : 0;
     }
+    return tile;
+}
+} // namespace
+
+int nsdg_mevp_pair_tile_rows()
+{
+    static const int ty[6] = { 16, 8, 16, 16, 8, 12 };
+    return ty[pair_tile()];
+}
+
+int nsdg_mevp_pair(nsdg_ctx* ctx, double dt, const double* u, const double* v, double* unew,
+    double* vnew, double* const* Sold, double* const* Snew, int64_t r0, int64_t r1, cudaStream_t st)
+{
+    DynState* d = ctx->dyn;
+    if (!st)
+        st = ctx->stream;
+    MevpArgs A = base_args(d, dt);
+    A.u = u;
+    A.v = v;
+    A.out0 = unew;
+    A.out1 = vnew;
+    set_stress(A, Sold, Snew);
+    A.r0 = (int)r0;
+    A.r1 = (int)r1;
+    const int tile = pair_tile();
+    const int nrows = (int)(r1 - r0);
+    if (nrows <= 0)
+        return NSDG_OK;
 #define NSDG_PAIR_LAUNCH(TX, TY, MINB)                                                            \
     do {                                                                                          \
         dim3 block(PairCfg<TX, TY>::NT),                                                          \
-            grid((unsigned)((d->nx + TX - 1) / TX), (unsigned)((d->nyl + TY - 1) / TY));          \
-        NSDG_KERNEL(ctx, NSDG_K_MEVP_PAIR, (mevp_pair_kernel<TX, TY, MINB><<<grid, block, 0, ctx->stream>>>(A))); \
+            grid((unsigned)((d->nx + TX - 1) / TX), (unsigned)((nrows + TY - 1) / TY));           \
+        if (st == ctx->stream) {                                                                  \
+            NSDG_KERNEL(ctx, NSDG_K_MEVP_PAIR, (mevp_pair_kernel<TX, TY, MINB><<<grid, block, 0, st>>>(A))); \
+        } else { /* the per-kernel profiler brackets the compute stream only */                   \
+            mevp_pair_kernel<TX, TY, MINB><<<grid, block, 0, st>>>(A);                            \
+            NSDG_LAUNCHED(ctx);                                                                   \
+        }                                                                                         \
     } while (0)
     switch (tile) {
     case 1:

@@ -25,11 +25,21 @@ def main():
     dist.broadcast_object_list(uid, src=0)
     ctx.comm_init(rank, world, uid[0])
     ok = True
-    for (nx, ny, bc, flags, nsub) in ((64, 16 * world + 3, BC_BOX, 0, 7),
-                                      (45, 9 * world, BC_PERIODIC, 0, 4),
-                                      (64, 16 * world, BC_BOX, DYN_SPLIT_MEVP, 5),
-                                      (96, 5 * world + 1, BC_BOX, DYN_SINGLE_MEVP, 3),
-                                      (40, 2 * world, BC_PERIODIC, 0, 6)):
+    cases = ((64, 16 * world + 3, BC_BOX, 0, 7),
+             (45, 9 * world, BC_PERIODIC, 0, 4),
+             (64, 16 * world, BC_BOX, DYN_SPLIT_MEVP, 5),
+             (96, 5 * world + 1, BC_BOX, DYN_SINGLE_MEVP, 3),
+             (40, 2 * world, BC_PERIODIC, 0, 6),
+             # >= 3 tile rows per strip: boundary tile rows first, halo
+             # exchange overlapped with the interior launch
+             (48, 49 * world, BC_BOX, 0, 6),
+             (37, 40 * world, BC_PERIODIC, 0, 7),
+             (48, 40 * world, BC_BOX, 0, 6),
+             (48, 49 * world, BC_PERIODIC, 0, 6))
+    only = os.environ.get("MGPU_CASES")  # e.g. "5,6" while debugging
+    if only:
+        cases = [cases[int(q)] for q in only.split(",")]
+    for (nx, ny, bc, flags, nsub) in cases:
         F, hx, hy = S.box_case(nx, ny, 6)
         rng = np.random.default_rng(11)
         F["U"] = 0.05 * rng.standard_normal((ny, nx))
