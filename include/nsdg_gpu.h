@@ -249,6 +249,18 @@ int nsdg_dyn_step(nsdg_ctx* ctx, double dt, int32_t nsub);
  * copies to be asynchronous.  Returns after everything has completed. */
 int nsdg_dyn_step_host(nsdg_ctx* ctx, double dt, int32_t nsub, const double* const* in,
     double* const* out);
+/* The same step, DEFERRED: returns as soon as everything is enqueued.  A time loop that calls
+ * this once per step gets the downloads of step k overlapped with the compute of step k+1 (U, V
+ * and the stress leave from a device-side snapshot) and the forcing of step k+1 uploaded into
+ * alternate device buffers while step k still computes.  The host buffers of a call (in and
+ * out) belong to the library until nsdg_dyn_host_wait returns: use distinct out buffers for
+ * consecutive steps, or wait in between.  nsdg_dyn_field_ptr values of the forcing fields change
+ * with every deferred call that uploads them.  Call nsdg_dyn_host_wait before using any other
+ * entry point on the dynamics state. */
+int nsdg_dyn_step_host_async(nsdg_ctx* ctx, double dt, int32_t nsub, const double* const* in,
+    double* const* out);
+/* blocks until every copy and kernel of earlier nsdg_dyn_step_host_async calls has completed */
+int nsdg_dyn_host_wait(nsdg_ctx* ctx);
 /* forcing ingestion for the dynamics: two resident time levels of (UATM, VATM, UOCN, VOCN),
  * host layout [ny_local][nx] each; blend sets the active forcing to f0 + w (f1 - f0) */
 int nsdg_dyn_upload_forcing_level(nsdg_ctx* ctx, int32_t level, const double* uatm,

@@ -109,6 +109,9 @@ SYMBOLS = {
     "nsdg_dyn_step": (ctypes.c_int, [_ctx, _dbl, _i32]),
     "nsdg_dyn_step_host": (ctypes.c_int, [_ctx, _dbl, _i32, ctypes.POINTER(c_double_p),
                                           ctypes.POINTER(c_double_p)]),
+    "nsdg_dyn_step_host_async": (ctypes.c_int, [_ctx, _dbl, _i32, ctypes.POINTER(c_double_p),
+                                                ctypes.POINTER(c_double_p)]),
+    "nsdg_dyn_host_wait": (ctypes.c_int, [_ctx]),
     "nsdg_dyn_upload_forcing_level": (ctypes.c_int, [_ctx, _i32] + [c_double_p] * 4),
     "nsdg_dyn_blend_forcing": (ctypes.c_int, [_ctx, _dbl]),
     "nsdg_dyn_mass": (ctypes.c_int, [_ctx, _i32, c_double_p]),

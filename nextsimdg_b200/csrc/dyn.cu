@@ -283,6 +283,12 @@ void nsdg_dyn_free(nsdg_ctx* ctx)
         return;
     for (int q = 0; q < NSDG_DF_COUNT; ++q)
         cudaFree(d->f[q]);
+    cudaFree(d->snap);
+    for (double* p : d->falt)
+        cudaFree(p);
+    for (cudaEvent_t e : { d->ev_done[0], d->ev_done[1], d->ev_ha_down, d->ev_snap_down })
+        if (e)
+            cudaEventDestroy(e);
     for (int f = 0; f < 2; ++f) {
         cudaFree(d->stage1[f]);
         cudaFree(d->stage2[f]);
@@ -485,20 +491,47 @@ int nsdg_dyn_step(nsdg_ctx* ctx, double dt, int32_t nsub)
     return nsdg_mevp_step(ctx, dt, nsub);
 }
 
-int nsdg_dyn_step_host(nsdg_ctx* ctx, double dt, int32_t nsub, const double* const* in,
-    double* const* out)
+// One model step with host buffers.  deferred = false: returns with every output on the host.
+// deferred = true: returns once everything is enqueued; the downloads of step k overlap the
+// compute of step k+1 and the forcing of step k+1 goes up while step k still computes.
+static int step_host_impl(nsdg_ctx* ctx, double dt, int32_t nsub, const double* const* in,
+    double* const* out, bool deferred)
 {
-    NSDG_ENTER(ctx);
     DynState* d = ctx->dyn;
     NSDG_REQUIRE(ctx, d, NSDG_ESTATE, "nsdg_dyn_init has not been called");
     NSDG_REQUIRE(ctx, dt > 0 && nsub >= 0, NSDG_EINVAL, "dt > 0 and nsub >= 0 required");
     const size_t inner = (size_t)d->nx * d->nyl;
-    auto copy = [&](int f, bool up, cudaStream_t st) -> cudaError_t {
+    if (!d->ev_done[0]) {
+        cudaEvent_t* evs[] = { &d->ev_done[0], &d->ev_done[1], &d->ev_ha_down, &d->ev_snap_down };
+        for (cudaEvent_t* e : evs)
+            NSDG_CUDA(ctx, cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+    }
+    const int64_t k = d->host_calls++;
+    const int forcing[4] = { NSDG_DF_UATM, NSDG_DF_VATM, NSDG_DF_UOCN, NSDG_DF_VOCN };
+    const int snapf[5] = { NSDG_DF_U, NSDG_DF_V, NSDG_DF_S11, NSDG_DF_S12, NSDG_DF_S22 };
+    const int snapoff[5] = { 0, 1, 2, 5, 8 };
+    int rc;
+    if (deferred) {
+        if (out && !d->snap && (rc = alloc_planes(ctx, &d->snap, 11)))
+            return rc;
+        for (int q = 0; q < 4; ++q)
+            if (in && in[forcing[q]] && !d->falt[q] && (rc = alloc_planes(ctx, &d->falt[q], 1)))
+                return rc;
+    }
+    auto upload = [&](int f, double* devbase) -> cudaError_t {
         for (int c = 0; c < d->ncomp[f]; ++c) {
-            double* dev = d->f[f] + (size_t)c * d->plane + NSDG_GHOST * d->nx;
-            cudaError_t e = up
-                ? cudaMemcpyAsync(dev, in[f] + c * inner, sizeof(double) * inner, cudaMemcpyHostToDevice, st)
-                : cudaMemcpyAsync(out[f] + c * inner, dev, sizeof(double) * inner, cudaMemcpyDeviceToHost, st);
+            cudaError_t e = cudaMemcpyAsync(devbase + (size_t)c * d->plane + NSDG_GHOST * d->nx,
+                in[f] + c * inner, sizeof(double) * inner, cudaMemcpyHostToDevice, ctx->h2d_stream);
+            if (e != cudaSuccess)
+                return e;
+        }
+        return cudaSuccess;
+    };
+    auto download = [&](int f, const double* devbase) -> cudaError_t {
+        for (int c = 0; c < d->ncomp[f]; ++c) {
+            cudaError_t e = cudaMemcpyAsync(out[f] + c * inner,
+                devbase + (size_t)c * d->plane + NSDG_GHOST * d->nx, sizeof(double) * inner,
+                cudaMemcpyDeviceToHost, ctx->d2h_stream);
             if (e != cudaSuccess)
                 return e;
         }
@@ -506,20 +539,43 @@ int nsdg_dyn_step_host(nsdg_ctx* ctx, double dt, int32_t nsub, const double* con
     };
     // ---- uploads: what the transport needs first
     const int first[] = { NSDG_DF_U, NSDG_DF_V, NSDG_DF_H, NSDG_DF_A };
-    const int second[] = { NSDG_DF_S11, NSDG_DF_S12, NSDG_DF_S22, NSDG_DF_UATM, NSDG_DF_VATM, NSDG_DF_UOCN, NSDG_DF_VOCN };
+    const int second[] = { NSDG_DF_S11, NSDG_DF_S12, NSDG_DF_S22 };
     if (in) {
+        bool state_in = false;
+        for (int f : first)
+            state_in |= in[f] != nullptr;
+        for (int f : second)
+            state_in |= in[f] != nullptr;
+        // state fields are overwritten in place: behind the previous step and its H, A download.
+        // Forcing goes to the alternate buffers, last read by the step before the previous one.
+        NSDG_CUDA(ctx, cudaStreamWaitEvent(ctx->h2d_stream, d->ev_done[k & 1], 0));
+        if (state_in) {
+            NSDG_CUDA(ctx, cudaStreamWaitEvent(ctx->h2d_stream, d->ev_done[(k + 1) & 1], 0));
+            NSDG_CUDA(ctx, cudaStreamWaitEvent(ctx->h2d_stream, d->ev_ha_down, 0));
+        }
         for (int f : first)
             if (in[f])
-                NSDG_CUDA(ctx, copy(f, true, ctx->h2d_stream));
+                NSDG_CUDA(ctx, upload(f, d->f[f]));
         NSDG_CUDA(ctx, cudaEventRecord(ctx->ev_pipe[0], ctx->h2d_stream));
         for (int f : second)
             if (in[f])
-                NSDG_CUDA(ctx, copy(f, true, ctx->h2d_stream));
+                NSDG_CUDA(ctx, upload(f, d->f[f]));
+        for (int q = 0; q < 4; ++q) {
+            const int f = forcing[q];
+            if (!in[f])
+                continue;
+            if (deferred) {
+                NSDG_CUDA(ctx, upload(f, d->falt[q]));
+                std::swap(d->f[f], d->falt[q]); // this step reads the new buffer
+            } else
+                NSDG_CUDA(ctx, upload(f, d->f[f]));
+        }
         NSDG_CUDA(ctx, cudaEventRecord(ctx->ev_pipe[1], ctx->h2d_stream));
         NSDG_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_pipe[0], 0));
     }
-    int rc = nsdg_transport_step_HA(ctx, dt);
-    if (rc)
+    // the transport overwrites H, A: behind their previous download
+    NSDG_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, d->ev_ha_down, 0));
+    if ((rc = nsdg_transport_step_HA(ctx, dt)))
         return rc;
     NSDG_CUDA(ctx, cudaEventRecord(ctx->ev_pipe[2], ctx->stream));
     // ---- H, A are final after the transport: they come down while the sub-cycle runs
@@ -527,22 +583,58 @@ int nsdg_dyn_step_host(nsdg_ctx* ctx, double dt, int32_t nsub, const double* con
         NSDG_CUDA(ctx, cudaStreamWaitEvent(ctx->d2h_stream, ctx->ev_pipe[2], 0));
         for (int f : { NSDG_DF_H, NSDG_DF_A })
             if (out[f])
-                NSDG_CUDA(ctx, copy(f, false, ctx->d2h_stream));
+                NSDG_CUDA(ctx, download(f, d->f[f]));
+        NSDG_CUDA(ctx, cudaEventRecord(d->ev_ha_down, ctx->d2h_stream));
     }
     if (in)
         NSDG_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_pipe[1], 0));
     if ((rc = nsdg_mevp_step(ctx, dt, nsub)))
         return rc;
+    if (out && deferred) {
+        // snapshot (device to device) once the previous snapshot has left
+        NSDG_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, d->ev_snap_down, 0));
+        for (int q = 0; q < 5; ++q)
+            if (out[snapf[q]])
+                NSDG_CUDA(ctx, cudaMemcpyAsync(d->snap + (size_t)snapoff[q] * d->plane, d->f[snapf[q]],
+                                   sizeof(double) * (size_t)d->ncomp[snapf[q]] * d->plane,
+                                   cudaMemcpyDeviceToDevice, ctx->stream));
+    }
     NSDG_CUDA(ctx, cudaEventRecord(ctx->ev_pipe[3], ctx->stream));
+    NSDG_CUDA(ctx, cudaEventRecord(d->ev_done[k & 1], ctx->stream));
     if (out) {
         NSDG_CUDA(ctx, cudaStreamWaitEvent(ctx->d2h_stream, ctx->ev_pipe[3], 0));
-        for (int f : { NSDG_DF_U, NSDG_DF_V, NSDG_DF_S11, NSDG_DF_S12, NSDG_DF_S22 })
-            if (out[f]) // d->f[] already points at the buffers that hold the new state
-                NSDG_CUDA(ctx, copy(f, false, ctx->d2h_stream));
-        NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->d2h_stream));
+        for (int q = 0; q < 5; ++q)
+            if (out[snapf[q]]) // d->f[] already points at the buffers that hold the new state
+                NSDG_CUDA(ctx, download(snapf[q], deferred ? d->snap + (size_t)snapoff[q] * d->plane : d->f[snapf[q]]));
+        NSDG_CUDA(ctx, cudaEventRecord(d->ev_snap_down, ctx->d2h_stream));
     }
-    NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return NSDG_OK;
+}
+
+int nsdg_dyn_host_wait(nsdg_ctx* ctx)
+{
+    NSDG_ENTER(ctx);
+    NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->h2d_stream));
+    NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->d2h_stream));
+    return NSDG_OK;
+}
+
+int nsdg_dyn_step_host(nsdg_ctx* ctx, double dt, int32_t nsub, const double* const* in,
+    double* const* out)
+{
+    NSDG_ENTER(ctx);
+    int rc = nsdg_dyn_host_wait(ctx); // deferred steps may still be reading what this one overwrites
+    if (!rc)
+        rc = step_host_impl(ctx, dt, nsub, in, out, false);
+    return rc ? rc : nsdg_dyn_host_wait(ctx);
+}
+
+int nsdg_dyn_step_host_async(nsdg_ctx* ctx, double dt, int32_t nsub, const double* const* in,
+    double* const* out)
+{
+    NSDG_ENTER(ctx);
+    return step_host_impl(ctx, dt, nsub, in, out, true);
 }
 
 int nsdg_dyn_upload_forcing_level(nsdg_ctx* ctx, int32_t level, const double* uatm,

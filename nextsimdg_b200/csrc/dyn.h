@@ -33,6 +33,14 @@ struct DynState {
     double* flevel[2] = {}; // forcing time levels: 4 planes each (UATM, VATM, UOCN, VOCN)
     bool have_flevel[2] = { false, false };
     double* scratch = nullptr; // reductions
+    // deferred host steps (nsdg_dyn_step_host_async): the velocity and stress of step k are
+    // snapshotted so that they can travel to the host while step k+1 computes; forcing uploads
+    // land in the alternate buffers while the current ones are still being read
+    double* snap = nullptr; // 11 planes: U, V, S11[3], S12[3], S22[3]
+    double* falt[4] = {}; // alternates of UATM, VATM, UOCN, VOCN
+    cudaEvent_t ev_done[2] = {}; // compute of host step k finished (k & 1)
+    cudaEvent_t ev_ha_down = nullptr, ev_snap_down = nullptr; // downloads of H,A / of the snapshot finished
+    int64_t host_calls = 0;
     double* host_stage = nullptr; // pinned staging for upload/download
     size_t host_stage_bytes = 0;
     // halo pack buffers (comm.cu)

@@ -276,11 +276,12 @@ class GpuDynamics:
     def blend_forcing(self, w):
         check(self.h, self.lib.nsdg_dyn_blend_forcing(self.h, float(w)))
 
-    def step_host(self, dt, nsub, inputs=None, outputs=None):
+    def step_host(self, dt, nsub, inputs=None, outputs=None, deferred=False):
         """One step with host buffers (nsdg_dyn_step_host): `inputs` maps field names to arrays
         (or raw addresses of pinned buffers) uploaded for this step, `outputs` maps field names
         to writable buffers; copies overlap the compute.  Missing names stay resident / are
-        not downloaded."""
+        not downloaded.  deferred=True (nsdg_dyn_step_host_async) returns once the step is
+        enqueued: its downloads overlap the next step; the buffers are valid after host_wait()."""
         def table(m, writable):
             t = (c_double_p * len(DYN_FIELDS))()
             keep = []
@@ -297,8 +298,15 @@ class GpuDynamics:
             return t, keep
         tin, k1 = table(inputs, False)
         tout, k2 = table(outputs, True)
-        check(self.h, self.lib.nsdg_dyn_step_host(self.h, float(dt), int(nsub),
-                                                  tin if inputs else None, tout if outputs else None))
+        fn = self.lib.nsdg_dyn_step_host_async if deferred else self.lib.nsdg_dyn_step_host
+        if deferred:  # the library owns the buffers until host_wait
+            self._pending = getattr(self, "_pending", []) + [k1, k2]
+        check(self.h, fn(self.h, float(dt), int(nsub), tin if inputs else None,
+                         tout if outputs else None))
+
+    def host_wait(self):
+        check(self.h, self.lib.nsdg_dyn_host_wait(self.h))
+        self._pending = []
 
     def mass(self, name):
         m = ctypes.c_double()

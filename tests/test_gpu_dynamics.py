@@ -183,6 +183,45 @@ def test_step_host_equals_resident_path(ctx):
         b.step_host(120.0, 1, {"H": np.zeros((3, 3))}, None)
 
 
+def test_deferred_host_steps_equal_resident_path(ctx):
+    """nsdg_dyn_step_host_async: downloads of step k overlap step k+1, forcing of step k+1 goes
+    up into alternate buffers while step k computes; every step's output must equal the resident
+    path's, with a forcing that changes from step to step."""
+    nx, ny, nsteps = 80, 48, 5
+    F, hx, hy = S.box_case(nx, ny, 6)
+    F["U"], F["V"] = random_velocity(nx, ny, 5, 0.05)
+    mp = MevpParams.defaults()
+    mp.bc = BC_PERIODIC
+    names = ("H", "A", "U", "V", "S11", "S12", "S22")
+    forcing = ("UATM", "VATM", "UOCN", "VOCN")
+    fk = [{k: np.ascontiguousarray(F[k] * (1.0 + 0.1 * s)) for k in forcing} for s in range(nsteps)]
+    a = GpuDynamics(ctx, nx, ny, hx, hy, 6, mevp=mp)
+    a.upload_all(F)
+    ref = []
+    for s in range(nsteps):
+        for k in forcing:
+            a.upload(k, fk[s][k])
+        a.step(120.0, 7)
+        ref.append({k: a.download(k) for k in names})
+    a.step(120.0, 7)  # one more with the last forcing
+    ref_last = {k: a.download(k) for k in names}
+    b = GpuDynamics(ctx, nx, ny, hx, hy, 6, mevp=mp)  # (one dynamics state per context: a is gone)
+    b.upload_all(F)
+    outs = [{k: np.full(b.field_shape(k), np.nan) for k in names} for _ in range(nsteps)]
+    for s in range(nsteps):
+        b.step_host(120.0, 7, fk[s], outs[s], deferred=True)
+    b.host_wait()
+    for s in range(nsteps):
+        for k in names:
+            assert np.array_equal(outs[s][k], ref[s][k]), (s, k)
+    # a blocking step after deferred ones continues from the same state
+    last = {k: np.empty(b.field_shape(k)) for k in names}
+    b.step_host(120.0, 7, None, last)
+    for k in names:
+        assert np.array_equal(last[k], ref_last[k]), k
+        assert np.array_equal(last[k], b.download(k)), k
+
+
 def test_dynamics_forcing_levels_blend(ctx):
     nx, ny = 48, 20
     F, hx, hy = S.box_case(nx, ny, 3)
