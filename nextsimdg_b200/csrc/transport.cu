@@ -122,7 +122,136 @@ __global__ void __launch_bounds__(256, MINB) transport_stage_kernel(const __grid
         vT[g] = (v01 * (1 - s) + v11 * s) * A.ihy * w;
     }
 
-    {
+    if constexpr (NC == 6) {
+        // dG2, three-point Gauss rule, written out in tensor-product form (same integrals as the
+        // generic branch below, ~45 % fewer FP64 instructions): with a = xi - 1/2, b = eta - 1/2
+        //   phi(a, b) = (c0 + c2 b + c4 (b^2 - 1/12)) + (c1 + c5 b) a + c3 (a^2 - 1/12)
+        // is evaluated row by row, the velocity at a volume point is a lerp of the edge point
+        // velocities, an edge trace is a 1-D quadratic, and the moments against psi are taken
+        // from row / column sums.  Gauss abscissae -g, 0, +g with g^2 = 3/20: g^2 - 1/12 = 1/15.
+        constexpr double g = 0.3872983346207417, W0 = 5. / 18., W1 = 8. / 18.;
+        constexpr double XI[3] = { 0.5 - g, 0.5, 0.5 + g };
+        constexpr double WQ[3] = { W0, W1, W0 };
+        double c[NC];
+        load_cell<NC>(c, A.src[f], A.plane, k);
+        double r0 = 0., r1 = 0., r2 = 0., r3 = 0., r4 = 0., r5 = 0.;
+        { // ---- volume term: int phi (u/hx dpsi/dxi + v/hy dpsi/deta)
+            // fx[b][a] = w_a w_b phi u/hx, fy[b][a] = w_a w_b phi v/hy (uL.. carry w_b/hx, vB.. w_a/hy)
+            double sx0 = 0., sx2 = 0., sxa = 0.; // sum_a fx of row b = 0, 2; sum over all of fx a/g
+            double sy_a0 = 0., sy_a2 = 0., syb = 0.; // sum_b fy of column a = 0, 2; sum of fy b/g
+#pragma unroll
+            for (int b = 0; b < 3; ++b) {
+                const double bb = XI[b] - 0.5;
+                const double p0 = (b == 1) ? c[0] - c[4] * (1. / 12.) : c[0] + c[2] * bb + c[4] * (1. / 15.);
+                const double p1 = (b == 1) ? c[1] : c[1] + c[5] * bb;
+                const double e = p0 + c[3] * (1. / 15.), o = p1 * g;
+                const double ph[3] = { e - o, p0 - c[3] * (1. / 12.), e + o };
+                const double du = uR[b] - uL[b];
+                double fxr[3], fyr[3];
+#pragma unroll
+                for (int a = 0; a < 3; ++a) {
+                    const double uu = uL[b] + du * XI[a]; // w_b u / hx
+                    const double vv = vB[a] + (vT[a] - vB[a]) * XI[b]; // w_a v / hy
+                    fxr[a] = (ph[a] * WQ[a]) * uu;
+                    fyr[a] = (ph[a] * WQ[b]) * vv;
+                }
+                const double sx = fxr[0] + fxr[1] + fxr[2], sy = fyr[0] + fyr[1] + fyr[2];
+                r1 += sx;
+                r2 += sy;
+                sxa += fxr[2] - fxr[0];
+                if (b == 0) {
+                    sx0 = sx;
+                    sy_a0 = fyr[0];
+                    sy_a2 = fyr[2];
+                    syb -= sy;
+                } else if (b == 2) {
+                    sx2 = sx;
+                    sy_a0 += fyr[0];
+                    sy_a2 += fyr[2];
+                    syb += sy;
+                } else {
+                    sy_a0 += fyr[0];
+                    sy_a2 += fyr[2];
+                }
+            }
+            r3 = (2. * g) * sxa; // sum fx 2a
+            r4 = (2. * g) * syb; // sum fy 2b
+            r5 = g * ((sx2 - sx0) + (sy_a2 - sy_a0)); // sum fx b + fy a
+        }
+        // ---- edges: trace(t) = T0 + T1 t + T2 (t^2 - 1/12) along the edge, t = -g, 0, +g
+        // own traces
+        const double m0 = c[0] + c[3] * (1. / 6.), n0 = c[0] + c[4] * (1. / 6.);
+        const double tl[3] = { m0 - 0.5 * c[1], c[2] - 0.5 * c[5], c[4] }; // xi = 0
+        const double tr[3] = { m0 + 0.5 * c[1], c[2] + 0.5 * c[5], c[4] }; // xi = 1
+        const double tb[3] = { n0 - 0.5 * c[2], c[1] - 0.5 * c[5], c[3] }; // eta = 0
+        const double tt[3] = { n0 + 0.5 * c[2], c[1] + 0.5 * c[5], c[3] }; // eta = 1
+        // flux moments of one edge: M0 = sum F, M1 = sum F t, M2 = sum F (t^2 - 1/12); `minus` is
+        // the trace on the side the normal velocity points away from
+        auto edge = [&](const double (&vn)[3], const double (&minus)[3], const double (&plus)[3], double& M0,
+                        double& M1, double& M2) {
+            const double em = minus[0] + minus[2] * (1. / 15.), om = minus[1] * g;
+            const double ep = plus[0] + plus[2] * (1. / 15.), op = plus[1] * g;
+            const double F0 = vn[0] * (vn[0] > 0. ? em - om : ep - op);
+            const double F1 = vn[1] * (vn[1] > 0. ? minus[0] - minus[2] * (1. / 12.) : plus[0] - plus[2] * (1. / 12.));
+            const double F2 = vn[2] * (vn[2] > 0. ? em + om : ep + op);
+            const double s02 = F0 + F2;
+            M0 = s02 + F1;
+            M1 = g * (F2 - F0);
+            M2 = s02 * (1. / 15.) - F1 * (1. / 12.);
+        };
+        double cn[NC];
+        double L0, L1, L2, R0, R1, R2;
+        load_cell<NC>(cn, A.src[f], A.plane, r * A.nx + im); // left neighbour: its xi = 1 trace
+        {
+            const double nb[3] = { cn[0] + cn[3] * (1. / 6.) + 0.5 * cn[1], cn[2] + 0.5 * cn[5], cn[4] };
+            edge(uL, nb, tl, L0, L1, L2);
+        }
+        load_cell<NC>(cn, A.src[f], A.plane, r * A.nx + ip); // right neighbour: its xi = 0 trace
+        {
+            const double nb[3] = { cn[0] + cn[3] * (1. / 6.) - 0.5 * cn[1], cn[2] - 0.5 * cn[5], cn[4] };
+            edge(uR, tr, nb, R0, R1, R2);
+        }
+        // psi on xi = 0 / 1: (1, -+1/2, t, 1/6, t^2 - 1/12, -+t/2); inflow through the left edge
+        // adds, outflow through the right edge subtracts
+        {
+            const double d0 = L0 - R0, s0 = L0 + R0, d1 = L1 - R1, s1 = L1 + R1;
+            r0 += d0;
+            r1 -= 0.5 * s0;
+            r2 += d1;
+            r3 += d0 * (1. / 6.);
+            r4 += L2 - R2;
+            r5 -= 0.5 * s1;
+        }
+        load_cell<NC>(cn, A.src[f], A.plane, rm * A.nx + i); // lower neighbour: its eta = 1 trace
+        {
+            const double nb[3] = { cn[0] + cn[4] * (1. / 6.) + 0.5 * cn[2], cn[1] + 0.5 * cn[5], cn[3] };
+            edge(vB, nb, tb, L0, L1, L2);
+        }
+        load_cell<NC>(cn, A.src[f], A.plane, rp * A.nx + i); // upper neighbour: its eta = 0 trace
+        {
+            const double nb[3] = { cn[0] + cn[4] * (1. / 6.) - 0.5 * cn[2], cn[1] - 0.5 * cn[5], cn[3] };
+            edge(vT, tt, nb, R0, R1, R2);
+        }
+        // psi on eta = 0 / 1: (1, t, -+1/2, t^2 - 1/12, 1/6, -+t/2)
+        {
+            const double d0 = L0 - R0, s0 = L0 + R0, d1 = L1 - R1, s1 = L1 + R1;
+            r0 += d0;
+            r1 += d1;
+            r2 -= 0.5 * s0;
+            r3 += L2 - R2;
+            r4 += d0 * (1. / 6.);
+            r5 -= 0.5 * s1;
+        }
+        const double rr[NC] = { r0, r1, r2, r3, r4, r5 };
+        constexpr double IM[6] = { 1., 12., 12., 180., 180., 144. };
+#pragma unroll
+        for (int q = 0; q < NC; ++q) {
+            double val = c[q] + A.dt * IM[q] * rr[q];
+            if (HAS_BASE)
+                val = A.a * __ldg(A.base[f] + q * A.plane + k) + A.b * val;
+            A.dst[f][q * A.plane + k] = val;
+        }
+    } else {
         double c[NC], cn[NC], rr[NC];
         load_cell<NC>(c, A.src[f], A.plane, k);
 #pragma unroll
@@ -268,7 +397,7 @@ int nsdg_transport_stage(nsdg_ctx* ctx, int nfields, double* const* src, double*
     static int minb = 0; // NSDG_TRANSPORT_MINB: resident-CTA target of the dG2 register budget (tuning)
     if (!minb) {
         const char* e = getenv("NSDG_TRANSPORT_MINB");
-        minb = e ? atoi(e) : 2;
+        minb = e ? atoi(e) : 3;
     }
     if (d->nc == 1)
         launch_stage<1, 4>(A, hb, grid, block, ctx->stream);
