@@ -361,13 +361,204 @@ def run_gpu(args):
     ctx.close()
 
 
+# ---------------------------------------------------------------------------------------------
+# --workload thermo: BASELINE configs[3], the per-cell column thermodynamics (the part of the
+# path that EXISTS in the reference: parity pinned, CPU arm = the reference's own sources)
+THERMO_BYTES = 160  # 15 input + 5 output doubles per cell-update
+THERMO_DT = 600.0
+
+
+def thermo_config(args, n):
+    return {"workload": f"synthetic {args.nx}x{args.ny} per-cell column thermodynamics "
+                        f"(NextsimPhysics/ThermoIce0), {n} GPU(s), independent cells",
+            "cells_per_gpu": args.nx * args.ny, "dt_s": THERMO_DT,
+            "l2": "working set 2.7 GB per GPU >> 126 MB L2",
+            "parity": "pinned: reference sources compiled in place (oracle/_ref/libnsdg_ref.so)"}
+
+
+def thermo_reference_rate(ncells, nsteps, nthreads):
+    """The reference's own column physics (DevStep::iterate body over std::vector<ElementData>,
+    oracle/ref_harness.cpp) on `nthreads` host threads; returns cell-updates/s."""
+    from nextsimdg_b200 import synthetic as S
+    from oracle import refthermo as R
+    R.configure(R.ini())
+    st, fo = S.thermo_inputs(ncells)
+    g = R.RefGrid(ncells, 1)
+    g.set_prognostic(st["hice"], st["cice"], st["hsnow"], st["sst"], st["sss"], st["tice0"])
+    g.set_forcing(*[fo[k] for k in R.FORC])
+    g.step(THERMO_DT, 1, nthreads)  # warm-up (first-touch, statics)
+    t0 = time.perf_counter()
+    g.step(THERMO_DT, nsteps, nthreads)
+    secs = time.perf_counter() - t0
+    g.close()
+    return ncells * nsteps / secs, secs
+
+
+def run_thermo_reference(args):
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    from oracle import refthermo as R
+    cores = os.cpu_count() or 1
+    n = 1 << 21
+    if R.available():
+        value, secs = thermo_reference_rate(n, args.steps, cores)
+        one, _ = thermo_reference_rate(n, 1, 1)
+        kind, note = "reference", f"single thread (as the reference runs): {one:.4g} cell-updates/s"
+    else:  # the compiled reference did not travel: the C restatement of the same arithmetic
+        from oracle import cpu_oracle as O
+        from nextsimdg_b200 import synthetic as S
+        from nextsimdg_b200._abi import ThermoParams
+        st, fo = S.thermo_inputs(n)
+        cores = os.cpu_count() or 1
+        t0 = time.perf_counter()
+        O.thermo_step(ThermoParams.defaults(), THERMO_DT, args.steps, st, fo, nthreads=cores)
+        secs = time.perf_counter() - t0
+        value, kind, note = n * args.steps / secs, "port", "oracle/thermo_port.c (OpenMP)"
+    line = {"impl": "reference", "metric": "cell-updates/sec (column thermodynamics)", "value": value,
+            "unit": "cell-updates/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * secs / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": thermo_config(args, args.gpus),
+            "cpu_baseline": {"value": value, "unit": "cell-updates/s", "cores": cores, "kind": kind,
+                             "sample": f"{n} cells of the same synthetic distribution, "
+                                       f"{args.steps} sweeps", "note": note},
+            "e2e": {"value": value, "unit": "cell-updates/s", "h2d_bytes_per_step": 0,
+                    "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def run_thermo(args):
+    import torch
+    import torch.distributed as dist
+    from nextsimdg_b200 import synthetic as S
+    from nextsimdg_b200._abi import ThermoParams
+    from nextsimdg_b200.gpu import Context, GpuStep
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torchrun")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; this framework has no CPU path")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    ctx = Context(local)
+    n = args.nx * args.ny  # cells of this rank: independent columns, no collective (SURVEY 8e)
+    st, fo = S.thermo_inputs(n, seed=S.THERMO_SEED + rank)
+    prog = dict(st)
+    prog["tice"] = prog.pop("tice0")
+    step = GpuStep(ctx, n, 1, ThermoParams.defaults())
+    step.setInitialData(prog, fo)
+    for _ in range(args.warmup):
+        step.iterate(THERMO_DT, 1)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = ctx.launches
+    ctx.profile_begin()
+    ctx.timer_start()
+    for _ in range(args.steps):
+        step.iterate(THERMO_DT, 1)
+    ms = ctx.timer_stop()
+    prof = ctx.profile_end()
+    launches = ctx.launches - l0
+    barrier()
+    extra = 0
+    if ms < 400.0:  # a sweep takes 0.4 ms: keep the same kernel running until nvidia-smi has samples
+        extra = 1000
+        step.iterate(THERMO_DT, extra)
+        barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    if clocks is not None and extra:
+        clocks["sampled_over"] = f"the timed sweeps plus {extra} more right after them"
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max = float(t.item())
+    value = n * world * args.steps / (ms_max * 1e-3)
+    got = step.get_prognostic()
+    if not all(np.isfinite(v).all() for v in got.values()):
+        raise SystemExit("bench.py: non-finite thermodynamic state after the timed steps")
+
+    # ---- e2e: nsdg_thermo_run_host with pinned host buffers: 14 arrays up, one sweep, 6 down
+    e2e_value, h2d, d2h = None, 0, 0
+    if not args.no_e2e:
+        def pin(a):
+            tpin = torch.empty(a.shape, dtype=torch.float64).pin_memory()
+            tpin.numpy()[...] = a
+            return tpin
+        keep = {k: pin(v) for k, v in list(prog.items()) + list(fo.items())}
+        hp = {k: keep[k].numpy() for k in prog}
+        hf = {k: keep[k].numpy() for k in fo}
+        step.run_host(THERMO_DT, 1, hp, hf)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            step.run_host(THERMO_DT, 1, hp, hf)
+        barrier()
+        te = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        e2e_value = n * world * args.steps / float(te.item())
+        h2d, d2h = 14 * n * 8, 6 * n * 8
+    if rank == 0:
+        peak, peak_src = peaks()
+        ktot, kcnt = prof["thermo_kernel"]
+        kavg = ktot / kcnt
+        achieved = THERMO_BYTES * n / (kavg * 1e-3) / 1e9
+        cpu = None
+        if args.gpus == 1 and not args.no_cpu:
+            from oracle import refthermo as R
+            if R.available():
+                cores = os.cpu_count() or 1
+                m = 1 << 21
+                rate, _ = thermo_reference_rate(m, 3, cores)
+                one, _ = thermo_reference_rate(m, 1, 1)
+                cpu = {"value": rate, "unit": "cell-updates/s", "cores": cores, "kind": "reference",
+                       "sample": f"{m} cells of the same distribution, 3 sweeps, the reference's own "
+                                 "column physics compiled in place (oracle/_ref)",
+                       "single_thread": one}
+        line = {"metric": "cell-updates/sec (column thermodynamics)", "value": value,
+                "unit": "cell-updates/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": thermo_config(args, world), "clocks": clocks,
+                "e2e": {"value": e2e_value, "unit": "cell-updates/s", "h2d_bytes_per_step": h2d,
+                        "d2h_bytes_per_step": d2h,
+                        "what": "nsdg_thermo_run_host per step: prognostic state + forcing up from "
+                                "pinned host memory, one sweep, prognostic state down"},
+                "gpu_launches": int(launches),
+                "roofline": {"bound": "hbm", "kernel": "thermo_kernel", "achieved": achieved,
+                             "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                             "peak_source": peak_src, "traffic": None,
+                             "algorithmic_bytes_per_launch": THERMO_BYTES * n,
+                             "units_per_launch": f"{n} cells x {THERMO_BYTES} B",
+                             "avg_launch_ms": kavg, "launches": kcnt, "share_of_step": ktot / ms},
+                "cpu_baseline": cpu}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    ctx.close()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="auto", choices=["auto", "16384sq"])
+    ap.add_argument("--workload", default="auto", choices=["auto", "16384sq", "thermo"])
     ap.add_argument("--nx", type=int, default=4096)
     ap.add_argument("--ny", type=int, default=4096, help="rows per GPU")
     ap.add_argument("--e2e-steps", type=int, default=5)
@@ -378,7 +569,9 @@ def main():
     ap.add_argument("--traffic", type=float, default=None,
                     help="dram bytes per launch of the dominant kernel from an ncu capture")
     args = ap.parse_args()
-    if args.impl == "reference":
+    if args.workload == "thermo":
+        run_thermo_reference(args) if args.impl == "reference" else run_thermo(args)
+    elif args.impl == "reference":
         run_reference(args)
     else:
         run_gpu(args)
