@@ -18,6 +18,7 @@
 // data-dependent branches (t1<tf, hi<minh, draught>hi, c<minc, hs>0) resolve as on the CPU and
 // the state agrees with the compiled reference to <= 1e-10 (tests/test_gpu_thermo.py).
 #include "ctx.h"
+#include <algorithm>
 #include "fp64_fast.cuh"
 
 namespace {
@@ -680,14 +681,66 @@ int nsdg_thermo_run_host(nsdg_ctx* ctx, double dt, int32_t nsteps, double* hice,
     const double* tdew, const double* slp, const double* qsw, const double* qlw,
     const double* mld, const double* snowfall, const double* wind)
 {
+    NSDG_ENTER(ctx);
+    ThermoState* t = ctx->thermo;
+    NSDG_REQUIRE(ctx, t, NSDG_ESTATE, "nsdg_thermo_init has not been called");
     int rc;
-    if ((rc = nsdg_thermo_upload_prognostic(ctx, hice, cice, hsnow, sst, sss, tice)))
-        return rc;
-    if ((rc = nsdg_thermo_upload_forcing(ctx, tair, tdew, slp, qsw, qlw, mld, snowfall, wind)))
-        return rc;
-    if ((rc = nsdg_thermo_step(ctx, dt, nsteps)))
-        return rc;
-    return nsdg_thermo_download_prognostic(ctx, hice, cice, hsnow, nullptr, nullptr, tice);
+    if (t->nlayers != 1 || t->n < (1 << 16) || nsteps < 1) { // small or layered: plain sequence
+        if ((rc = nsdg_thermo_upload_prognostic(ctx, hice, cice, hsnow, sst, sss, tice)))
+            return rc;
+        if ((rc = nsdg_thermo_upload_forcing(ctx, tair, tdew, slp, qsw, qlw, mld, snowfall, wind)))
+            return rc;
+        if ((rc = nsdg_thermo_step(ctx, dt, nsteps)))
+            return rc;
+        return nsdg_thermo_download_prognostic(ctx, hice, cice, hsnow, nullptr, nullptr, tice);
+    }
+    // Cells are independent: cut them into chunks and run upload -> sweeps -> download as a
+    // three-stage pipeline over three streams, so that both PCIe directions and the SMs work at
+    // the same time (the call is bound by the 14-array upload).
+    NSDG_REQUIRE(ctx, dt > 0, NSDG_EINVAL, "dt must be > 0");
+    const double* in[14] = { hice, cice, hsnow, sst, sss, tice, tair, tdew, slp, qsw, qlw, mld, snowfall, wind };
+    const int inf[14] = { NSDG_TF_HICE, NSDG_TF_CICE, NSDG_TF_HSNOW, NSDG_TF_SST, NSDG_TF_SSS, NSDG_TF_TICE0,
+        NSDG_TF_TAIR, NSDG_TF_TAIR + 1, NSDG_TF_TAIR + 2, NSDG_TF_TAIR + 3, NSDG_TF_TAIR + 4,
+        NSDG_TF_TAIR + 5, NSDG_TF_TAIR + 6, NSDG_TF_TAIR + 7 };
+    for (const double* a : in)
+        NSDG_REQUIRE(ctx, a, NSDG_EINVAL, "null host array");
+    double* out[4] = { hice, cice, hsnow, tice };
+    const int outf[4] = { NSDG_TF_HICE, NSDG_TF_CICE, NSDG_TF_HSNOW, NSDG_TF_TICE0 };
+    const int nchunks = 8;
+    const int64_t per = ((t->n + nchunks - 1) / nchunks + 255) / 256 * 256;
+    const double idt = 1. / dt;
+    NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->stream)); // earlier work on the fields is finished
+    for (int64_t c0 = 0; c0 < t->n; c0 += per) {
+        const int64_t cn = std::min<int64_t>(per, t->n - c0);
+        for (int q = 0; q < 14; ++q)
+            NSDG_CUDA(ctx, cudaMemcpyAsync(t->fields[inf[q]] + c0, in[q] + c0, sizeof(double) * (size_t)cn,
+                               cudaMemcpyHostToDevice, ctx->h2d_stream));
+        NSDG_CUDA(ctx, cudaEventRecord(ctx->ev_pipe[0], ctx->h2d_stream));
+        NSDG_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_pipe[0], 0));
+        ThermoPtrs p;
+        for (int q = 0; q < NSDG_TF_COUNT; ++q)
+            p.f[q] = t->fields[q] + c0;
+        p.diag = nullptr;
+        const unsigned grid = (unsigned)((cn + 255) / 256);
+        for (int s = 0; s < nsteps; ++s) {
+            nsdg_prof_begin(ctx, NSDG_K_THERMO);
+            if (t->slab_ocean)
+                thermo_kernel<false, true><<<grid, 256, 0, ctx->stream>>>(t->params, p, dt, idt, cn);
+            else
+                thermo_kernel<false, false><<<grid, 256, 0, ctx->stream>>>(t->params, p, dt, idt, cn);
+            nsdg_prof_end(ctx);
+            NSDG_LAUNCHED(ctx);
+        }
+        NSDG_CUDA(ctx, cudaEventRecord(ctx->ev_pipe[1], ctx->stream));
+        NSDG_CUDA(ctx, cudaStreamWaitEvent(ctx->d2h_stream, ctx->ev_pipe[1], 0));
+        for (int q = 0; q < 4; ++q)
+            NSDG_CUDA(ctx, cudaMemcpyAsync(out[q] + c0, t->fields[outf[q]] + c0, sizeof(double) * (size_t)cn,
+                               cudaMemcpyDeviceToHost, ctx->d2h_stream));
+    }
+    t->have_prog = t->have_forcing = true;
+    NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->d2h_stream));
+    NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return NSDG_OK;
 }
 
 } // extern "C"
