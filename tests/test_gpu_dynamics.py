@@ -266,6 +266,41 @@ def test_size_independent_properties_large_grid(ctx):
     assert np.array_equal(dyn2.download("H")[0], H[0])
 
 
+def test_full_size_4096sq_is_the_tiled_small_problem(ctx):
+    """BASELINE configs[2] size.  A periodic 4096^2 problem whose inputs are a 256^2 periodic
+    problem tiled 16 x 16 must reproduce the tiled 256^2 solution BIT FOR BIT (every cell sees the
+    same neighbourhood; tile, wave and wrap position must not matter), and the 256^2 solution is
+    within tolerance of the oracle: the full-size run is pinned to the oracle through both."""
+    m, reps, nsub = 256, 16, 8
+    n = m * reps
+    F, hx, hy = S.box_case(m, m, 6)
+    F["U"], F["V"] = random_velocity(m, m, 17, 0.05)
+    r = np.random.default_rng(23)
+    for k in ("S11", "S12", "S22"):
+        F[k] = 30.0 * r.standard_normal((3, m, m))
+    mp = MevpParams.defaults()
+    mp.bc = BC_PERIODIC
+    names = ("H", "A", "U", "V", "S11", "S12", "S22")
+    small = GpuDynamics(ctx, m, m, hx, hy, 6, mevp=mp)
+    small.upload_all(F)
+    small.step(120.0, nsub)
+    got_small = {k: small.download(k) for k in names}
+    ref = O.dyn_step(mp, *[F[k] for k in names], F["UATM"], F["VATM"], F["UOCN"], F["VOCN"], hx, hy,
+                     120.0, nsub)
+    for k, a in zip(names, ref):
+        assert maxrel(got_small[k], a) < RTOL, k
+    big = GpuDynamics(ctx, n, n, hx, hy, 6, mevp=mp)
+    big.upload_all({k: np.tile(v, (1, reps, reps) if v.ndim == 3 else (reps, reps)) for k, v in F.items()})
+    big.step(120.0, nsub)
+    for k in names:
+        a = big.download(k)
+        t = np.tile(got_small[k], (1, reps, reps) if a.ndim == 3 else (reps, reps))
+        assert np.array_equal(a, t), k
+    mH = big.mass("H")
+    big.step(120.0, nsub)
+    assert abs(big.mass("H") - mH) / mH < 1e-13
+
+
 def test_error_behaviour(ctx):
     with pytest.raises(NsdgError):
         GpuDynamics(ctx, 16, 16, 1.0, 1.0, ncomp=4)
