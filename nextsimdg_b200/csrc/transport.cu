@@ -79,8 +79,13 @@ struct StageArgs {
     const double* v;
     double a, b, dt, ihx, ihy;
     int nx, nyl, plane, r0, r1;
-    int wrap;
+    int wrap, prefetch;
 };
+
+__device__ __forceinline__ void prefetch_line(const double* p)
+{
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+}
 
 // one tracer per blockIdx.z (the velocity reads of the second tracer hit L2): half the registers
 // of a two-tracer thread, so three CTAs instead of one fit an SM
@@ -104,6 +109,23 @@ __global__ void __launch_bounds__(256, MINB) transport_stage_kernel(const __grid
     const int ip = (i == A.nx - 1) ? 0 : i + 1;
     const int k = r * A.nx + i;
     const int f = blockIdx.z;
+    if (NC == 6 && A.prefetch) {
+        // the kernel is latency bound with 24 warps per SM and cannot keep all 36 loads of a
+        // thread in flight in 80 registers: pull the streams that are used last (the RK base, the
+        // rows above and below the CTA) towards L1/L2 now, without holding registers
+        if (HAS_BASE)
+#pragma unroll
+            for (int q = 0; q < NC; ++q)
+                prefetch_line(A.base[f] + q * A.plane + k);
+        if (threadIdx.y == 0)
+#pragma unroll
+            for (int q = 0; q < NC; ++q)
+                prefetch_line(A.src[f] + q * A.plane + rm * A.nx + i);
+        if (threadIdx.y == blockDim.y - 1)
+#pragma unroll
+            for (int q = 0; q < NC; ++q)
+                prefetch_line(A.src[f] + q * A.plane + rp * A.nx + i);
+    }
 
     const double u00 = __ldg(A.u + r * A.nx + i), u10 = __ldg(A.u + r * A.nx + ip);
     const double u01 = __ldg(A.u + rp * A.nx + i), u11 = __ldg(A.u + rp * A.nx + ip);
@@ -390,6 +412,12 @@ int nsdg_transport_stage(nsdg_ctx* ctx, int nfields, double* const* src, double*
     A.r0 = (int)r0;
     A.r1 = (int)r1;
     A.wrap = d->wrap ? 1 : 0;
+    static int pf = -1; // NSDG_TRANSPORT_PREFETCH=0/1 (tuning)
+    if (pf < 0) {
+        const char* e = getenv("NSDG_TRANSPORT_PREFETCH");
+        pf = e ? atoi(e) : 1;
+    }
+    A.prefetch = pf;
     dim3 block(64, 4);
     dim3 grid((unsigned)((d->nx + 63) / 64), (unsigned)((r1 - r0 + 3) / 4), (unsigned)nfields);
     const bool hb = base != nullptr;
@@ -397,7 +425,7 @@ int nsdg_transport_stage(nsdg_ctx* ctx, int nfields, double* const* src, double*
     static int minb = 0; // NSDG_TRANSPORT_MINB: resident-CTA target of the dG2 register budget (tuning)
     if (!minb) {
         const char* e = getenv("NSDG_TRANSPORT_MINB");
-        minb = e ? atoi(e) : 3;
+        minb = e ? atoi(e) : 4;
     }
     if (d->nc == 1)
         launch_stage<1, 4>(A, hb, grid, block, ctx->stream);
@@ -407,6 +435,8 @@ int nsdg_transport_stage(nsdg_ctx* ctx, int nfields, double* const* src, double*
         launch_stage<6, 1>(A, hb, grid, block, ctx->stream);
     else if (minb == 3)
         launch_stage<6, 3>(A, hb, grid, block, ctx->stream);
+    else if (minb == 4)
+        launch_stage<6, 4>(A, hb, grid, block, ctx->stream);
     else
         launch_stage<6, 2>(A, hb, grid, block, ctx->stream);
     nsdg_prof_end(ctx);
