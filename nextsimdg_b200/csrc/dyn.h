@@ -25,7 +25,7 @@ struct DynState {
     double* stage1[2] = {};
     double* stage2[2] = {};
     // per-step mEVP work arrays
-    double* pg = nullptr; // ice strength at the 2x2 Gauss points, 4 planes
+    double* pg = nullptr; // HALF the ice strength (P/2) at the 2x2 Gauss points, 4 planes
     double* nd = nullptr; // per-node constants of the sub-cycle, 4 planes: cx0, cy0, mdt, acd
     double* s2[3] = {}; // ping-pong partners of S11, S12, S22 (fused sub-iteration)
     double* u2 = nullptr; // ping-pong partner of U,V

@@ -34,6 +34,7 @@ struct MevpArgs {
     int nx, nyl, plane, r0, r1, j0;
     int wrap, nc, bc, ny_global;
     double ihx, ihy, ie2, dmin2, ia; // stress: 1/hx, 1/hy, 1/e^2, Delta_min^2, 1/alpha
+    double hx2, hy2, hx4, hy4, ome, e2x2, oma, ia4, ia3g; // products of the above (stress_relax)
     double c1, c2, c3, c4; // divergence: 0.5/hx, 1/(12 hx), 0.5/hy, 1/(12 hy)
     double beta, beta1, dtf; // beta, 1+beta, dt*f
     double p_star, c_star, rho_ice, h_min, idt, car, cor, fcor; // prepare kernels
@@ -98,7 +99,8 @@ __device__ __forceinline__ double eval_dg(const double* f, int plane, int k, int
     return s;
 }
 
-// ice strength at the Gauss points: out0 = pg (4 planes), g = 2*b + a
+// HALF the ice strength at the Gauss points (the VP law only ever uses P/2): out0 = pg (4 planes),
+// g = 2*b + a
 __global__ void __launch_bounds__(256) pressure_kernel(const __grid_constant__ MevpArgs A)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -113,7 +115,7 @@ __global__ void __launch_bounds__(256) pressure_kernel(const __grid_constant__ M
             const double xa = a ? GQ : -GQ, yb = b ? GQ : -GQ;
             double h = eval_dg(A.H, A.plane, k, A.nc, xa, yb);
             double c = eval_dg(A.A, A.plane, k, A.nc, xa, yb);
-            A.out0[(2 * b + a) * A.plane + k] = A.p_star * h * exp(-A.c_star * (1. - c));
+            A.out0[(2 * b + a) * A.plane + k] = (0.5 * A.p_star) * h * exp(-A.c_star * (1. - c));
         }
 }
 
@@ -144,68 +146,57 @@ __global__ void __launch_bounds__(256) nodal_kernel(const __grid_constant__ Mevp
 
 // ---- arithmetic shared by all sub-iteration kernels ------------------------------------------
 
-// L2 projection to dG1 of the viscous-plastic stress of the bilinear velocity (u00..v11 at the
-// cell's corner nodes) evaluated at the 2x2 Gauss points with strengths pr[g], g = 2*b + a
-__device__ __forceinline__ void stress_project(const MevpArgs& A, double u00, double u10, double u01, double u11,
-    double v00, double v10, double v01, double v11, const double (&pr)[4], double (&p11)[3],
-    double (&p12)[3], double (&p22)[3])
+// S <- S + (proj - S)/alpha, where proj is the L2 projection to dG1 of the viscous-plastic stress
+// of the bilinear velocity (u00..v11 at the cell's corner nodes) evaluated at the 2x2 Gauss points
+// with HALF strengths hp[g] = P_g/2, g = 2*b + a.  Every product of constants is taken on the
+// host (hx2 = 1/(2hx), hx4 = 1/(4hx), ome = 1 - 1/e^2, e2x2 = 2/e^2, oma = 1 - 1/alpha,
+// ia4 = 1/(4 alpha), ia3g = 3 GQ/alpha), which removes 29 of ~190 FP64 instructions per call.
+__device__ __forceinline__ void stress_relax(const MevpArgs& A, double u00, double u10, double u01, double u11,
+    double v00, double v10, double v01, double v11, const double (&hp)[4], double (&so11)[3],
+    double (&so12)[3], double (&so22)[3])
 {
     // dG1 coefficients (mean, xi, eta) of the strain rates, exact for bilinear velocity
     const double ax = u10 - u00, bx = u11 - u01, cyy = u01 - u00, dyy = u11 - u10;
     const double avx = v10 - v00, bvx = v11 - v01, cvy = v01 - v00, dvy = v11 - v10;
-    const double e11_0 = 0.5 * (ax + bx) * A.ihx, e11_2 = (bx - ax) * A.ihx;
-    const double e22_0 = 0.5 * (cvy + dvy) * A.ihy, e22_1 = (dvy - cvy) * A.ihy;
-    const double e12_0 = 0.5 * (0.5 * (cyy + dyy) * A.ihy + 0.5 * (avx + bvx) * A.ihx);
-    const double e12_1 = 0.5 * (dyy - cyy) * A.ihy, e12_2 = 0.5 * (bvx - avx) * A.ihx;
+    const double e11_0 = (ax + bx) * A.hx2, e11_2 = (bx - ax) * A.ihx;
+    const double e22_0 = (cvy + dvy) * A.hy2, e22_1 = (dvy - cvy) * A.ihy;
+    const double e12_0 = (cyy + dyy) * A.hy4 + (avx + bvx) * A.hx4;
+    const double e12_1 = (dyy - cyy) * A.hy2, e12_2 = (bvx - avx) * A.hx2;
     double s11[4], s12[4], s22[4];
 #pragma unroll
     for (int b = 0; b < 2; ++b) {
         const double yb = b ? GQ : -GQ;
         const double g11 = e11_0 + e11_2 * yb; // e11 varies with eta only
+        const double g12b = e12_0 + e12_2 * yb;
 #pragma unroll
         for (int a = 0; a < 2; ++a) {
             const double xa = a ? GQ : -GQ;
             const double g22 = e22_0 + e22_1 * xa; // e22 varies with xi only
-            const double g12 = e12_0 + e12_1 * xa + e12_2 * yb;
+            const double g12 = g12b + e12_1 * xa;
             const double tr = g11 + g22, df = g11 - g22;
             // zeta = P/(2 Delta) with one reciprocal square root instead of sqrt + divide
-            const double hp = 0.5 * pr[2 * b + a];
-            const double zeta = hp * rsqrt_pos(A.dmin2 + tr * tr + A.ie2 * (df * df + 4. * g12 * g12));
-            const double eta = zeta * A.ie2;
-            const double iso = (zeta - eta) * tr - hp;
-            const double eta2 = 2. * eta;
+            const double h = hp[2 * b + a];
+            const double zeta = h * rsqrt_pos(A.dmin2 + tr * tr + A.ie2 * (df * df + 4. * g12 * g12));
+            const double iso = (zeta * tr) * A.ome - h; // (zeta - eta) tr - P/2, eta = zeta/e^2
+            const double eta2 = zeta * A.e2x2;
             s11[2 * b + a] = eta2 * g11 + iso;
             s22[2 * b + a] = eta2 * g22 + iso;
             s12[2 * b + a] = eta2 * g12;
         }
     }
-    // (s, psi_c)/(psi_c, psi_c): weights 1/4, +-3 GQ, +-3 GQ at the points (-,-) (+,-) (-,+) (+,+)
-#define NSDG_PROJ(p, s)                                                                           \
+    // (s, psi_c)/(psi_c, psi_c): weights 1/4, +-3 GQ, +-3 GQ at the points (-,-) (+,-) (-,+) (+,+);
+    // relaxation folded in: S_c <- (1 - 1/alpha) S_c + proj_c/alpha
+#define NSDG_RELAX(so, s)                                                                         \
     do {                                                                                          \
         const double lo = s[0] + s[1], hi = s[2] + s[3];                                          \
-        p[0] = 0.25 * (lo + hi);                                                                  \
-        p[1] = (3. * GQ) * ((s[1] - s[0]) + (s[3] - s[2]));                                       \
-        p[2] = (3. * GQ) * (hi - lo);                                                             \
+        so[0] = (lo + hi) * A.ia4 + so[0] * A.oma;                                                \
+        so[1] = ((s[1] - s[0]) + (s[3] - s[2])) * A.ia3g + so[1] * A.oma;                         \
+        so[2] = (hi - lo) * A.ia3g + so[2] * A.oma;                                               \
     } while (0)
-    NSDG_PROJ(p11, s11);
-    NSDG_PROJ(p12, s12);
-    NSDG_PROJ(p22, s22);
-#undef NSDG_PROJ
-}
-
-// S <- S + (proj - S)/alpha
-__device__ __forceinline__ void stress_relax(const MevpArgs& A, double u00, double u10, double u01, double u11,
-    double v00, double v10, double v01, double v11, const double (&pr)[4], double (&so11)[3],
-    double (&so12)[3], double (&so22)[3])
-{
-    double p11[3], p12[3], p22[3];
-    stress_project(A, u00, u10, u01, u11, v00, v10, v01, v11, pr, p11, p12, p22);
-#pragma unroll
-    for (int c = 0; c < 3; ++c) {
-        so11[c] += A.ia * (p11[c] - so11[c]);
-        so12[c] += A.ia * (p12[c] - so12[c]);
-        so22[c] += A.ia * (p22[c] - so22[c]);
-    }
+    NSDG_RELAX(so11, s11);
+    NSDG_RELAX(so12, s12);
+    NSDG_RELAX(so22, s22);
+#undef NSDG_RELAX
 }
 
 // -(S, grad phi_n)/(hx hy) at a node from the 7 stress coefficients (S11_0, S11_2, S12_0, S12_1,
@@ -602,6 +593,15 @@ MevpArgs base_args(DynState* d, double dt)
     A.ie2 = 1. / (P.ellipse_e * P.ellipse_e);
     A.dmin2 = P.delta_min * P.delta_min;
     A.ia = 1. / P.alpha;
+    A.hx2 = 0.5 * A.ihx;
+    A.hy2 = 0.5 * A.ihy;
+    A.hx4 = 0.25 * A.ihx;
+    A.hy4 = 0.25 * A.ihy;
+    A.ome = 1. - A.ie2;
+    A.e2x2 = 2. * A.ie2;
+    A.oma = 1. - A.ia;
+    A.ia4 = 0.25 * A.ia;
+    A.ia3g = 3. * GQ * A.ia;
     A.c1 = 0.5 * A.ihx;
     A.c2 = A.ihx * (1. / 12.);
     A.c3 = 0.5 * A.ihy;
