@@ -552,13 +552,178 @@ def run_thermo(args):
     ctx.close()
 
 
+# ---------------------------------------------------------------------------------------------
+# --workload cone: BASELINE configs[1], 1024^2 dG1 rotating-cone advection (periodic, Heun RK2)
+CONE_N = 1024
+CONE_BYTES = (5 * 3 + 4) * 8  # Heun RK2, one dG1 field: 152 B per cell and step
+
+
+def cone_setup():
+    from nextsimdg_b200 import synthetic as S
+    phi, u, v, hx, hy, f0 = S.cone_case(CONE_N, CONE_N, 3)
+    vmax = float(np.sqrt(u * u + v * v).max())
+    dt = (0.1 / 3.0) * hx / vmax  # CFL = 0.1 / (2k + 1), k = 1
+    return phi, u, v, hx, hy, dt
+
+
+def cone_config(n):
+    return {"workload": f"synthetic {CONE_N}x{CONE_N} dG1 rotating-cone advection, periodic BCs, "
+                        f"Heun RK2, {n} GPU(s) (independent replicas for N > 1)",
+            "cells_per_gpu": CONE_N * CONE_N, "cfl": "0.1/3",
+            "l2": "working set 67 MB (field, RK stage, velocity) FITS the 126 MB L2 at this config's own "
+                  "size and is not flushed: consecutive steps of a real run find it there too; the HBM "
+                  "fraction below is therefore not a DRAM utilisation",
+            "parity": "unpinned against draenog/nextsimdg (no transport in the reference snapshot)"}
+
+
+def run_cone_reference(args):
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    from oracle import cpu_oracle as O
+    phi, u, v, hx, hy, dt = cone_setup()
+    O.transport_step(phi, u, v, hx, hy, dt)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        phi = O.transport_step(phi, u, v, hx, hy, dt)
+    secs = time.perf_counter() - t0
+    value = CONE_N * CONE_N * args.steps / secs
+    cores = os.cpu_count() or 1
+    line = {"impl": "reference", "metric": "cell-updates/sec (dG1 transport step)", "value": value,
+            "unit": "cell-updates/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * secs / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": cone_config(args.gpus),
+            "cpu_baseline": {"value": value, "unit": "cell-updates/s", "cores": cores, "kind": "port",
+                             "sample": f"the full {CONE_N}^2 grid, {args.steps} steps, "
+                                       "oracle/dg_transport.c (OpenMP)"},
+            "e2e": {"value": value, "unit": "cell-updates/s", "h2d_bytes_per_step": 0,
+                    "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def run_cone(args):
+    import torch
+    import torch.distributed as dist
+    from nextsimdg_b200.gpu import Context, GpuDynamics
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torchrun")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; this framework has no CPU path")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    ctx = Context(local)
+    phi, u, v, hx, hy, dt = cone_setup()
+    n = CONE_N * CONE_N
+    dyn = GpuDynamics(ctx, CONE_N, CONE_N, hx, hy, 3)
+    dyn.upload_all(dict(H=phi, U=u, V=v))
+    m0 = dyn.mass("H")
+    steps = max(args.steps, 2000)  # a step takes ~30 us: time enough of them for the clocks sampler
+    for _ in range(max(args.warmup, 3)):
+        dyn.transport_step(dt, "H")
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = ctx.launches
+    ctx.timer_start()
+    for _ in range(steps):
+        dyn.transport_step(dt, "H")
+    ms = ctx.timer_stop()
+    launches = ctx.launches - l0
+    barrier()
+    # per-launch times from a short profiled run (the event pairs would perturb the timed one)
+    ctx.profile_begin()
+    for _ in range(50):
+        dyn.transport_step(dt, "H")
+    prof = ctx.profile_end()
+    time.sleep(0.3)
+    clocks = sampler.stop() if rank == 0 else None
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max = float(t.item())
+    value = n * world * steps / (ms_max * 1e-3)
+    drift = abs(dyn.mass("H") - m0) / m0
+    got = dyn.download("H")
+    if not np.isfinite(got).all():
+        raise SystemExit("bench.py: non-finite tracer after the timed steps")
+    e2e_value, h2d, d2h = None, 0, 0
+    if not args.no_e2e:
+        # per step: the field goes up from the host, one step, the field comes down
+        esteps = 50
+        host = np.ascontiguousarray(got)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(esteps):
+            dyn.upload("H", host)
+            dyn.transport_step(dt, "H")
+            host = dyn.download("H")
+        barrier()
+        te = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        e2e_value = n * world * esteps / float(te.item())
+        h2d = d2h = 3 * n * 8
+    if rank == 0:
+        peak, peak_src = peaks()
+        ktot, kcnt = prof["transport_stage_kernel"]
+        kavg = ktot / kcnt
+        kbytes = CONE_BYTES * n / 2.0  # two stage launches per step
+        achieved = kbytes / (kavg * 1e-3) / 1e9
+        cpu = None
+        if args.gpus == 1 and not args.no_cpu:
+            from oracle import cpu_oracle as O
+            p2 = phi
+            t0 = time.perf_counter()
+            for _ in range(20):
+                p2 = O.transport_step(p2, u, v, hx, hy, dt)
+            secs = time.perf_counter() - t0
+            cpu = {"value": n * 20 / secs, "unit": "cell-updates/s", "cores": os.cpu_count() or 1,
+                   "kind": "port", "sample": f"the full {CONE_N}^2 grid, 20 steps, oracle/dg_transport.c"}
+        line = {"metric": "cell-updates/sec (dG1 transport step)", "value": value,
+                "unit": "cell-updates/s", "n_gpus": world, "steps": steps, "warmup": max(args.warmup, 3),
+                "ms_per_step": ms_max / steps, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": cone_config(world),
+                "clocks": clocks,
+                "e2e": {"value": e2e_value, "unit": "cell-updates/s", "h2d_bytes_per_step": h2d,
+                        "d2h_bytes_per_step": d2h,
+                        "what": "nsdg_dyn_upload + nsdg_transport_step + nsdg_dyn_download per step"},
+                "gpu_launches": int(launches), "mass_drift_rel": drift,
+                "roofline": {"bound": "hbm", "kernel": "transport_stage_kernel", "achieved": achieved,
+                             "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                             "peak_source": peak_src, "traffic": None,
+                             "algorithmic_bytes_per_launch": kbytes,
+                             "units_per_launch": f"{n} cells x {CONE_BYTES}/2 B (one of two RK stages)",
+                             "avg_launch_ms": kavg, "launches": kcnt,
+                             "whole_step": {"bytes_per_cell": CONE_BYTES,
+                                            "achieved": CONE_BYTES * n * steps / (ms * 1e-3) / 1e9,
+                                            "frac": CONE_BYTES * n * steps / (ms * 1e-3) / 1e9 / peak}},
+                "cpu_baseline": cpu}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    ctx.close()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="auto", choices=["auto", "16384sq", "thermo"])
+    ap.add_argument("--workload", default="auto", choices=["auto", "16384sq", "thermo", "cone"])
     ap.add_argument("--nx", type=int, default=4096)
     ap.add_argument("--ny", type=int, default=4096, help="rows per GPU")
     ap.add_argument("--e2e-steps", type=int, default=5)
@@ -571,6 +736,8 @@ def main():
     args = ap.parse_args()
     if args.workload == "thermo":
         run_thermo_reference(args) if args.impl == "reference" else run_thermo(args)
+    elif args.workload == "cone":
+        run_cone_reference(args) if args.impl == "reference" else run_cone(args)
     elif args.impl == "reference":
         run_reference(args)
     else:

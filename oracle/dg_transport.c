@@ -5,7 +5,7 @@
  * there is no reference file:line to cite and no golden vector.  This file states the scheme
  * (after Richter et al., GMD 2023, "A dynamical core based on a discontinuous Galerkin method
  * for higher-order finite-element sea ice modeling", sect. on DG advection) and is pinned only
- * by analytic known-answer tests (tests/test_oracle_transport.py): constant preservation, mass
+ * by analytic known-answer tests (tests/test_oracle_dynamics.py): constant preservation, mass
  * conservation, exact translation of polynomials at order k+1, convergence order.
  *
  * Scheme

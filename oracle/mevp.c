@@ -4,7 +4,7 @@
  * reference snapshot, CMakeLists.txt:43-46).  Scheme after Kimmritz et al. (2016) / Bouillon
  * et al. (2013) for mEVP, Richter et al. (GMD 2023) for the CG1-velocity / dG1-stress pairing,
  * and Mehlmann et al. (2021) for the benchmark parameters and momentum equation.  Pinned only
- * by analytic KATs (tests/test_oracle_mevp.py): uniform velocity => zero strain; zero strain =>
+ * by analytic KATs (tests/test_oracle_dynamics.py): uniform velocity => zero strain; zero strain =>
  * stress relaxes to -P/2 I; hand-computed linear-shear strain rates; residual decrease.
  *
  * Discretisation
