@@ -24,9 +24,15 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
-# stdout carries exactly one JSON line: NCCL's own banner ("NCCL version ...", printed to stdout
-# when the box sets NCCL_DEBUG) goes to stderr instead
-os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+# stdout carries exactly ONE JSON line.  Libraries write there too (this image sets
+# NCCL_DEBUG=VERSION and NCCL prints its banner to stdout), so file descriptor 1 is pointed at
+# stderr for the whole run and the JSON line goes to the saved descriptor.
+_JSON_FD = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(line):
+    os.write(_JSON_FD, (json.dumps(line) + "\n").encode())
 
 NSUB = 100
 DT = 120.0
@@ -108,6 +114,31 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def bind_to_gpu_numa_node(local):
+    """Pin this rank (and therefore the pinned host buffers it first-touches) to the CPUs next to
+    its GPU: with 8 ranks on a two-socket host the staging traffic otherwise crosses the socket
+    interconnect.  NSDG_BENCH_NUMA=0 disables.  Returns a short description for the JSON line."""
+    if os.environ.get("NSDG_BENCH_NUMA", "1") == "0":
+        return "off"
+    try:
+        import torch
+        pr = torch.cuda.get_device_properties(local)
+        bdf = f"{pr.pci_domain_id:04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
+        base = f"/sys/bus/pci/devices/{bdf}"
+        node = open(base + "/numa_node").read().strip()
+        cpus = set()
+        for part in open(base + "/local_cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return f"node {node}: no usable cpus"
+        os.sched_setaffinity(0, cpus)
+        return f"node {node}, {len(cpus)} cpus"
+    except Exception as e:  # not fatal: the numbers are just measured unbound
+        return f"unavailable ({type(e).__name__})"
+
+
 def cpu_step(F, hx, hy, mp, nsteps=1):
     """The oracle's restatement of the bench step on the host cores (OpenMP, all threads)."""
     from oracle import cpu_oracle as O
@@ -149,7 +180,7 @@ def run_reference(args):
                                      "snapshot has no dynamics code; this is oracle/ (C, OpenMP)"},
             "e2e": {"value": value, "unit": "cell-updates/s", "h2d_bytes_per_step": 0,
                     "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def workload_config(args, n):
@@ -192,6 +223,7 @@ def run_gpu(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    numa = bind_to_gpu_numa_node(local) if world > 1 else "single rank: not bound"
     ctx = Context(local)
     # ---- grid of this rank
     if args.workload == "16384sq":
@@ -339,7 +371,7 @@ def run_gpu(args):
                 "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": workload_config(args, world), "clocks": clocks,
                 "e2e": {"value": e2e_value, "unit": "cell-updates/s", "h2d_bytes_per_step": h2d,
-                        "d2h_bytes_per_step": d2h, "steps": e2e_steps,
+                        "d2h_bytes_per_step": d2h, "steps": e2e_steps, "host_numa_binding": numa,
                         "what": "nsdg_dyn_step_host_async per step + nsdg_dyn_host_wait inside "
                                 "the timed region: every step uploads its forcing (wind, ocean "
                                 "current) from pinned host memory and downloads the full prognostic "
@@ -354,7 +386,7 @@ def run_gpu(args):
                 "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu,
                 "max_abs_u": umax,
                 "halo_bytes_sent_per_rank": ctx.comm_bytes_sent if world > 1 else 0}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -424,7 +456,7 @@ def run_thermo_reference(args):
                                        f"{args.steps} sweeps", "note": note},
             "e2e": {"value": value, "unit": "cell-updates/s", "h2d_bytes_per_step": 0,
                     "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def run_thermo(args):
@@ -545,7 +577,7 @@ def run_thermo(args):
                              "units_per_launch": f"{n} cells x {THERMO_BYTES} B",
                              "avg_launch_ms": kavg, "launches": kcnt, "share_of_step": ktot / ms},
                 "cpu_baseline": cpu}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -597,7 +629,7 @@ def run_cone_reference(args):
                                        "oracle/dg_transport.c (OpenMP)"},
             "e2e": {"value": value, "unit": "cell-updates/s", "h2d_bytes_per_step": 0,
                     "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def run_cone(args):
@@ -710,7 +742,7 @@ def run_cone(args):
                                             "achieved": CONE_BYTES * n * steps / (ms * 1e-3) / 1e9,
                                             "frac": CONE_BYTES * n * steps / (ms * 1e-3) / 1e9 / peak}},
                 "cpu_baseline": cpu}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
