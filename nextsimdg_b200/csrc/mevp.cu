@@ -217,19 +217,24 @@ __device__ __forceinline__ void stress_div(const MevpArgs& A, const Div7& q, dou
 #undef SUM_AB
 }
 
-// one sub-iteration of the momentum equation at node n (see the header of this file)
-__device__ __forceinline__ void node_update(const MevpArgs& A, int n, double dx, double dy, double u, double v,
-    double& unew, double& vnew)
+// one sub-iteration of the momentum equation at a node (see the header of this file)
+__device__ __forceinline__ void node_update_vals(const MevpArgs& A, double uo, double vo, double cx0, double cy0,
+    double mdt, double acd, double dx, double dy, double u, double v, double& unew, double& vnew)
 {
-    const double uo = __ldg(A.uo + n), vo = __ldg(A.vo + n);
-    const double cx0 = __ldg(A.nd + n), cy0 = __ldg(A.nd + A.plane + n);
-    const double mdt = __ldg(A.nd + 2 * A.plane + n), acd = __ldg(A.nd + 3 * A.plane + n);
     const double du = uo - u, dv = vo - v;
     const double cd = acd * sqrt(du * du + dv * dv);
     const double mb = mdt * A.beta, mf = mdt * A.dtf;
     const double inv = rcp_pos(mdt * A.beta1 + cd);
     unew = (mb * u + cx0 + cd * uo + mf * v + dx) * inv;
     vnew = (mb * v + cy0 + cd * vo - mf * u + dy) * inv;
+}
+__device__ __forceinline__ void node_update(const MevpArgs& A, int n, double dx, double dy, double u, double v,
+    double& unew, double& vnew)
+{
+    const double uo = __ldg(A.uo + n), vo = __ldg(A.vo + n);
+    const double cx0 = __ldg(A.nd + n), cy0 = __ldg(A.nd + A.plane + n);
+    const double mdt = __ldg(A.nd + 2 * A.plane + n), acd = __ldg(A.nd + 3 * A.plane + n);
+    node_update_vals(A, uo, vo, cx0, cy0, mdt, acd, dx, dy, u, v, unew, vnew);
 }
 
 // closed box: the node lines i == 0 and global j == 0 (jrow = plane row - NSDG_GHOST; a strip's
@@ -515,23 +520,40 @@ __global__ void __launch_bounds__(PairCfg<TX, TY>::NT, MINB) mevp_pair_kernel(co
         stress_relax(A, u00, u10, u01, u11, v00, v10, v01, v11, pr, so11, so12, so22);
         div_to_smem(ss, NA, tid, so11, so12, so22);
     }
-    __syncthreads();
-
+    // The node streams of phase B are requested BEFORE the barrier (nothing of phase A's arithmetic
+    // is live any more): their round trip to L2 overlaps the wait for the slowest warp and the
+    // shared-memory gather below instead of starting after them (profiles/r1x_pair_ablation.txt).
     // ---- B: velocity p+1 of node (bx, by) = global column i0-1+bx, interior row r0-2+by
+    const int bx = tid % BX, by = tid / BX;
+    bool b_active = false;
+    double nuo = 0., nvo = 0., ncx = 0., ncy = 0., nmdt = 0., nacd = 0., nub = 0., nvb = 0.;
     if (tid < NB) {
-        const int bx = tid % BX, by = tid / BX;
         const int ni = wrap_idx(i0 - 1 + bx, A.nx);
         int nrow = r0 - 1 + by; // plane row
         if (A.wrap)
             nrow = NSDG_GHOST + wrap_idx(nrow - NSDG_GHOST, A.nyl);
         else
             nrow = min(nrow, A.nyl + 2 * NSDG_GHOST - 1);
-        double un_ = 0., vn_ = 0.;
-        if (!dirichlet(A, ni, nrow - NSDG_GHOST)) {
+        b_active = !dirichlet(A, ni, nrow - NSDG_GHOST);
+        if (b_active) {
             const int n = nrow * A.nx + ni;
+            nuo = __ldg(A.uo + n);
+            nvo = __ldg(A.vo + n);
+            ncx = __ldg(A.nd + n);
+            ncy = __ldg(A.nd + A.plane + n);
+            nmdt = __ldg(A.nd + 2 * A.plane + n);
+            nacd = __ldg(A.nd + 3 * A.plane + n);
+            nub = __ldg(A.u + n);
+            nvb = __ldg(A.v + n);
+        }
+    }
+    __syncthreads();
+    if (tid < NB) {
+        double un_ = 0., vn_ = 0.;
+        if (b_active) {
             double dx, dy;
             div_from_smem(A, ss, NA, by * AX + bx, AX, dx, dy);
-            node_update(A, n, dx, dy, __ldg(A.u + n), __ldg(A.v + n), un_, vn_);
+            node_update_vals(A, nuo, nvo, ncx, ncy, nmdt, nacd, dx, dy, nub, nvb, un_, vn_);
         }
         su1[tid] = un_;
         sv1[tid] = vn_;
@@ -555,24 +577,31 @@ __global__ void __launch_bounds__(PairCfg<TX, TY>::NT, MINB) mevp_pair_kernel(co
             }
         }
     }
+    // ---- D: velocity p+2 of the owned nodes; its node streams are requested before the barrier too
+    const int tx = tid % TX, ty = tid / TX;
+    const int dni = i0 + tx, dnr = r0 + ty;
+    const bool d_owned = tid < TX * TY && dni < A.nx && dnr < A.r1;
+    const bool d_active = d_owned && !dirichlet(A, dni, dnr - NSDG_GHOST);
+    const int dn = dnr * A.nx + dni;
+    if (d_active) {
+        nuo = __ldg(A.uo + dn);
+        nvo = __ldg(A.vo + dn);
+        ncx = __ldg(A.nd + dn);
+        ncy = __ldg(A.nd + A.plane + dn);
+        nmdt = __ldg(A.nd + 2 * A.plane + dn);
+        nacd = __ldg(A.nd + 3 * A.plane + dn);
+    }
     __syncthreads();
-
-    // ---- D: velocity p+2 of the owned nodes
-    if (tid < TX * TY) {
-        const int tx = tid % TX, ty = tid / TX;
-        const int ni = i0 + tx, nr = r0 + ty;
-        if (ni < A.nx && nr < A.r1) {
-            const int n = nr * A.nx + ni;
-            double un_ = 0., vn_ = 0.;
-            if (!dirichlet(A, ni, nr - NSDG_GHOST)) {
-                const int b = (ty + 1) * BX + tx + 1;
-                double dx, dy;
-                div_from_smem(A, ss, NA, (ty + 1) * AX + tx + 1, AX, dx, dy);
-                node_update(A, n, dx, dy, su1[b], sv1[b], un_, vn_);
-            }
-            A.out0[n] = un_;
-            A.out1[n] = vn_;
+    if (d_owned) {
+        double un_ = 0., vn_ = 0.;
+        if (d_active) {
+            const int b = (ty + 1) * BX + tx + 1;
+            double dx, dy;
+            div_from_smem(A, ss, NA, (ty + 1) * AX + tx + 1, AX, dx, dy);
+            node_update_vals(A, nuo, nvo, ncx, ncy, nmdt, nacd, dx, dy, su1[b], sv1[b], un_, vn_);
         }
+        A.out0[dn] = un_;
+        A.out1[dn] = vn_;
     }
 }
 
