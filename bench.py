@@ -68,7 +68,7 @@ class ClockSampler:
 
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+         "clocks_event_reasons.sw_power_cap,power.draw,power.limit")
 
     def __init__(self, index):
         self.index, self.proc, self.lines = index, None, []
@@ -96,7 +96,7 @@ class ClockSampler:
             self.proc.wait(timeout=5)
         except Exception:
             self.proc.kill()
-        sm, mx, reasons = [], None, set()
+        sm, mx, reasons, pw, plim = [], None, set(), [], None
         names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
         for ln in self.lines:
             f = [x.strip() for x in ln.split(",")]
@@ -110,8 +110,14 @@ class ClockSampler:
             for nm, val in zip(names, f[2:6]):
                 if val.lower().startswith("active"):
                     reasons.add(nm)
+            try:
+                pw.append(float(f[6]))
+                plim = float(f[7])
+            except (IndexError, ValueError):
+                pass
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm),
+                "power_w": float(np.median(pw)) if pw else None, "power_limit_w": plim}
 
 
 def bind_to_gpu_numa_node(local):
