@@ -266,6 +266,30 @@ def test_size_independent_properties_large_grid(ctx):
     assert np.array_equal(dyn2.download("H")[0], H[0])
 
 
+@pytest.mark.parametrize("ncomp,order", [(1, 1), (3, 2), (6, 3)])
+def test_gpu_transport_convergence_against_the_analytic_solution(ctx, ncomp, order):
+    """Independent of the oracle: uniform flow on the periodic unit square translates a smooth
+    field exactly; the CUDA transport must converge to the shifted field at order k + 1, and
+    reach a small absolute error at 256^2 (dG2: < 1e-7)."""
+    def smooth(x, y):
+        return 1.0 + 0.5 * np.sin(2 * np.pi * x) * np.cos(2 * np.pi * y)
+
+    errs, T = [], 0.1
+    for n in (64, 128, 256):
+        hx = hy = 1.0 / n
+        dyn = GpuDynamics(ctx, n, n, hx, hy, ncomp)
+        u, v = np.full((n, n), 0.7), np.full((n, n), -0.3)
+        dyn.upload_all(dict(H=S.project(smooth, n, n, hx, hy, ncomp), U=u, V=v))
+        nst = int(round(T / (0.05 * hx)))
+        for _ in range(nst):
+            dyn.transport_step(T / nst, "H")
+        errs.append(S.l2_error(dyn.download("H"), lambda x, y: smooth(x - 0.7 * T, y + 0.3 * T), hx, hy))
+    assert np.log2(errs[0] / errs[1]) > order - 0.15, errs
+    assert np.log2(errs[1] / errs[2]) > order - 0.15, errs
+    if ncomp == 6:
+        assert errs[2] < 1e-7, errs
+
+
 def test_full_size_4096sq_is_the_tiled_small_problem(ctx):
     """BASELINE configs[2] size.  A periodic 4096^2 problem whose inputs are a 256^2 periodic
     problem tiled 16 x 16 must reproduce the tiled 256^2 solution BIT FOR BIT (every cell sees the
