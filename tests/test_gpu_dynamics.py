@@ -266,6 +266,66 @@ def test_size_independent_properties_large_grid(ctx):
     assert np.array_equal(dyn2.download("H")[0], H[0])
 
 
+@pytest.mark.parametrize("flags", [0, DYN_SINGLE_MEVP, DYN_SPLIT_MEVP], ids=["pair", "fused", "split"])
+def test_gpu_mevp_analytic_uniform_flow(ctx, flags):
+    """Independent of the oracle: ice drifting with a uniform ocean current, no wind, no Coriolis,
+    uniform H = 2, A = 1 on a periodic grid.  Zero strain => sigma_VP = -P/2 I, so after n
+    sub-iterations S11_0 = S22_0 = -(P/2)(1 - (1 - 1/alpha)^n), every other coefficient 0, and
+    the velocity does not change (uniform stress has no divergence, no relative drag)."""
+    nx, ny, n = 80, 48, 10
+    mp = MevpParams.defaults()
+    mp.bc = BC_PERIODIC
+    mp.alpha = mp.beta = 300.0
+    mp.f_coriolis = 0.0
+    H = np.zeros((6, ny, nx))
+    H[0] = 2.0
+    A = np.zeros((6, ny, nx))
+    A[0] = 1.0
+    one = np.ones((ny, nx))
+    dyn = GpuDynamics(ctx, nx, ny, 1000.0, 1000.0, 6, mevp=mp, flags=flags)
+    dyn.upload_all(dict(H=H, A=A, U=0.1 * one, V=-0.2 * one, UOCN=0.1 * one, VOCN=-0.2 * one,
+                        UATM=0 * one, VATM=0 * one))
+    dyn.mevp_step(120.0, n)
+    P = mp.p_star * 2.0
+    want = -0.5 * P * (1.0 - (1.0 - 1.0 / mp.alpha) ** n)
+    for k in ("S11", "S22"):
+        s = dyn.download(k)
+        assert np.abs(s[0] / want - 1).max() < 1e-12, k
+        assert np.abs(s[1:]).max() < 1e-9 * P, k
+    assert np.abs(dyn.download("S12")).max() < 1e-9 * P
+    assert np.abs(dyn.download("U") - 0.1).max() < 1e-13
+    assert np.abs(dyn.download("V") + 0.2).max() < 1e-13
+
+
+@pytest.mark.parametrize("flags", [DYN_SINGLE_MEVP, DYN_SPLIT_MEVP], ids=["fused", "split"])
+def test_gpu_mevp_analytic_linear_shear(ctx, flags):
+    """Independent of the oracle: u = g y, v = 0 (away from the periodic seam) has e12 = g/2,
+    e11 = e22 = 0, hence Delta = sqrt(dmin^2 + g^2/e^2), s12 = P g/(2 e^2 Delta), s11 = -P/2;
+    one sub-iteration from S = 0 leaves exactly 1/alpha of it in the dG1 means."""
+    nx, ny, g = 64, 40, 1e-6
+    hx = hy = 1000.0
+    mp = MevpParams.defaults()
+    mp.bc = BC_PERIODIC
+    mp.alpha = mp.beta = 300.0
+    H = np.zeros((6, ny, nx))
+    H[0] = 2.0
+    A = np.zeros((6, ny, nx))
+    A[0] = 1.0
+    yn = (np.arange(ny) * hy)[:, None] + 0.0 * np.arange(nx)[None, :]
+    z = np.zeros((ny, nx))
+    dyn = GpuDynamics(ctx, nx, ny, hx, hy, 6, mevp=mp, flags=flags)
+    dyn.upload_all(dict(H=H, A=A, U=g * yn, V=z, UOCN=z, VOCN=z, UATM=z, VATM=z))
+    dyn.mevp_step(120.0, 1)
+    P = mp.p_star * 2.0
+    delta = np.sqrt(mp.delta_min ** 2 + g * g / mp.ellipse_e ** 2)
+    inner = (slice(1, ny - 1), slice(None))
+    s12, s11, s22 = dyn.download("S12"), dyn.download("S11"), dyn.download("S22")
+    assert np.allclose(s12[0][inner], P * g / (2 * mp.ellipse_e ** 2 * delta) / mp.alpha, rtol=1e-12)
+    assert np.allclose(s11[0][inner], -0.5 * P / mp.alpha, rtol=1e-12)
+    assert np.allclose(s22[0][inner], -0.5 * P / mp.alpha, rtol=1e-12)
+    assert np.abs(s12[1:][:, 1:ny - 1]).max() < 1e-9 * P
+
+
 @pytest.mark.parametrize("ncomp,order", [(1, 1), (3, 2), (6, 3)])
 def test_gpu_transport_convergence_against_the_analytic_solution(ctx, ncomp, order):
     """Independent of the oracle: uniform flow on the periodic unit square translates a smooth
