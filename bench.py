@@ -755,6 +755,12 @@ def run_cone(args):
     ctx.close()
 
 
+def use_all_host_threads():
+    """The CPU arms use every host core; torchrun presets OMP_NUM_THREADS=1 for its workers, which
+    would silently turn the OpenMP oracle into a single-thread run."""
+    os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -772,6 +778,8 @@ def main():
     ap.add_argument("--traffic", type=float, default=None,
                     help="dram bytes per launch of the dominant kernel from an ncu capture")
     args = ap.parse_args()
+    if args.impl == "reference":
+        use_all_host_threads()  # before the oracle library (and its OpenMP runtime) is loaded
     if args.workload == "thermo":
         run_thermo_reference(args) if args.impl == "reference" else run_thermo(args)
     elif args.workload == "cone":
