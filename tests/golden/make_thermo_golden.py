@@ -12,12 +12,19 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 
+CUSTOM_KEYS_INI = (
+    "[nextsim_thermo]\ndrag_ocean_q = 1.7e-3\ndrag_ocean_t = 0.9e-3\ndrag_ice_t = 1.1e-3\n"
+    "albedoW = 0.09\nI_0 = 0.2\nmin_conc = 1e-6\nmin_thick = 0.02\n"
+    "[thermoice0]\nks = 0.28\nflooding = false\n[Hibler]\nh0 = 0.4\nphiM = 0.6\n")
+
 CONFIGS = {
     # name: (freezing, albedo, extra ini)
     "linear_smu": ("LinearFreezing", "SMUIceAlbedo", ""),
     "unesco_ccsm": ("UnescoFreezing", "CCSMIceAlbedo",
                     "[CCSMIceAlbedo]\niceAlbedo = 0.63\nsnowAlbedo = 0.88\n"),
     "linear_smu2": ("LinearFreezing", "SMU2IceAlbedo", ""),
+    # every configuration key of the path away from its default, flooding off
+    "custom_keys": ("UnescoFreezing", "SMUIceAlbedo", CUSTOM_KEYS_INI),
 }
 N, NSTEPS, DT, SEED = 2000, 4, 600.0, 777
 

@@ -44,7 +44,15 @@ def params(name):
                 "Nextsim::IIceAlbedo = Nextsim::CCSMIceAlbedo\n[CCSMIceAlbedo]\n"
                 "iceAlbedo = 0.63\nsnowAlbedo = 0.88\n"),
             "linear_smu2": thermo_params_from_ini(
-                "[Modules]\nNextsim::IIceAlbedo = Nextsim::SMU2IceAlbedo\n")}[name]
+                "[Modules]\nNextsim::IIceAlbedo = Nextsim::SMU2IceAlbedo\n"),
+            "custom_keys": custom_keys_params()}[name]
+
+
+def custom_keys_params():
+    sys.path.insert(0, GOLD)
+    import make_thermo_golden as G
+    return thermo_params_from_ini("[Modules]\nNextsim::IFreezingPoint = Nextsim::UnescoFreezing\n"
+                                  "Nextsim::IIceAlbedo = Nextsim::SMUIceAlbedo\n" + G.CUSTOM_KEYS_INI)
 
 
 def run_gpu(ctx, p, st, fo, dt, nsteps, nlayers=1, diag=False):
@@ -96,7 +104,7 @@ def test_reference_golden_cases(ctx):
     assert g["tice"][0] == pytest.approx(-1.444501803353837, rel=RTOL)
 
 
-@pytest.mark.parametrize("name", ["linear_smu", "unesco_ccsm", "linear_smu2"])
+@pytest.mark.parametrize("name", ["linear_smu", "unesco_ccsm", "linear_smu2", "custom_keys"])
 def test_against_reference_fixtures(ctx, name):
     """Multi-step runs against fixtures generated by the reference's own sources."""
     sys.path.insert(0, GOLD)

@@ -23,8 +23,18 @@ def params(freezing=0, albedo=0, ice=0.538, snow=0.8256):
     return p
 
 
+def custom_keys_params():
+    """Every configuration key of the path away from its default (the INI text the golden
+    generator fed to the reference), parsed by the product's own config reader."""
+    sys.path.insert(0, GOLD)
+    import make_thermo_golden as G
+    from nextsimdg_b200.config import thermo_params_from_ini
+    return thermo_params_from_ini("[Modules]\nNextsim::IFreezingPoint = Nextsim::UnescoFreezing\n"
+                                  "Nextsim::IIceAlbedo = Nextsim::SMUIceAlbedo\n" + G.CUSTOM_KEYS_INI)
+
+
 CONFIGS = {"linear_smu": params(0, 0), "unesco_ccsm": params(1, 2, 0.63, 0.88),
-           "linear_smu2": params(0, 1)}
+           "linear_smu2": params(0, 1), "custom_keys": custom_keys_params()}
 
 
 def one_cell(p, dt, hice, cice, hsnow, sst, sss, tice, tair, tdew, slp, qsw, qlw, mld, snowfall,
@@ -150,7 +160,10 @@ def test_port_matches_reference_fixtures(name):
                 for k in ("qia", "qio", "subl", "dqdt", "hifroms"):
                     np.testing.assert_array_equal(d[k], gold[f"{tag}_s0_{k}"], err_msg=f"{tag} {k}")
     # the fixtures exercise every branch
-    assert np.any(gold["cold_s0_hifroms"] > 0), "flooding branch not covered"
+    if name == "custom_keys":
+        assert not np.any(gold["cold_s0_hifroms"] > 0), "flooding = false must switch snow-ice off"
+    else:
+        assert np.any(gold["cold_s0_hifroms"] > 0), "flooding branch not covered"
     assert np.any(gold["cold_s3_newice"] > 0), "new-ice branch not covered"
     assert np.any(gold["rand_s0_cice"] == 0) and np.any(gold["rand_s3_cice"] > 0)
 
