@@ -11,8 +11,10 @@ self-describing container instead (same names, same dimension order, same elemen
     b"NSDGR1\\n" | uint64 little-endian header length | JSON header | raw little-endian float64
 
 The JSON header holds {"structure": {"type": ...}, "dims": {"x", "y", "nLayers"}, "data":
-[{"name", "dims", "offset", "count"}]}.  `from_netcdf` converts a reference restart when the
-netCDF4 python package is importable (it is not here: the call then raises).  The hidden
+[{"name", "dims", "offset", "count"}]}.  `read_netcdf` / `from_netcdf` read a reference restart
+directly: through the netCDF4 python package when importable, else through `hdf5lite`, this
+package's own reader for the HDF5 subset such files use (it reads the reference's shipped
+`run/dev1.res.nc`; tests/golden/dev1_restart.npz holds what it found there).  The hidden
 per-cell state `newice`, which the reference does not write, is an
 optional extra variable so that a resumed GPU run continues bit-identically.
 """
@@ -82,19 +84,46 @@ def dev_restart(nx=10, nlayers=1):
             "sst": np.full(n, -1.0), "sss": np.full(n, 32.0), "tice": np.full(n * nlayers, -1.0)}
 
 
+def read_netcdf(nc_path):
+    """Read a reference netCDF-4 restart (the layout core/src/DevGridIO.cpp:101-138 reads:
+    group `structure` with attribute `type`, group `data` with hice, cice, hsnow, sst, sss [x][y]
+    and tice [x][y][nLayers]) -> (state, meta) as `read_restart` returns them.  Uses the netCDF4
+    python package when importable, else the built-in HDF5 subset reader (`hdf5lite`), which
+    handles the uncompressed files `run/dev_res.py` style scripts write."""
+    try:
+        import netCDF4
+    except ImportError:
+        netCDF4 = None
+    if netCDF4 is not None:
+        ds = netCDF4.Dataset(nc_path)
+        data = ds.groups["data"]
+        arrays = {k: np.asarray(data.variables[k][:], dtype=np.float64) for k in PROGNOSTIC}
+        structure = ds.groups["structure"].type
+    else:
+        from .hdf5lite import File
+        f = File(nc_path)
+        missing = [k for k in PROGNOSTIC if k not in f.names("/data")]
+        if missing:
+            raise ValueError(f"{nc_path}: group 'data' lacks {missing}")
+        arrays = {k: f.read("/data/" + k).astype(np.float64) for k in PROGNOSTIC}
+        structure = f.attrs("/structure").get("type")
+    if structure != STRUCTURE_TYPE:
+        # core/src/StructureFactory.cpp:41-43 throws std::invalid_argument for an unknown structure
+        raise ValueError(f"{nc_path}: structure type {structure!r}, expected {STRUCTURE_TYPE!r}")
+    if arrays["tice"].ndim != 3:
+        raise ValueError(f"{nc_path}: tice must be [x][y][nLayers]")
+    nx, ny, nl = arrays["tice"].shape
+    for k in PROGNOSTIC[:-1]:
+        if arrays[k].shape != (nx, ny):
+            raise ValueError(f"{nc_path}: {k} has shape {arrays[k].shape}, expected {(nx, ny)}")
+    state = {k: np.ascontiguousarray(a).ravel() for k, a in arrays.items()}
+    return state, {"nx": nx, "ny": ny, "nlayers": nl, "structure": structure}
+
+
 def from_netcdf(nc_path, out_path):
     """Convert a reference netCDF-4 restart (DevGridIO layout) to NSDGR1."""
-    try:
-        import netCDF4  # noqa: F401
-    except ImportError as e:
-        raise RuntimeError("from_netcdf needs the netCDF4 python package, which this image does "
-                           "not have; generate the state with dev_restart() or write_restart()") from e
-    ds = netCDF4.Dataset(nc_path)
-    data = ds.groups["data"]
-    nx, ny = data.dimensions["x"].size, data.dimensions["y"].size
-    nl = data.dimensions["nLayers"].size
-    state = {k: np.asarray(data.variables[k][:], dtype=np.float64).ravel() for k in PROGNOSTIC}
-    write_restart(out_path, state, nx, ny, nl, structure=ds.groups["structure"].type)
+    state, m = read_netcdf(nc_path)
+    write_restart(out_path, state, m["nx"], m["ny"], m["nlayers"], structure=m["structure"])
 
 
 if __name__ == "__main__":

@@ -186,5 +186,40 @@ def test_soa_restart_roundtrip_and_layout(tmp_path):
         f.write(b"XXXX")
     with pytest.raises(ValueError):
         R.read_restart(p)
-    with pytest.raises(RuntimeError):
+    with pytest.raises(OSError):
         R.from_netcdf("/nonexistent.nc", p)
+
+
+def test_reference_restart_file_content_pins_dev1_inputs(tmp_path):
+    """BASELINE configs[0]: what the reference's shipped run/dev1.res.nc holds (extracted by
+    tests/golden/make_dev1_restart_golden.py with hdf5lite) is what dev_restart()/dev1_inputs()
+    synthesise; where the reference tree is present (build container) the file itself is re-read
+    and converted."""
+    from nextsimdg_b200 import hdf5lite, restart as R, synthetic as S
+    g = np.load(os.path.join(ROOT, "tests", "golden", "dev1_restart.npz"))
+    assert tuple(g["dims"]) == (10, 10, 1) and str(g["structure_type"]) == "devgrid"
+    assert set(R.PROGNOSTIC) <= set(g["data_names"].tolist())
+    syn = R.dev_restart(10, 1)
+    st, _ = S.dev1_inputs(100)
+    for k in R.PROGNOSTIC:
+        assert np.array_equal(g[k], syn[k]), k
+        assert np.array_equal(g[k], st["tice0" if k == "tice" else k]), k
+    src = "/root/reference/run/dev1.res.nc"
+    if os.path.exists(src):
+        state, meta = R.read_netcdf(src)
+        assert meta == {"nx": 10, "ny": 10, "nlayers": 1, "structure": "devgrid"}
+        for k in R.PROGNOSTIC:
+            assert np.array_equal(state[k], g[k]), k
+        f = hdf5lite.File(src)
+        assert f.names("/") == ["data", "structure"]
+        assert f.names("/data") == sorted(g["data_names"].tolist())  # 9 links: dense storage
+        assert f.shape("/data/tice") == (10, 10, 1) and f.shape("/data/x") == (10,)
+        out = str(tmp_path / "dev1.nsdgr")
+        R.from_netcdf(src, out)
+        back, m2 = R.read_restart(out)
+        assert m2 == meta and all(np.array_equal(back[k], state[k]) for k in R.PROGNOSTIC)
+    # not HDF5 / unsupported features fail loudly
+    bad = tmp_path / "bad.nc"
+    bad.write_bytes(b"CDF\x01" + b"\0" * 64)
+    with pytest.raises(hdf5lite.Hdf5Unsupported):
+        hdf5lite.File(str(bad))
