@@ -293,6 +293,39 @@ def test_restart_write_resume_is_bit_identical(ctx, tmp_path):
     assert np.array_equal(resumed.get_newice(), want_ni)
 
 
+def test_dev1_config_end_to_end(ctx, tmp_path):
+    """BASELINE configs[0]: run/dev1.cfg with the content of the reference's dev1.res.nc
+    (tests/golden/dev1_restart.npz, extracted from the shipped file) through run.run_config:
+    restart -> SoA -> GPU step -> restart.  Pins: SURVEY.md 8c (compiled reference)."""
+    from nextsimdg_b200 import restart as R, run as RUN
+    g = np.load(os.path.join(GOLD, "dev1_restart.npz"))
+    nx, ny, nl = (int(x) for x in g["dims"])
+    R.write_restart(str(tmp_path / "dev1.nsdgr"), {k: g[k] for k in R.PROGNOSTIC}, nx, ny, nl)
+    cfg = tmp_path / "dev1.cfg"  # run/dev1.cfg with the container's file name
+    cfg.write_text("[model]\ninit_file = dev1.nsdgr\nstart = 0\nstop = 1\ntime_step = 1\n")
+    final, plan = RUN.run_config(str(cfg), ctx, base_dir=str(tmp_path))
+    assert plan["nsteps"] == 1
+    pins = {"hice": 0.04668325240678619, "cice": 0.36670813101696548, "hsnow": 0.0,
+            "tice": -1.444501803353837, "sst": -1.0, "sss": 32.0}
+    for k, v in pins.items():
+        assert final[k].shape == (nx * ny * (nl if k == "tice" else 1),)
+        assert np.all(np.abs(final[k] - v) <= ATOL + RTOL * abs(v)), (k, final[k][0], v)
+    back, meta = R.read_restart(str(tmp_path / RUN.FINAL_FILE_NAME))
+    assert meta["nx"] == nx and meta["structure"] == "devgrid"
+    for k in R.PROGNOSTIC:
+        assert np.array_equal(back[k], final[k]), k
+    # a second run resumes from the written restart (t = 1 -> 3, two more steps) and equals
+    # three steps of the oracle from the initial file
+    cfg.write_text("[model]\ninit_file = %s\nstart = 1\nrun_length = 2\ntime_step = 1\n"
+                   % RUN.FINAL_FILE_NAME)
+    final3, plan = RUN.run_config(str(cfg), ctx, out_path=str(tmp_path / "r3.nsdgr"),
+                                  base_dir=str(tmp_path))
+    assert plan["nsteps"] == 2
+    st, fo = S.dev1_inputs(nx * ny)
+    ref, _, _ = O.thermo_step(ThermoParams.defaults(), 1.0, 3, st, fo)
+    compare_state(final3, ref, 0)
+
+
 @pytest.mark.parametrize("n", [5000, 300_001])  # the larger one takes the chunked 3-stream pipeline
 def test_run_host_equals_resident_path(ctx, n):
     st, fo = S.thermo_inputs(n, 8)

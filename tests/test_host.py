@@ -223,3 +223,29 @@ def test_reference_restart_file_content_pins_dev1_inputs(tmp_path):
     bad.write_bytes(b"CDF\x01" + b"\0" * 64)
     with pytest.raises(hdf5lite.Hdf5Unsupported):
         hdf5lite.File(str(bad))
+
+
+def test_run_plan_follows_the_reference_iterator():
+    """[model] keys of core/src/Model.cpp:23-29; loop of core/src/Iterator.cpp:57-59."""
+    from nextsimdg_b200 import run as RUN
+    from nextsimdg_b200._abi import FREEZING_KINDS
+    dev1 = "[model]\ninit_file = dev1.res.nc\nstart = 0\nstop = 1\ntime_step = 1\n"  # run/dev1.cfg
+    pl = RUN.plan_from_config(dev1)
+    assert (pl["init_file"], pl["start"], pl["stop"], pl["time_step"], pl["nsteps"]) == \
+        ("dev1.res.nc", 0, 1, 1, 1)
+    # t = 10, 13, 16, 19 < 20: four iterations; run_length wins over stop (Iterator.cpp:42-50)
+    assert RUN.plan_from_config("[model]\nstart=10\nstop=20\ntime_step=3\n")["nsteps"] == 4
+    pl = RUN.plan_from_config("[model]\nstart=10\nstop=20\nrun_length=30\ntime_step=10\n"
+                              "[Modules]\nNextsim::IFreezingPoint = Nextsim::UnescoFreezing\n")
+    assert pl["stop"] == 40 and pl["nsteps"] == 3
+    assert pl["params"].freezing_kind == FREEZING_KINDS["Nextsim::UnescoFreezing"]
+    assert RUN.plan_from_config("[model]\nstart=5\nstop=5\ntime_step=0\n")["nsteps"] == 0
+    assert RUN.plan_from_config("")["nsteps"] == 0
+    with pytest.raises(ValueError):
+        RUN.plan_from_config("[model]\nstart=0\nstop=5\ntime_step=0\n")
+    with pytest.raises(ValueError):
+        RUN.plan_from_config("[model]\nstart=zero\n")
+    with pytest.raises(ValueError):
+        RUN.plan_from_config("[Modules]\nNextsim::IIceAlbedo = Nextsim::NoSuchAlbedo\n")
+    f = RUN.dummy_forcing(3)
+    assert f["qlw"].tolist() == [311.0] * 3 and f["wind"].tolist() == [0.0] * 3
