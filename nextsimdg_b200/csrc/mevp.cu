@@ -605,6 +605,252 @@ __global__ void __launch_bounds__(PairCfg<TX, TY>::NT, MINB) mevp_pair_kernel(co
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Marching pair: the same two sub-iterations per launch, but a WARP owns 28 columns and marches
+// up a band of RY rows; a lane is a column, neighbours in x come through warp shuffles and
+// neighbours in y are the lane's own registers of the previous row.  No shared memory, no
+// barriers, warps free-run.  Step s of the march works on row ra = band start - 2 + s:
+//   A  stress p+1   of cell row ra      (32 lanes valid; u^p rows ra, ra+1)
+//   B  velocity p+1 of node row ra      (lanes 1..31;   S^{p+1} rows ra-1, ra)
+//   C  stress p+2   of cell row ra-1    (lanes 1..30;   u^{p+1} rows ra-1, ra)   -> HBM (owned)
+//   D  velocity p+2 of node row ra-1    (lanes 2..30;   S^{p+2} rows ra-2, ra-1) -> HBM (owned)
+// Lanes 2..29 are owned (28 columns = 7 whole 32-byte sectors per stored row).  Redundant work:
+// 32/28 in x and (RY+3)/RY in y instead of the (19/16)^2, (18/16)^2, (17/16)^2 of the tiled
+// kernel.  The loads of step s+1 are issued at the top of step s (register software pipeline).
+// Same formulas, same operand order as every other sub-iteration kernel: bit-identical results.
+__device__ __forceinline__ int plane_row(const MevpArgs& A, int r)
+{
+    if (A.wrap)
+        return NSDG_GHOST + wrap_idx(r - NSDG_GHOST, A.nyl);
+    return min(r, A.nyl + 2 * NSDG_GHOST - 1);
+}
+
+struct MarchRow {
+    double s11[3], s12[3], s22[3], pg[4]; // S^p and P_g/2 of cell row r
+    double un, vn, unr, vnr; // u^p of node row r+1 (own column; right neighbour, lane 31 only)
+    double uo, vo, cx0, cy0, mdt, acd; // node constants of node row r
+    int k; // r * nx + column
+    bool act; // node (column, r) is not a Dirichlet node
+};
+
+__device__ __forceinline__ void march_load(const MevpArgs& A, int r, int gi, int gip, int lane, MarchRow& R)
+{
+    const int gr = plane_row(A, r), grp = plane_row(A, r + 1);
+    const int k = gr * A.nx + gi;
+    R.k = k;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        R.s11[c] = __ldg(A.S11 + c * A.plane + k);
+        R.s12[c] = __ldg(A.S12 + c * A.plane + k);
+        R.s22[c] = __ldg(A.S22 + c * A.plane + k);
+    }
+#pragma unroll
+    for (int g = 0; g < 4; ++g)
+        R.pg[g] = __ldg(A.pg + g * A.plane + k);
+    R.un = __ldg(A.u + grp * A.nx + gi);
+    R.vn = __ldg(A.v + grp * A.nx + gi);
+    R.unr = R.vnr = 0.;
+    if (lane == 31) {
+        R.unr = __ldg(A.u + grp * A.nx + gip);
+        R.vnr = __ldg(A.v + grp * A.nx + gip);
+    }
+    R.uo = __ldg(A.uo + k);
+    R.vo = __ldg(A.vo + k);
+    R.cx0 = __ldg(A.nd + k);
+    R.cy0 = __ldg(A.nd + A.plane + k);
+    R.mdt = __ldg(A.nd + 2 * A.plane + k);
+    R.acd = __ldg(A.nd + 3 * A.plane + k);
+    R.act = !dirichlet(A, gi, gr - NSDG_GHOST);
+}
+
+__device__ __forceinline__ void prefetch_l2(const double* p)
+{
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+}
+// request the 21 streams march_load(r) reads (no registers held)
+__device__ __forceinline__ void march_prefetch(const MevpArgs& A, int r, int gi)
+{
+    const int k = plane_row(A, r) * A.nx + gi, kn = plane_row(A, r + 1) * A.nx + gi;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        prefetch_l2(A.S11 + c * A.plane + k);
+        prefetch_l2(A.S12 + c * A.plane + k);
+        prefetch_l2(A.S22 + c * A.plane + k);
+    }
+#pragma unroll
+    for (int g = 0; g < 4; ++g)
+        prefetch_l2(A.pg + g * A.plane + k);
+    prefetch_l2(A.u + kn);
+    prefetch_l2(A.v + kn);
+    prefetch_l2(A.uo + k);
+    prefetch_l2(A.vo + k);
+#pragma unroll
+    for (int c = 0; c < 4; ++c)
+        prefetch_l2(A.nd + c * A.plane + k);
+}
+
+__device__ __forceinline__ double from_right(double x, double edge, int lane)
+{
+    const double y = __shfl_down_sync(0xffffffffu, x, 1);
+    return lane == 31 ? edge : y;
+}
+// the 7 divergence coefficients of a cell's stress, in the order Div7 / div_to_smem use
+__device__ __forceinline__ void div7_of(double (&q)[7], const double (&s11)[3], const double (&s12)[3],
+    const double (&s22)[3])
+{
+    q[0] = s11[0];
+    q[1] = s11[2];
+    q[2] = s12[0];
+    q[3] = s12[1];
+    q[4] = s12[2];
+    q[5] = s22[0];
+    q[6] = s22[1];
+}
+// divergence at the lane's node from its own column (below: lo, at the node row: hi) and the
+// column of the lane to the left
+__device__ __forceinline__ void march_div(const MevpArgs& A, const double (&lo)[7], const double (&hi)[7],
+    double& dx, double& dy)
+{
+    Div7 q;
+#pragma unroll
+    for (int c = 0; c < 7; ++c) {
+        q.x10[c] = lo[c];
+        q.x11[c] = hi[c];
+        q.x00[c] = __shfl_up_sync(0xffffffffu, lo[c], 1);
+        q.x01[c] = __shfl_up_sync(0xffffffffu, hi[c], 1);
+    }
+    stress_div(A, q, dx, dy);
+}
+
+constexpr int MARCH_OWN = 28, MARCH_OFF = 2;
+
+template <int RY, int WPB, int MINB, int PF>
+__global__ void __launch_bounds__(WPB * 32, MINB) mevp_march_kernel(const __grid_constant__ MevpArgs A)
+{
+    const int lane = threadIdx.x & 31;
+    const int cb = (blockIdx.x * WPB + (threadIdx.x >> 5)) * MARCH_OWN; // first owned column
+    if (cb >= A.nx)
+        return; // whole warp
+    const int cu = cb - MARCH_OFF + lane; // unwrapped column of this lane
+    const int gi = wrap_idx(cu, A.nx);
+    const int gip = (gi == A.nx - 1) ? 0 : gi + 1;
+    const bool own_col = lane >= MARCH_OFF && lane < MARCH_OFF + MARCH_OWN && cu < A.nx;
+    const int b0 = A.r0 + blockIdx.y * RY; // owned node/cell rows [b0, b1)
+    const int b1 = min(b0 + RY, A.r1);
+    const int nsteps = b1 - b0 + 3;
+
+    // carried from row to row
+    double uc, vc, ucr, vcr; // u^p of node row ra (own, right)
+    double p11[3] = { 0., 0., 0. }, p12[3] = { 0., 0., 0. }, p22[3] = { 0., 0., 0. }; // S^{p+1}, cell row ra-1
+    double ppg[4] = { 0., 0., 0., 0. }; // P_g/2, cell row ra-1
+    double u1p = 0., v1p = 0.; // u^{p+1}, node row ra-1
+    double d2p[7] = { 0., 0., 0., 0., 0., 0., 0. }; // divergence coefficients of S^{p+2}, cell row ra-2
+    double puo = 0., pvo = 0., pcx = 0., pcy = 0., pmdt = 1., pacd = 0.; // node constants, node row ra-1
+    int kp = 0;
+    bool actp = false;
+
+    MarchRow R;
+    {
+        const int g0 = plane_row(A, b0 - 2);
+        uc = __ldg(A.u + g0 * A.nx + gi);
+        vc = __ldg(A.v + g0 * A.nx + gi);
+        ucr = from_right(uc, __ldg(A.u + g0 * A.nx + gip), lane);
+        vcr = from_right(vc, __ldg(A.v + g0 * A.nx + gip), lane);
+    }
+    if (PF == 0)
+        march_load(A, b0 - 2, gi, gip, lane, R);
+    else {
+#pragma unroll 1
+        for (int q = 0; q < PF; ++q)
+            march_prefetch(A, b0 - 2 + q, gi);
+    }
+
+#pragma unroll 1
+    for (int s = 0; s < nsteps; ++s) {
+        const int ra = b0 - 2 + s;
+        MarchRow N;
+        if (PF == 0)
+            march_load(A, ra + 1, gi, gip, lane, N); // consumed by the next step (wasted on the last one)
+        else {
+            // PF > 0: no register pipeline; the rows PF steps ahead are pulled into L2 instead
+            if (s + PF < nsteps)
+                march_prefetch(A, ra + PF, gi);
+            march_load(A, ra, gi, gip, lane, R);
+        }
+
+        // ---- A: stress p+1 of cell row ra
+        const double unr = from_right(R.un, R.unr, lane), vnr = from_right(R.vn, R.vnr, lane);
+        stress_relax(A, uc, ucr, R.un, unr, vc, vcr, R.vn, vnr, R.pg, R.s11, R.s12, R.s22);
+
+        // ---- B: velocity p+1 of node row ra
+        double lo[7], hi[7], dx, dy, u1c, v1c;
+        div7_of(lo, p11, p12, p22);
+        div7_of(hi, R.s11, R.s12, R.s22);
+        march_div(A, lo, hi, dx, dy);
+        node_update_vals(A, R.uo, R.vo, R.cx0, R.cy0, R.mdt, R.acd, dx, dy, uc, vc, u1c, v1c);
+        if (!R.act)
+            u1c = v1c = 0.;
+
+        // ---- C: stress p+2 of cell row ra-1
+        {
+            const double u1pr = __shfl_down_sync(0xffffffffu, u1p, 1), v1pr = __shfl_down_sync(0xffffffffu, v1p, 1);
+            const double u1cr = __shfl_down_sync(0xffffffffu, u1c, 1), v1cr = __shfl_down_sync(0xffffffffu, v1c, 1);
+            stress_relax(A, u1p, u1pr, u1c, u1cr, v1p, v1pr, v1c, v1cr, ppg, p11, p12, p22);
+        }
+        const bool own = own_col && ra - 1 >= b0 && ra - 1 < b1;
+        if (own) {
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                A.S11n[c * A.plane + kp] = p11[c];
+                A.S12n[c * A.plane + kp] = p12[c];
+                A.S22n[c * A.plane + kp] = p22[c];
+            }
+        }
+
+        // ---- D: velocity p+2 of node row ra-1
+        double u2, v2;
+        div7_of(hi, p11, p12, p22);
+        march_div(A, d2p, hi, dx, dy);
+        node_update_vals(A, puo, pvo, pcx, pcy, pmdt, pacd, dx, dy, u1p, v1p, u2, v2);
+        if (!actp)
+            u2 = v2 = 0.;
+        if (own) {
+            A.out0[kp] = u2;
+            A.out1[kp] = v2;
+        }
+
+        // ---- rotate the rows
+#pragma unroll
+        for (int c = 0; c < 7; ++c)
+            d2p[c] = hi[c];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            p11[c] = R.s11[c];
+            p12[c] = R.s12[c];
+            p22[c] = R.s22[c];
+        }
+#pragma unroll
+        for (int g = 0; g < 4; ++g)
+            ppg[g] = R.pg[g];
+        u1p = u1c;
+        v1p = v1c;
+        puo = R.uo;
+        pvo = R.vo;
+        pcx = R.cx0;
+        pcy = R.cy0;
+        pmdt = R.mdt;
+        pacd = R.acd;
+        kp = R.k;
+        actp = R.act;
+        uc = R.un;
+        vc = R.vn;
+        ucr = unr;
+        vcr = vnr;
+        if (PF == 0)
+            R = N;
+    }
+}
+
 MevpArgs base_args(DynState* d, double dt)
 {
     MevpArgs A = {};
@@ -795,10 +1041,34 @@ int pair_tile()
 }
 } // namespace
 
+namespace {
+// NSDG_MEVP_MARCH=<rows per band> selects the marching pair kernel (0 = tiled pair kernel)
+int march_rows()
+{
+    static int ry = -1;
+    if (ry < 0) {
+        const char* e = getenv("NSDG_MEVP_MARCH");
+        ry = e ? atoi(e) : 0;
+        if (ry != 0 && ry != 32 && ry != 64 && ry != 128)
+            ry = 64;
+    }
+    return ry;
+}
+int march_minb()
+{
+    static int m = -1;
+    if (m < 0) {
+        const char* e = getenv("NSDG_MARCH_MINB");
+        m = e ? atoi(e) : 3;
+    }
+    return m;
+}
+} // namespace
+
 int nsdg_mevp_pair_tile_rows()
 {
     static const int ty[6] = { 16, 8, 16, 16, 8, 12 };
-    return ty[pair_tile()];
+    return march_rows() ? march_rows() : ty[pair_tile()];
 }
 
 int nsdg_mevp_pair(nsdg_ctx* ctx, double dt, const double* u, const double* v, double* unew,
@@ -819,6 +1089,43 @@ int nsdg_mevp_pair(nsdg_ctx* ctx, double dt, const double* u, const double* v, d
     const int nrows = (int)(r1 - r0);
     if (nrows <= 0)
         return NSDG_OK;
+    if (const int ry = march_rows()) {
+        constexpr int WPB = 4;
+        const int nwarps = (int)((d->nx + MARCH_OWN - 1) / MARCH_OWN);
+#define NSDG_MARCH_LAUNCH(RY, MINB, PF)                                                              \
+    do {                                                                                          \
+        dim3 block(WPB * 32), grid((unsigned)((nwarps + WPB - 1) / WPB), (unsigned)((nrows + RY - 1) / RY)); \
+        if (st == ctx->stream) {                                                                  \
+            NSDG_KERNEL(ctx, NSDG_K_MEVP_PAIR, (mevp_march_kernel<RY, WPB, MINB, PF><<<grid, block, 0, st>>>(A))); \
+        } else {                                                                                  \
+            mevp_march_kernel<RY, WPB, MINB, PF><<<grid, block, 0, st>>>(A);                      \
+            NSDG_LAUNCHED(ctx);                                                                   \
+        }                                                                                         \
+    } while (0)
+        const int mb = march_minb();
+#define NSDG_MARCH_RY(RY)                                                                         \
+    do {                                                                                          \
+        if (mb == 4)                                                                              \
+            NSDG_MARCH_LAUNCH(RY, 4, 2);                                                          \
+        else if (mb == 2)                                                                         \
+            NSDG_MARCH_LAUNCH(RY, 2, 0);                                                          \
+        else if (mb == 5)                                                                         \
+            NSDG_MARCH_LAUNCH(RY, 5, 2);                                                          \
+        else if (mb == 30)                                                                        \
+            NSDG_MARCH_LAUNCH(RY, 3, 0);                                                          \
+        else                                                                                      \
+            NSDG_MARCH_LAUNCH(RY, 3, 2);                                                          \
+    } while (0)
+        if (ry == 32)
+            NSDG_MARCH_RY(32);
+        else if (ry == 128)
+            NSDG_MARCH_RY(128);
+        else
+            NSDG_MARCH_RY(64);
+#undef NSDG_MARCH_RY
+#undef NSDG_MARCH_LAUNCH
+        return NSDG_OK;
+    }
 #define NSDG_PAIR_LAUNCH(TX, TY, MINB)                                                            \
     do {                                                                                          \
         dim3 block(PairCfg<TX, TY>::NT),                                                          \
