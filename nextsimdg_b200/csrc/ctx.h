@@ -34,6 +34,7 @@ enum NsdgKernelId {
     NSDG_K_VELOCITY,
     NSDG_K_MEVP_FUSED,
     NSDG_K_MEVP_PAIR,
+    NSDG_K_MEVP_MARCH,
     NSDG_K_PACK,
     NSDG_K_UNPACK,
     NSDG_K_BLEND,

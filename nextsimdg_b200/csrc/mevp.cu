@@ -33,6 +33,7 @@ constexpr double GQ = 0.28867513459481287; // 1/(2 sqrt 3)
 struct MevpArgs {
     int nx, nyl, plane, r0, r1, j0;
     int wrap, nc, bc, ny_global;
+    int band; // rows per band of the marching kernel
     double ihx, ihy, ie2, dmin2, ia; // stress: 1/hx, 1/hy, 1/e^2, Delta_min^2, 1/alpha
     double hx2, hy2, hx4, hy4, ome, e2x2, oma, ia4, ia3g; // products of the above (stress_relax)
     double c1, c2, c3, c4; // divergence: 0.5/hx, 1/(12 hx), 0.5/hy, 1/(12 hy)
@@ -200,21 +201,38 @@ __device__ __forceinline__ void stress_relax(const MevpArgs& A, double u00, doub
 }
 
 // -(S, grad phi_n)/(hx hy) at a node from the 7 stress coefficients (S11_0, S11_2, S12_0, S12_1,
-// S12_2, S22_0, S22_1) of its 4 adjacent cells x00 (lower left), x10, x01, x11: with sa = +,-,+,-
-// and sb = +,+,-,- the analytic dG1 x Q1 integrals collapse to signed sums times four constants
+// S12_2, S22_0, S22_1) of its 4 adjacent cells x00 (lower left), x10, x01, x11.  The analytic
+// dG1 x Q1 integrals collapse to signed sums times four constants; they are taken cell column by
+// cell column: with lo / hi the cells below / above the node row in one column,
+//   P = c1 (lo0 + hi0) + c2 (lo1 - hi1) + c4 (lo3 - hi3),   Q = c3 (lo2 - hi2)
+// the column gives P + Q to the node on its right and Q - P to the node on its left (same for y
+// with the coefficients 2, 4, 6 and 5), so that a node needs TWO numbers per direction from its
+// neighbour column (the marching kernel shuffles those instead of 14 coefficients).
+struct ColPart {
+    double lx, ly; // this column is the LEFT column of the node
+    double rx, ry; // this column is the RIGHT column of the node
+};
+__device__ __forceinline__ ColPart col_part(const MevpArgs& A, const double (&lo)[7], const double (&hi)[7])
+{
+    const double px = A.c1 * (lo[0] + hi[0]) + A.c2 * (lo[1] - hi[1]) + A.c4 * (lo[3] - hi[3]);
+    const double qx = A.c3 * (lo[2] - hi[2]);
+    const double py = A.c1 * (lo[2] + hi[2]) + A.c2 * (lo[4] - hi[4]) + A.c4 * (lo[6] - hi[6]);
+    const double qy = A.c3 * (lo[5] - hi[5]);
+    ColPart c;
+    c.lx = px + qx;
+    c.ly = py + qy;
+    c.rx = qx - px;
+    c.ry = qy - py;
+    return c;
+}
 struct Div7 {
     double x00[7], x10[7], x01[7], x11[7];
 };
 __device__ __forceinline__ void stress_div(const MevpArgs& A, const Div7& q, double& dx, double& dy)
 {
-#define SUM_A(c) (q.x00[c] - q.x10[c] + q.x01[c] - q.x11[c]) /* sum sa X */
-#define SUM_B(c) (q.x00[c] + q.x10[c] - q.x01[c] - q.x11[c]) /* sum sb X */
-#define SUM_AB(c) (q.x00[c] - q.x10[c] - q.x01[c] + q.x11[c]) /* sum sa sb X */
-    dx = -(A.c1 * SUM_A(0) + A.c2 * SUM_AB(1) + A.c3 * SUM_B(2) + A.c4 * SUM_AB(3));
-    dy = -(A.c1 * SUM_A(2) + A.c2 * SUM_AB(4) + A.c3 * SUM_B(5) + A.c4 * SUM_AB(6));
-#undef SUM_A
-#undef SUM_B
-#undef SUM_AB
+    const ColPart l = col_part(A, q.x00, q.x01), r = col_part(A, q.x10, q.x11);
+    dx = -(l.lx + r.rx);
+    dy = -(l.ly + r.ry);
 }
 
 // one sub-iteration of the momentum equation at a node (see the header of this file)
@@ -606,17 +624,24 @@ __global__ void __launch_bounds__(PairCfg<TX, TY>::NT, MINB) mevp_pair_kernel(co
 }
 
 // ---------------------------------------------------------------------------------------------
-// Marching pair: the same two sub-iterations per launch, but a WARP owns 28 columns and marches
-// up a band of RY rows; a lane is a column, neighbours in x come through warp shuffles and
-// neighbours in y are the lane's own registers of the previous row.  No shared memory, no
+// Marching pair (default): the same two sub-iterations per launch, but a WARP owns 28 columns
+// and marches up a band of rows; a lane is a column, neighbours in x come through warp shuffles
+// and neighbours in y are the lane's own registers of the previous row.  No shared memory, no
 // barriers, warps free-run.  Step s of the march works on row ra = band start - 2 + s:
 //   A  stress p+1   of cell row ra      (32 lanes valid; u^p rows ra, ra+1)
 //   B  velocity p+1 of node row ra      (lanes 1..31;   S^{p+1} rows ra-1, ra)
 //   C  stress p+2   of cell row ra-1    (lanes 1..30;   u^{p+1} rows ra-1, ra)   -> HBM (owned)
 //   D  velocity p+2 of node row ra-1    (lanes 2..30;   S^{p+2} rows ra-2, ra-1) -> HBM (owned)
 // Lanes 2..29 are owned (28 columns = 7 whole 32-byte sectors per stored row).  Redundant work:
-// 32/28 in x and (RY+3)/RY in y instead of the (19/16)^2, (18/16)^2, (17/16)^2 of the tiled
-// kernel.  The loads of step s+1 are issued at the top of step s (register software pipeline).
+// 32/28 in x and (rows+3)/rows in y instead of the (19/16)^2, (18/16)^2, (17/16)^2 of the tiled
+// kernel; a node needs two numbers per direction from the lane on its left (col_part).
+// The 21 loads of row ra+1 (+2 on lane 31) are issued at the top of step ra and consumed one
+// step later: a register software pipeline.  Three row records rotate through the roles
+// "previous / current / being loaded" (the loop is unrolled by three), so a register that is
+// the target of a load in flight is never copied.  ~240 registers, 8 warps per SM: measured
+// faster than every variant with more resident warps (L2 prefetch instead of the register
+// pipeline, idle values parked in shared memory: profiles/r1z_march_sweep.txt) -- a load that
+// is not a full step ahead costs more than the occupancy buys.
 // Same formulas, same operand order as every other sub-iteration kernel: bit-identical results.
 __device__ __forceinline__ int plane_row(const MevpArgs& A, int r)
 {
@@ -626,9 +651,10 @@ __device__ __forceinline__ int plane_row(const MevpArgs& A, int r)
 }
 
 struct MarchRow {
-    double s11[3], s12[3], s22[3], pg[4]; // S^p and P_g/2 of cell row r
-    double un, vn, unr, vnr; // u^p of node row r+1 (own column; right neighbour, lane 31 only)
+    double s11[3], s12[3], s22[3], pg[4]; // S^p (A: -> S^{p+1}, C: -> S^{p+2}) and P_g/2 of cell row r
+    double un, vn, unr, vnr; // u^p of node row r+1: own column, right neighbour
     double uo, vo, cx0, cy0, mdt, acd; // node constants of node row r
+    double u1, v1; // u^{p+1} of node row r (phase B)
     int k; // r * nx + column
     bool act; // node (column, r) is not a Dirichlet node
 };
@@ -650,7 +676,7 @@ __device__ __forceinline__ void march_load(const MevpArgs& A, int r, int gi, int
     R.un = __ldg(A.u + grp * A.nx + gi);
     R.vn = __ldg(A.v + grp * A.nx + gi);
     R.unr = R.vnr = 0.;
-    if (lane == 31) {
+    if (lane == 31) { // the other lanes take it from their right neighbour (from_right)
         R.unr = __ldg(A.u + grp * A.nx + gip);
         R.vnr = __ldg(A.v + grp * A.nx + gip);
     }
@@ -661,32 +687,6 @@ __device__ __forceinline__ void march_load(const MevpArgs& A, int r, int gi, int
     R.mdt = __ldg(A.nd + 2 * A.plane + k);
     R.acd = __ldg(A.nd + 3 * A.plane + k);
     R.act = !dirichlet(A, gi, gr - NSDG_GHOST);
-}
-
-__device__ __forceinline__ void prefetch_l2(const double* p)
-{
-    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
-}
-// request the 21 streams march_load(r) reads (no registers held)
-__device__ __forceinline__ void march_prefetch(const MevpArgs& A, int r, int gi)
-{
-    const int k = plane_row(A, r) * A.nx + gi, kn = plane_row(A, r + 1) * A.nx + gi;
-#pragma unroll
-    for (int c = 0; c < 3; ++c) {
-        prefetch_l2(A.S11 + c * A.plane + k);
-        prefetch_l2(A.S12 + c * A.plane + k);
-        prefetch_l2(A.S22 + c * A.plane + k);
-    }
-#pragma unroll
-    for (int g = 0; g < 4; ++g)
-        prefetch_l2(A.pg + g * A.plane + k);
-    prefetch_l2(A.u + kn);
-    prefetch_l2(A.v + kn);
-    prefetch_l2(A.uo + k);
-    prefetch_l2(A.vo + k);
-#pragma unroll
-    for (int c = 0; c < 4; ++c)
-        prefetch_l2(A.nd + c * A.plane + k);
 }
 
 __device__ __forceinline__ double from_right(double x, double edge, int lane)
@@ -707,148 +707,112 @@ __device__ __forceinline__ void div7_of(double (&q)[7], const double (&s11)[3], 
     q[6] = s22[1];
 }
 // divergence at the lane's node from its own column (below: lo, at the node row: hi) and the
-// column of the lane to the left
+// column part of the lane to the left
 __device__ __forceinline__ void march_div(const MevpArgs& A, const double (&lo)[7], const double (&hi)[7],
     double& dx, double& dy)
 {
-    Div7 q;
-#pragma unroll
-    for (int c = 0; c < 7; ++c) {
-        q.x10[c] = lo[c];
-        q.x11[c] = hi[c];
-        q.x00[c] = __shfl_up_sync(0xffffffffu, lo[c], 1);
-        q.x01[c] = __shfl_up_sync(0xffffffffu, hi[c], 1);
-    }
-    stress_div(A, q, dx, dy);
+    const ColPart c = col_part(A, lo, hi);
+    dx = -(__shfl_up_sync(0xffffffffu, c.lx, 1) + c.rx);
+    dy = -(__shfl_up_sync(0xffffffffu, c.ly, 1) + c.ry);
 }
 
-constexpr int MARCH_OWN = 28, MARCH_OFF = 2;
+constexpr int MARCH_OWN = 28, MARCH_OFF = 2, MARCH_WPB = 4;
 
-template <int RY, int WPB, int MINB, int PF>
-__global__ void __launch_bounds__(WPB * 32, MINB) mevp_march_kernel(const __grid_constant__ MevpArgs A)
+// One step of the march at row ra.  X: row ra-1 (S^{p+1}, P_g, node constants, u^{p+1}; its
+// un/vn/unr/vnr are u^p of node row ra), Y: the loaded data of row ra, Z: target of the loads of
+// row ra+1.  d2p: divergence coefficients of S^{p+2}, cell row ra-2.  own: this lane stores row
+// ra-1.
+__device__ __forceinline__ void march_step(const MevpArgs& A, int ra, int gi, int gip, int lane, bool own,
+    MarchRow& X, MarchRow& Y, MarchRow& Z, double (&d2p)[7])
+{
+    march_load(A, ra + 1, gi, gip, lane, Z); // consumed by the next step (wasted on the last one)
+
+    // ---- A: stress p+1 of cell row ra
+    Y.unr = from_right(Y.un, Y.unr, lane);
+    Y.vnr = from_right(Y.vn, Y.vnr, lane);
+    stress_relax(A, X.un, X.unr, Y.un, Y.unr, X.vn, X.vnr, Y.vn, Y.vnr, Y.pg, Y.s11, Y.s12, Y.s22);
+
+    // ---- B: velocity p+1 of node row ra
+    double lo[7], hi[7], dx, dy;
+    div7_of(lo, X.s11, X.s12, X.s22);
+    div7_of(hi, Y.s11, Y.s12, Y.s22);
+    march_div(A, lo, hi, dx, dy);
+    node_update_vals(A, Y.uo, Y.vo, Y.cx0, Y.cy0, Y.mdt, Y.acd, dx, dy, X.un, X.vn, Y.u1, Y.v1);
+    if (!Y.act)
+        Y.u1 = Y.v1 = 0.;
+
+    // ---- C: stress p+2 of cell row ra-1
+    {
+        const double u1pr = __shfl_down_sync(0xffffffffu, X.u1, 1), v1pr = __shfl_down_sync(0xffffffffu, X.v1, 1);
+        const double u1cr = __shfl_down_sync(0xffffffffu, Y.u1, 1), v1cr = __shfl_down_sync(0xffffffffu, Y.v1, 1);
+        stress_relax(A, X.u1, u1pr, Y.u1, u1cr, X.v1, v1pr, Y.v1, v1cr, X.pg, X.s11, X.s12, X.s22);
+    }
+    if (own) {
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            A.S11n[c * A.plane + X.k] = X.s11[c];
+            A.S12n[c * A.plane + X.k] = X.s12[c];
+            A.S22n[c * A.plane + X.k] = X.s22[c];
+        }
+    }
+
+    // ---- D: velocity p+2 of node row ra-1
+    double u2, v2;
+    div7_of(hi, X.s11, X.s12, X.s22);
+    march_div(A, d2p, hi, dx, dy);
+    node_update_vals(A, X.uo, X.vo, X.cx0, X.cy0, X.mdt, X.acd, dx, dy, X.u1, X.v1, u2, v2);
+    if (!X.act)
+        u2 = v2 = 0.;
+    if (own) {
+        A.out0[X.k] = u2;
+        A.out1[X.k] = v2;
+    }
+#pragma unroll
+    for (int c = 0; c < 7; ++c)
+        d2p[c] = hi[c];
+}
+
+__global__ void __launch_bounds__(MARCH_WPB * 32, 2) mevp_march_kernel(const __grid_constant__ MevpArgs A)
 {
     const int lane = threadIdx.x & 31;
-    const int cb = (blockIdx.x * WPB + (threadIdx.x >> 5)) * MARCH_OWN; // first owned column
+    const int cb = (blockIdx.x * MARCH_WPB + (threadIdx.x >> 5)) * MARCH_OWN; // first owned column
     if (cb >= A.nx)
         return; // whole warp
     const int cu = cb - MARCH_OFF + lane; // unwrapped column of this lane
     const int gi = wrap_idx(cu, A.nx);
     const int gip = (gi == A.nx - 1) ? 0 : gi + 1;
     const bool own_col = lane >= MARCH_OFF && lane < MARCH_OFF + MARCH_OWN && cu < A.nx;
-    const int b0 = A.r0 + blockIdx.y * RY; // owned node/cell rows [b0, b1)
-    const int b1 = min(b0 + RY, A.r1);
+    const int b0 = A.r0 + blockIdx.y * A.band; // owned node/cell rows [b0, b1)
+    const int b1 = min(b0 + A.band, A.r1);
     const int nsteps = b1 - b0 + 3;
 
-    // carried from row to row
-    double uc, vc, ucr, vcr; // u^p of node row ra (own, right)
-    double p11[3] = { 0., 0., 0. }, p12[3] = { 0., 0., 0. }, p22[3] = { 0., 0., 0. }; // S^{p+1}, cell row ra-1
-    double ppg[4] = { 0., 0., 0., 0. }; // P_g/2, cell row ra-1
-    double u1p = 0., v1p = 0.; // u^{p+1}, node row ra-1
-    double d2p[7] = { 0., 0., 0., 0., 0., 0., 0. }; // divergence coefficients of S^{p+2}, cell row ra-2
-    double puo = 0., pvo = 0., pcx = 0., pcy = 0., pmdt = 1., pacd = 0.; // node constants, node row ra-1
-    int kp = 0;
-    bool actp = false;
-
-    MarchRow R;
+    MarchRow X = {}, Y, Z;
+    X.mdt = 1.;
+    double d2p[7] = { 0., 0., 0., 0., 0., 0., 0. };
     {
         const int g0 = plane_row(A, b0 - 2);
-        uc = __ldg(A.u + g0 * A.nx + gi);
-        vc = __ldg(A.v + g0 * A.nx + gi);
-        ucr = from_right(uc, __ldg(A.u + g0 * A.nx + gip), lane);
-        vcr = from_right(vc, __ldg(A.v + g0 * A.nx + gip), lane);
+        X.un = __ldg(A.u + g0 * A.nx + gi);
+        X.vn = __ldg(A.v + g0 * A.nx + gi);
+        X.unr = from_right(X.un, __ldg(A.u + g0 * A.nx + gip), lane);
+        X.vnr = from_right(X.vn, __ldg(A.v + g0 * A.nx + gip), lane);
     }
-    if (PF == 0)
-        march_load(A, b0 - 2, gi, gip, lane, R);
-    else {
+    march_load(A, b0 - 2, gi, gip, lane, Y);
+    // step s works on row ra = b0 - 2 + s and stores the owned row ra - 1 when 3 <= s; the first
+    // steps run phases C / D on the zero-initialised records (finite values, never stored)
+#define NSDG_STEP(s, X, Y, Z) march_step(A, b0 - 2 + (s), gi, gip, lane, own_col && (s) >= 3, X, Y, Z, d2p)
+    int s = 0;
 #pragma unroll 1
-        for (int q = 0; q < PF; ++q)
-            march_prefetch(A, b0 - 2 + q, gi);
+    for (; s + 2 < nsteps; s += 3) {
+        NSDG_STEP(s, X, Y, Z);
+        NSDG_STEP(s + 1, Y, Z, X);
+        NSDG_STEP(s + 2, Z, X, Y);
     }
-
-#pragma unroll 1
-    for (int s = 0; s < nsteps; ++s) {
-        const int ra = b0 - 2 + s;
-        MarchRow N;
-        if (PF == 0)
-            march_load(A, ra + 1, gi, gip, lane, N); // consumed by the next step (wasted on the last one)
-        else {
-            // PF > 0: no register pipeline; the rows PF steps ahead are pulled into L2 instead
-            if (s + PF < nsteps)
-                march_prefetch(A, ra + PF, gi);
-            march_load(A, ra, gi, gip, lane, R);
-        }
-
-        // ---- A: stress p+1 of cell row ra
-        const double unr = from_right(R.un, R.unr, lane), vnr = from_right(R.vn, R.vnr, lane);
-        stress_relax(A, uc, ucr, R.un, unr, vc, vcr, R.vn, vnr, R.pg, R.s11, R.s12, R.s22);
-
-        // ---- B: velocity p+1 of node row ra
-        double lo[7], hi[7], dx, dy, u1c, v1c;
-        div7_of(lo, p11, p12, p22);
-        div7_of(hi, R.s11, R.s12, R.s22);
-        march_div(A, lo, hi, dx, dy);
-        node_update_vals(A, R.uo, R.vo, R.cx0, R.cy0, R.mdt, R.acd, dx, dy, uc, vc, u1c, v1c);
-        if (!R.act)
-            u1c = v1c = 0.;
-
-        // ---- C: stress p+2 of cell row ra-1
-        {
-            const double u1pr = __shfl_down_sync(0xffffffffu, u1p, 1), v1pr = __shfl_down_sync(0xffffffffu, v1p, 1);
-            const double u1cr = __shfl_down_sync(0xffffffffu, u1c, 1), v1cr = __shfl_down_sync(0xffffffffu, v1c, 1);
-            stress_relax(A, u1p, u1pr, u1c, u1cr, v1p, v1pr, v1c, v1cr, ppg, p11, p12, p22);
-        }
-        const bool own = own_col && ra - 1 >= b0 && ra - 1 < b1;
-        if (own) {
-#pragma unroll
-            for (int c = 0; c < 3; ++c) {
-                A.S11n[c * A.plane + kp] = p11[c];
-                A.S12n[c * A.plane + kp] = p12[c];
-                A.S22n[c * A.plane + kp] = p22[c];
-            }
-        }
-
-        // ---- D: velocity p+2 of node row ra-1
-        double u2, v2;
-        div7_of(hi, p11, p12, p22);
-        march_div(A, d2p, hi, dx, dy);
-        node_update_vals(A, puo, pvo, pcx, pcy, pmdt, pacd, dx, dy, u1p, v1p, u2, v2);
-        if (!actp)
-            u2 = v2 = 0.;
-        if (own) {
-            A.out0[kp] = u2;
-            A.out1[kp] = v2;
-        }
-
-        // ---- rotate the rows
-#pragma unroll
-        for (int c = 0; c < 7; ++c)
-            d2p[c] = hi[c];
-#pragma unroll
-        for (int c = 0; c < 3; ++c) {
-            p11[c] = R.s11[c];
-            p12[c] = R.s12[c];
-            p22[c] = R.s22[c];
-        }
-#pragma unroll
-        for (int g = 0; g < 4; ++g)
-            ppg[g] = R.pg[g];
-        u1p = u1c;
-        v1p = v1c;
-        puo = R.uo;
-        pvo = R.vo;
-        pcx = R.cx0;
-        pcy = R.cy0;
-        pmdt = R.mdt;
-        pacd = R.acd;
-        kp = R.k;
-        actp = R.act;
-        uc = R.un;
-        vc = R.vn;
-        ucr = unr;
-        vcr = vnr;
-        if (PF == 0)
-            R = N;
+    if (s < nsteps) {
+        NSDG_STEP(s, X, Y, Z);
+        if (s + 1 < nsteps)
+            NSDG_STEP(s + 1, Y, Z, X);
     }
+#undef NSDG_STEP
 }
 
 MevpArgs base_args(DynState* d, double dt)
@@ -1042,26 +1006,18 @@ int pair_tile()
 } // namespace
 
 namespace {
-// NSDG_MEVP_MARCH=<rows per band> selects the marching pair kernel (0 = tiled pair kernel)
+// NSDG_MEVP_MARCH=<rows per band> of the marching pair kernel (default 64); 0 selects the tiled
+// pair kernel
 int march_rows()
 {
     static int ry = -1;
     if (ry < 0) {
         const char* e = getenv("NSDG_MEVP_MARCH");
-        ry = e ? atoi(e) : 0;
-        if (ry != 0 && ry != 32 && ry != 64 && ry != 128)
+        ry = e ? atoi(e) : 64;
+        if (ry < 0 || ry > 4096)
             ry = 64;
     }
     return ry;
-}
-int march_minb()
-{
-    static int m = -1;
-    if (m < 0) {
-        const char* e = getenv("NSDG_MARCH_MINB");
-        m = e ? atoi(e) : 3;
-    }
-    return m;
 }
 } // namespace
 
@@ -1090,40 +1046,15 @@ int nsdg_mevp_pair(nsdg_ctx* ctx, double dt, const double* u, const double* v, d
     if (nrows <= 0)
         return NSDG_OK;
     if (const int ry = march_rows()) {
-        constexpr int WPB = 4;
         const int nwarps = (int)((d->nx + MARCH_OWN - 1) / MARCH_OWN);
-#define NSDG_MARCH_LAUNCH(RY, MINB, PF)                                                              \
-    do {                                                                                          \
-        dim3 block(WPB * 32), grid((unsigned)((nwarps + WPB - 1) / WPB), (unsigned)((nrows + RY - 1) / RY)); \
-        if (st == ctx->stream) {                                                                  \
-            NSDG_KERNEL(ctx, NSDG_K_MEVP_PAIR, (mevp_march_kernel<RY, WPB, MINB, PF><<<grid, block, 0, st>>>(A))); \
-        } else {                                                                                  \
-            mevp_march_kernel<RY, WPB, MINB, PF><<<grid, block, 0, st>>>(A);                      \
-            NSDG_LAUNCHED(ctx);                                                                   \
-        }                                                                                         \
-    } while (0)
-        const int mb = march_minb();
-#define NSDG_MARCH_RY(RY)                                                                         \
-    do {                                                                                          \
-        if (mb == 4)                                                                              \
-            NSDG_MARCH_LAUNCH(RY, 4, 2);                                                          \
-        else if (mb == 2)                                                                         \
-            NSDG_MARCH_LAUNCH(RY, 2, 0);                                                          \
-        else if (mb == 5)                                                                         \
-            NSDG_MARCH_LAUNCH(RY, 5, 2);                                                          \
-        else if (mb == 30)                                                                        \
-            NSDG_MARCH_LAUNCH(RY, 3, 0);                                                          \
-        else                                                                                      \
-            NSDG_MARCH_LAUNCH(RY, 3, 2);                                                          \
-    } while (0)
-        if (ry == 32)
-            NSDG_MARCH_RY(32);
-        else if (ry == 128)
-            NSDG_MARCH_RY(128);
-        else
-            NSDG_MARCH_RY(64);
-#undef NSDG_MARCH_RY
-#undef NSDG_MARCH_LAUNCH
+        A.band = ry;
+        dim3 block(MARCH_WPB * 32), grid((unsigned)((nwarps + MARCH_WPB - 1) / MARCH_WPB), (unsigned)((nrows + ry - 1) / ry));
+        if (st == ctx->stream) {
+            NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<<<grid, block, 0, st>>>(A)));
+        } else { /* the per-kernel profiler brackets the compute stream only */
+            mevp_march_kernel<<<grid, block, 0, st>>>(A);
+            NSDG_LAUNCHED(ctx);
+        }
         return NSDG_OK;
     }
 #define NSDG_PAIR_LAUNCH(TX, TY, MINB)                                                            \

@@ -395,3 +395,22 @@ def test_error_behaviour(ctx):
         dyn.transport_step(0.1, "U")
     with pytest.raises(ValueError):
         dyn.upload("H", np.zeros((3, 16, 15)))
+
+
+def test_pair_kernel_variants_bit_identical():
+    """The sub-iteration kernels share their arithmetic: the marching pair kernel (default, band
+    heights 64 / 16 / 5 rows) and the tiled pair kernel give the same bits on periodic and box
+    grids, ragged sizes and a grid narrower than the halo (tools/dyn_digest.py; the variant is
+    chosen per process by NSDG_MEVP_MARCH)."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    digests = {}
+    for march in ("64", "16", "5", "0"):
+        env = dict(os.environ, NSDG_MEVP_MARCH=march)
+        r = subprocess.run([sys.executable, os.path.join(root, "tools", "dyn_digest.py")], env=env,
+                           capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stderr[-2000:]
+        digests[march] = [ln for ln in r.stdout.splitlines() if ln.startswith("digest")][-1]
+    assert len(set(digests.values())) == 1, digests
