@@ -295,8 +295,8 @@ def run_gpu(args):
     # ---- e2e: one C-ABI call per step with HOST (pinned) buffers, nsdg_dyn_step_host: this
     # step's forcing goes up, the full prognostic state comes down, copies overlap the compute;
     # the model state itself stays resident between steps (as DevStep's state stays in memory)
-    e2e_value = e2e_blocking = e2e_full = None
-    h2d = d2h = h2d_full = e2e_steps = 0
+    e2e_value = e2e_blocking = e2e_full = e2e_fields = None
+    h2d = d2h = h2d_full = d2h_fields = e2e_steps = 0
     if not args.no_e2e:
         names = ("H", "A", "U", "V", "S11", "S12", "S22", "UATM", "VATM", "UOCN", "VOCN")
         forcing = ("UATM", "VATM", "UOCN", "VOCN")
@@ -311,7 +311,7 @@ def run_gpu(args):
         # a second set of output buffers: a consumer reads step k's set while step k+1 fills the other
         host2 = {k: torch.empty(host[k].shape, dtype=torch.float64).pin_memory() for k in outs}
 
-        def e2e_run(in_names, nsteps, deferred):
+        def e2e_run(in_names, nsteps, deferred, outs=outs):
             ins = {k: host[k].data_ptr() for k in in_names}
             outp = [{k: host[k].data_ptr() for k in outs}, {k: host2[k].data_ptr() for k in outs}]
             dyn.step_host(DT, NSUB, ins, outp[0])  # untimed first call
@@ -331,6 +331,11 @@ def run_gpu(args):
         h2d = sum(host[k].numel() * 8 for k in forcing)
         d2h = sum(host[k].numel() * 8 for k in outs)
         e2e_value = e2e_run(forcing, e2e_steps, True)
+        # the same with the stress left on the device (it is internal state of the rheology; the
+        # fields other model components read are H, A, U, V)
+        outs_fields = ("H", "A", "U", "V")
+        d2h_fields = sum(host[k].numel() * 8 for k in outs_fields)
+        e2e_fields = e2e_run(forcing, e2e_steps, True, outs_fields)
         e2e_blocking = e2e_run(forcing, min(e2e_steps, 3), False)
         # for transparency: the blocking call with the WHOLE state uploaded every step as well
         h2d_full = sum(host[k].numel() * 8 for k in names)
@@ -399,6 +404,9 @@ def run_gpu(args):
                                 "current) from pinned host memory and downloads the full prognostic "
                                 "state (H, A, U, V, S); the downloads of step k overlap the compute "
                                 "of step k+1; the state stays resident between steps",
+                        "fields_only": {"value": e2e_fields, "d2h_bytes_per_step": d2h_fields,
+                                        "what": "same call, downloads H, A, U, V only (the stress "
+                                                "stays resident as internal state of the rheology)"},
                         "blocking": {"value": e2e_blocking,
                                      "what": "nsdg_dyn_step_host: same copies, each call returns "
                                              "with its outputs on the host"},
