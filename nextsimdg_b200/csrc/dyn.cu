@@ -195,7 +195,7 @@ int mevp_cycle(nsdg_ctx* ctx, double dt, int nsub)
         const char* e = getenv("NSDG_HALO_OVERLAP");
         overlap_env = e ? (atoi(e) != 0) : 1;
     }
-    const int ty = nsdg_mevp_pair_tile_rows();
+    const int ty = nsdg_mevp_pair_tile_rows(ctx);
     const int64_t ntr = (d->nyl + ty - 1) / ty; // tile rows of the strip
     // the two top interior rows are sent up: they must lie inside the last boundary launch
     const int64_t ntop = (d->nyl - (ntr - 1) * ty >= 2) ? 1 : 2;

@@ -81,11 +81,11 @@ int nsdg_mevp_velocity(nsdg_ctx* ctx, double dt, const double* u, const double* 
 int nsdg_mevp_fused(nsdg_ctx* ctx, double dt, const double* u, const double* v, double* unew,
     double* vnew, double* const* Sold, double* const* Snew, int64_t r0, int64_t r1);
 // two sub-iterations in one launch (temporal blocking) on the owned rows [r0,r1); r0 must sit on
-// a tile-row boundary (NSDG_GHOST + k * nsdg_mevp_pair_tile_rows())
+// a tile-row boundary (NSDG_GHOST + k * nsdg_mevp_pair_tile_rows(ctx))
 int nsdg_mevp_pair(nsdg_ctx* ctx, double dt, const double* u, const double* v, double* unew,
     double* vnew, double* const* Sold, double* const* Snew, int64_t r0, int64_t r1,
     cudaStream_t st = nullptr);
-int nsdg_mevp_pair_tile_rows();
+int nsdg_mevp_pair_tile_rows(nsdg_ctx* ctx);
 
 // comm.cu -----------------------------------------------------------------------------------
 // Ring halo exchange of up to 3 plane groups in ONE message per neighbour.  No-op on a single

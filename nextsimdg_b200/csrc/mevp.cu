@@ -23,6 +23,7 @@
 // than 2^31 elements) and every quotient that does not depend on the cell is taken on the host.
 #include "dyn.h"
 #include "fp64_fast.cuh"
+#include <algorithm>
 #include <cstdlib>
 #include <string>
 
@@ -1006,25 +1007,82 @@ int pair_tile()
 } // namespace
 
 namespace {
-// NSDG_MEVP_MARCH=<rows per band> of the marching pair kernel (default 64); 0 selects the tiled
-// pair kernel
-int march_rows()
+// NSDG_MEVP_MARCH=<rows per band> of the marching pair kernel; 0 selects the tiled pair kernel;
+// unset (-1): the band height is chosen per strip by march_auto_rows
+int march_env()
 {
-    static int ry = -1;
-    if (ry < 0) {
+    static int ry = -2;
+    if (ry == -2) {
         const char* e = getenv("NSDG_MEVP_MARCH");
-        ry = e ? atoi(e) : 64;
-        if (ry < 0 || ry > 4096)
-            ry = 64;
+        ry = e ? atoi(e) : -1;
+        if (ry < -1 || ry > 4096)
+            ry = -1;
     }
     return ry;
 }
+
+// Band height of the marching kernel for a strip of nrows x nx cells.  All CTAs of a launch cost
+// the same (rows + 3 march steps) except those of the last, shorter band, and 2 CTAs are resident
+// per SM, so the launch takes whole waves: the cost model is greedy list scheduling of the CTAs in
+// launch order on the CTA slots.  Taller bands have fewer redundant rows; the best height puts the
+// CTAs into full waves (4096^2 on 148 SMs: 8 bands of 512 rows = 296 CTAs = one wave, 0.844 ms
+// against 0.878 ms for 64 bands of 64 rows, profiles/r1z_band_rows.txt).  Strips (multi): the
+// halo exchange starts when the boundary bands are done and its kernels need CTA slots beside the
+// interior bands, so a few slots are left out of the model and a band may take at most a quarter
+// of the launch.
+int march_auto_rows(int64_t nrows, int64_t nx, int sm_count, bool multi)
+{
+    const int64_t gx = ((nx + MARCH_OWN - 1) / MARCH_OWN + MARCH_WPB - 1) / MARCH_WPB;
+    const int64_t slots = std::max<int64_t>(2 * sm_count - (multi ? sm_count / 6 : 0), 1);
+    int best = (int)std::min<int64_t>(nrows, 64);
+    double best_t = 1e300;
+    for (int64_t nb = 1; nb <= nrows; ++nb) {
+        const int64_t ry = (nrows + nb - 1) / nb;
+        if (ry > 1024)
+            continue;
+        if (ry < 32)
+            break;
+        const int64_t full = nrows / ry, rem = nrows - full * ry;
+        const double c = (double)(ry + 3), cr = (double)(rem + 3);
+        const int64_t nfull = full * gx, q = nfull / slots, r = nfull % slots;
+        double t = (double)(q + (r > 0)) * c;
+        if (rem > 0)
+            t = (gx <= slots - r) ? std::max(t, (double)q * c + cr) : (double)(q + 1) * c + cr;
+        if (multi && (t < 4. * c || full + (rem > 0) < 4))
+            continue;
+        if (t < best_t) {
+            best_t = t;
+            best = (int)ry;
+        }
+    }
+    return std::max(best, 1);
+}
+
+int march_rows(nsdg_ctx* ctx)
+{
+    const int e = march_env();
+    if (e >= 0)
+        return e;
+    DynState* d = ctx->dyn;
+    // cached per context geometry (one strip per context)
+    static thread_local nsdg_ctx* c_ctx = nullptr;
+    static thread_local int64_t c_ny = -1, c_nx = -1;
+    static thread_local int c_ry = 64;
+    if (c_ctx != ctx || c_ny != d->nyl || c_nx != d->nx) {
+        c_ctx = ctx;
+        c_ny = d->nyl;
+        c_nx = d->nx;
+        c_ry = march_auto_rows(d->nyl, d->nx, ctx->sm_count, !d->wrap);
+    }
+    return c_ry;
+}
 } // namespace
 
-int nsdg_mevp_pair_tile_rows()
+int nsdg_mevp_pair_tile_rows(nsdg_ctx* ctx)
 {
     static const int ty[6] = { 16, 8, 16, 16, 8, 12 };
-    return march_rows() ? march_rows() : ty[pair_tile()];
+    const int ry = march_rows(ctx);
+    return ry ? ry : ty[pair_tile()];
 }
 
 int nsdg_mevp_pair(nsdg_ctx* ctx, double dt, const double* u, const double* v, double* unew,
@@ -1045,7 +1103,7 @@ int nsdg_mevp_pair(nsdg_ctx* ctx, double dt, const double* u, const double* v, d
     const int nrows = (int)(r1 - r0);
     if (nrows <= 0)
         return NSDG_OK;
-    if (const int ry = march_rows()) {
+    if (const int ry = march_rows(ctx)) {
         const int nwarps = (int)((d->nx + MARCH_OWN - 1) / MARCH_OWN);
         A.band = ry;
         dim3 block(MARCH_WPB * 32), grid((unsigned)((nwarps + MARCH_WPB - 1) / MARCH_WPB), (unsigned)((nrows + ry - 1) / ry));

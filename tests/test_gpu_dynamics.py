@@ -399,7 +399,7 @@ def test_error_behaviour(ctx):
 
 def test_pair_kernel_variants_bit_identical():
     """The sub-iteration kernels share their arithmetic: the marching pair kernel (default, band
-    heights 64 / 16 / 5 rows) and the tiled pair kernel give the same bits on periodic and box
+    heights chosen per grid / 64 / 16 / 5 rows) and the tiled pair kernel give the same bits on periodic and box
     grids, ragged sizes and a grid narrower than the halo (tools/dyn_digest.py; the variant is
     chosen per process by NSDG_MEVP_MARCH)."""
     import os
@@ -407,8 +407,11 @@ def test_pair_kernel_variants_bit_identical():
     import sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     digests = {}
-    for march in ("64", "16", "5", "0"):
-        env = dict(os.environ, NSDG_MEVP_MARCH=march)
+    for march in ("auto", "64", "16", "5", "0"):
+        env = dict(os.environ)
+        env.pop("NSDG_MEVP_MARCH", None)  # auto: band height chosen per grid (march_auto_rows)
+        if march != "auto":
+            env["NSDG_MEVP_MARCH"] = march
         r = subprocess.run([sys.executable, os.path.join(root, "tools", "dyn_digest.py")], env=env,
                            capture_output=True, text=True, timeout=600)
         assert r.returncode == 0, r.stderr[-2000:]
