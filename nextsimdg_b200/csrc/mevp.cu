@@ -1027,13 +1027,13 @@ int march_env()
 // launch order on the CTA slots.  Taller bands have fewer redundant rows; the best height puts the
 // CTAs into full waves (4096^2 on 148 SMs: 8 bands of 512 rows = 296 CTAs = one wave, 0.844 ms
 // against 0.878 ms for 64 bands of 64 rows, profiles/r1z_band_rows.txt).  Strips (multi): the
-// halo exchange starts when the boundary bands are done and its kernels need CTA slots beside the
-// interior bands, so a few slots are left out of the model and a band may take at most a quarter
-// of the launch.
+// halo exchange starts when the boundary bands are done, so a band may take at most a quarter of
+// the launch (4096^2 per rank: 32 bands of 128 rows = four waves; leaving CTA slots out of the
+// model for the exchange kernels was measured slower).
 int march_auto_rows(int64_t nrows, int64_t nx, int sm_count, bool multi)
 {
     const int64_t gx = ((nx + MARCH_OWN - 1) / MARCH_OWN + MARCH_WPB - 1) / MARCH_WPB;
-    const int64_t slots = std::max<int64_t>(2 * sm_count - (multi ? sm_count / 6 : 0), 1);
+    const int64_t slots = std::max<int64_t>(2 * sm_count, 1);
     int best = (int)std::min<int64_t>(nrows, 64);
     double best_t = 1e300;
     for (int64_t nb = 1; nb <= nrows; ++nb) {
