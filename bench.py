@@ -50,7 +50,7 @@ SUBITS_PER_LAUNCH = {"mevp_pair_kernel": 2, "mevp_march_kernel": 2}
 # dram__bytes_read.sum + dram__bytes_write.sum per launch at 4096^2 cells from the ncu --set full
 # captures summarised in profiles/r1t_ncu_full_summary.txt (r1d_... for the fused kernel,
 # r1z_march_ncu_summary.txt for the marching kernel)
-NCU_TRAFFIC_4096SQ = {"mevp_pair_kernel": 4.2719e9, "mevp_march_kernel": 4.3913e9,
+NCU_TRAFFIC_4096SQ = {"mevp_pair_kernel": 4.2719e9, "mevp_march_kernel": 4.2980e9,
                       "mevp_fused_kernel": 4.5397e9,
                       "transport_stage_kernel": 3.7266e9}
 BYTES_STEP_SPLIT = BYTES_TRANSPORT_STEP + BYTES_PREPARE + NSUB * (BYTES_STRESS + BYTES_VELOCITY)
@@ -378,8 +378,8 @@ def run_gpu(args):
                 "dram_gbs": kbytes / units / (kavg_ms * 1e-3) / 1e9,
                 "dram_frac_of_peak": kbytes / units / (kavg_ms * 1e-3) / 1e9 / peak,
                 "note": "frac > dram_frac_of_peak because two sub-iterations share one pass "
-                        "over HBM (profiles/: marching kernel 76 % of the measured HBM "
-                        "peak by ncu DRAM bytes, FP64 pipe 53 %)"}
+                        "over HBM (profiles/: marching kernel 79 % of the measured HBM "
+                        "peak, FP64 pipe 55 %)"}
         cpu = None
         if args.gpus == 1 and not args.no_cpu:
             n = args.cpu_sample
