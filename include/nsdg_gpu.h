@@ -268,6 +268,11 @@ int nsdg_dyn_upload_forcing_level(nsdg_ctx* ctx, int32_t level, const double* ua
 int nsdg_dyn_blend_forcing(nsdg_ctx* ctx, double w);
 /* sum over this rank's cells of the mean coefficient times cell area (mass diagnostic) */
 int nsdg_dyn_mass(nsdg_ctx* ctx, int32_t field, double* mass);
+/* rows per band the mEVP marching kernel uses for a strip of nrows x nx cells on a GPU with
+ * sm_count SMs (strip != 0: part of a strip decomposition, the halo exchange runs beside the
+ * interior bands).  Pure host arithmetic (no GPU needed); the environment variable
+ * NSDG_MEVP_MARCH=<rows> overrides it at run time, NSDG_MEVP_MARCH=0 selects the tiled kernel. */
+int nsdg_mevp_band_rows(int64_t nrows, int64_t nx, int32_t sm_count, int32_t strip);
 
 /* ---- strip decomposition (one process per GPU) ---- */
 #define NSDG_COMM_ID_BYTES 128

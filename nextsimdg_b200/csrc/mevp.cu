@@ -12,13 +12,15 @@
 //             so that one sub-iteration of the momentum equation is
 //               cd = acd |u_o - u|,  u' = (mdt beta u + cx0 + cd u_o + mdt dt f v + D_x)/(mdt (1+beta) + cd)
 //             (the oracle's formula with the p-independent terms summed once)
-// Per sub-iteration, three interchangeable implementations (all HBM streams over component-
-// major planes, coalesced; neighbours via L1/L2):
+// Per sub-iteration, four interchangeable, mutually bit-identical implementations (all HBM
+// streams over component-major planes, coalesced):
 //   split   stress_kernel + velocity_kernel                          24 + 17 = 41 doubles/cell
 //   fused   mevp_fused_kernel: stress + velocity in one launch, the new stress goes to the
 //           velocity phase through shared memory                     32 doubles/cell
 //   pair    mevp_pair_kernel: TWO sub-iterations per launch (temporal blocking on a 2-cell
 //           halo; periodic wrap or the strip's ghost rows)           32 doubles/cell per PAIR
+//   march   mevp_march_kernel (default): the same pair, but a warp marches up a band of rows
+//           with a register software pipeline, x-neighbours by shuffle   32 doubles/cell per PAIR
 // All index arithmetic is 32-bit (validated by the host: every array of the sub-cycle has fewer
 // than 2^31 elements) and every quotient that does not depend on the cell is taken on the host.
 #include "dyn.h"
@@ -1077,6 +1079,13 @@ int march_rows(nsdg_ctx* ctx)
     return c_ry;
 }
 } // namespace
+
+extern "C" int nsdg_mevp_band_rows(int64_t nrows, int64_t nx, int32_t sm_count, int32_t strip)
+{
+    if (nrows <= 0 || nx <= 0 || sm_count <= 0)
+        return NSDG_EINVAL;
+    return march_auto_rows(nrows, nx, sm_count, strip != 0);
+}
 
 int nsdg_mevp_pair_tile_rows(nsdg_ctx* ctx)
 {

@@ -249,3 +249,22 @@ def test_run_plan_follows_the_reference_iterator():
         RUN.plan_from_config("[Modules]\nNextsim::IIceAlbedo = Nextsim::NoSuchAlbedo\n")
     f = RUN.dummy_forcing(3)
     assert f["qlw"].tolist() == [311.0] * 3 and f["wind"].tolist() == [0.0] * 3
+
+
+def test_marching_kernel_band_rows():
+    """Band height of the mEVP marching kernel (host arithmetic, csrc/mevp.cu march_auto_rows):
+    a wave model over the 2 x SMs resident CTAs.  Pins the choices measured in
+    profiles/r1z_band_rows.txt and the invariants the strip split in dyn.cu relies on."""
+    lib = _abi.load()
+    rows = lib.nsdg_mevp_band_rows
+    assert rows(4096, 4096, 148, 0) == 512       # 8 bands x 37 CTAs = one wave of 296
+    assert rows(4096, 4096, 148, 1) == 128       # strips: four waves, the exchange starts after the first
+    assert rows(16384, 16384, 148, 0) == 1024    # capped
+    assert rows(2048, 16384, 148, 1) == 256      # 8-GPU strong scaling strip of configs[4]
+    assert rows(0, 16, 148, 0) < 0 and rows(16, 0, 148, 0) < 0 and rows(16, 16, 0, 0) < 0
+    for nrows, nx, strip in ((5, 17, 0), (48, 48, 0), (49, 48, 1), (211, 300, 0), (1024, 1024, 0),
+                             (512, 4096, 1), (4099, 4096, 1)):
+        ry = rows(nrows, nx, 148, strip)
+        assert 1 <= ry <= max(nrows, 1) and ry <= 1024, (nrows, nx, strip, ry)
+        if nrows >= 64:
+            assert ry >= 32, (nrows, nx, strip, ry)
