@@ -1066,15 +1066,16 @@ int march_rows(nsdg_ctx* ctx)
     if (e >= 0)
         return e;
     DynState* d = ctx->dyn;
-    // cached per context geometry (one strip per context)
-    static thread_local nsdg_ctx* c_ctx = nullptr;
+    // cached for the last geometry asked for (pure function of these four numbers)
     static thread_local int64_t c_ny = -1, c_nx = -1;
-    static thread_local int c_ry = 64;
-    if (c_ctx != ctx || c_ny != d->nyl || c_nx != d->nx) {
-        c_ctx = ctx;
+    static thread_local int c_sm = -1, c_strip = -1, c_ry = 64;
+    const int strip = d->wrap ? 0 : 1;
+    if (c_ny != d->nyl || c_nx != d->nx || c_sm != ctx->sm_count || c_strip != strip) {
         c_ny = d->nyl;
         c_nx = d->nx;
-        c_ry = march_auto_rows(d->nyl, d->nx, ctx->sm_count, !d->wrap);
+        c_sm = ctx->sm_count;
+        c_strip = strip;
+        c_ry = march_auto_rows(d->nyl, d->nx, ctx->sm_count, strip != 0);
     }
     return c_ry;
 }
