@@ -61,6 +61,10 @@ public:
             gpu.check(nsdg_dyn_set_mevp_params(gpu.ctx, mevp), "nsdg_dyn_set_mevp_params");
         registerModule();
     }
+    //! One dynamics state per context (a second nsdg_dyn_init is NSDG_ESTATE): released here.
+    ~GpuDynamics() override { nsdg_dyn_release(gpu.ctx); }
+    GpuDynamics(const GpuDynamics&) = delete;
+    GpuDynamics& operator=(const GpuDynamics&) = delete;
     std::string getName() const override { return "GpuDynamics"; }
 
     void setData(const ModelState& state) override
@@ -130,6 +134,9 @@ public:
             v.assign(n, 0.);
         registerModule();
     }
+    ~GpuColumnPhysics() override { nsdg_thermo_release(gpu.ctx); }
+    GpuColumnPhysics(const GpuColumnPhysics&) = delete;
+    GpuColumnPhysics& operator=(const GpuColumnPhysics&) = delete;
     std::string getName() const override { return "GpuColumnPhysics"; }
 
     void setData(const ModelState& state) override

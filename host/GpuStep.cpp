@@ -131,6 +131,8 @@ void GpuStep::setInitialData(IStructure& dataStructure)
             tice.push_back(d.iceTemperature(l < d.nIceLayers() ? l : 0));
     }
     n = hice.size();
+    // this adapter owns its context: a repeated setInitialData replaces its own state explicitly
+    check(nsdg_thermo_release(ctx), "nsdg_thermo_release");
     check(nsdg_thermo_init(ctx, (int64_t)n, nLayers), "nsdg_thermo_init");
     check(nsdg_thermo_set_params(ctx, &params), "nsdg_thermo_set_params");
     check(nsdg_thermo_upload_prognostic(ctx, hice.data(), cice.data(), hsnow.data(), sst.data(),

@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define NSDG_ABI_VERSION 2
+#define NSDG_ABI_VERSION 3
 
 typedef struct nsdg_ctx nsdg_ctx;
 
@@ -157,6 +157,31 @@ typedef struct nsdg_dyn_config {
 /* one sub-iteration per launch: do not use the pair-fused (two sub-iterations per launch) kernel */
 #define NSDG_DYN_SINGLE_MEVP 2
 
+/* Tuning knobs of the dynamics, per context (nsdg_dyn_set_tuning after nsdg_dyn_init).  0 means
+ * "default" in every field, so a zeroed struct is the shipped configuration.  The environment
+ * variables named beside each field override it when nsdg_dyn_init runs (A/B runs without
+ * touching the caller). */
+typedef struct nsdg_dyn_tuning {
+    int32_t march_rows; /* rows per band of the marching pair kernel: 0 = chosen per strip
+                           (nsdg_mevp_band_rows), > 0 fixed, -1 = tiled pair kernel instead
+                           [NSDG_MEVP_MARCH=<rows>, 0 = tiled] */
+    int32_t pair; /* two sub-iterations per launch: 0/1 on, -1 off            [NSDG_MEVP_PAIR=0/1] */
+    int32_t halo_overlap; /* NCCL halo path: boundary bands first, exchange beside the interior
+                             launch: 0/1 on, -1 off                        [NSDG_HALO_OVERLAP=0/1] */
+    int32_t halo_peer; /* strips: boundary bands store straight into the neighbour's ghost rows
+                          over NVLink peer memory (no pack / NCCL / unpack in the sub-cycle):
+                          0/1 on when the peer mapping exists, -1 off         [NSDG_HALO_PEER=0/1] */
+    int32_t pair_tile; /* tiled pair kernel: 0 = 16x16, 1 = 32x8, 2 = 32x16, 3 = 16x16 (3 CTAs/SM),
+                          4 = 16x8, 5 = 16x12                                [NSDG_PAIR_TILE=WxH] */
+    int32_t fused_tile; /* fused kernel: 0 = 32x8, 1 = 64x4, 2 = 32x16, 3 = 64x8, 4 = 16x16
+                                                                            [NSDG_FUSED_TILE=WxH] */
+    int32_t transport_march; /* transport stage: 0/1 marching kernel for dG2 / dG1, -1 one thread
+                                per cell                                 [NSDG_TRANSPORT_MARCH=0/1] */
+    int32_t graph; /* CUDA-graph replay of the sub-cycle's launches: 0 = automatic (single rank,
+                      grids below 2^20 cells), 1 on, -1 off                    [NSDG_DYN_GRAPH=0/1] */
+    int32_t reserved[8]; /* must be 0 */
+} nsdg_dyn_tuning;
+
 /* ---- context ---- */
 int nsdg_abi_version(void);
 int nsdg_create(nsdg_ctx** out, int device);
@@ -179,7 +204,10 @@ const char* nsdg_profile_kernel_name(int32_t kernel);
 
 /* ---- column thermodynamics ---- */
 void nsdg_thermo_default_params(nsdg_thermo_params* p);
+/* One thermodynamics state and one dynamics state per context.  *_init on a context that
+ * already holds a state of that kind fails with NSDG_ESTATE; *_release frees it first. */
 int nsdg_thermo_init(nsdg_ctx* ctx, int64_t ncells, int32_t nlayers);
+int nsdg_thermo_release(nsdg_ctx* ctx);
 int nsdg_thermo_set_params(nsdg_ctx* ctx, const nsdg_thermo_params* p);
 /* host -> device; tice is [ncells][nlayers] layer-fastest, only layer 0 is kept */
 int nsdg_thermo_upload_prognostic(nsdg_ctx* ctx, const double* hice, const double* cice,
@@ -222,6 +250,10 @@ int nsdg_thermo_run_host(nsdg_ctx* ctx, double dt, int32_t nsteps, double* hice,
 /* ---- dynamics: DG transport + mEVP ---- */
 void nsdg_mevp_default_params(nsdg_mevp_params* p);
 int nsdg_dyn_init(nsdg_ctx* ctx, const nsdg_dyn_config* cfg);
+int nsdg_dyn_release(nsdg_ctx* ctx);
+/* t == NULL restores the defaults (plus environment overrides); get returns what is in effect */
+int nsdg_dyn_set_tuning(nsdg_ctx* ctx, const nsdg_dyn_tuning* t);
+int nsdg_dyn_get_tuning(const nsdg_ctx* ctx, nsdg_dyn_tuning* t);
 int nsdg_dyn_set_mevp_params(nsdg_ctx* ctx, const nsdg_mevp_params* p);
 /* interior of this rank's strip, host layout [ncomp_of_field][ny_local][nx] */
 int nsdg_dyn_upload(nsdg_ctx* ctx, int32_t field, const double* host);
@@ -279,8 +311,11 @@ int nsdg_mevp_band_rows(int64_t nrows, int64_t nx, int32_t sm_count, int32_t str
 int nsdg_comm_get_unique_id(void* id_out /* NSDG_COMM_ID_BYTES */);
 int nsdg_comm_init(nsdg_ctx* ctx, const void* id, int32_t rank, int32_t nranks);
 int nsdg_comm_rank(const nsdg_ctx* ctx, int32_t* rank, int32_t* nranks);
-/* bytes sent per rank by halo exchanges since creation (diagnostic) */
+/* bytes sent per rank by halo exchanges since creation (diagnostic; NCCL messages and peer stores) */
 int64_t nsdg_comm_bytes_sent(const nsdg_ctx* ctx);
+/* 1 when the sub-cycle's halo goes through NVLink peer stores from inside the marching kernel
+ * (neighbours' planes mapped with CUDA IPC at nsdg_dyn_init), 0 when it goes through NCCL */
+int nsdg_comm_halo_peer(const nsdg_ctx* ctx);
 
 #ifdef __cplusplus
 }

@@ -64,6 +64,16 @@ DYN_SPLIT_MEVP = 1
 DYN_SINGLE_MEVP = 2
 
 
+class DynTuning(ctypes.Structure):
+    """nsdg_dyn_tuning: 0 = default in every field (include/nsdg_gpu.h)."""
+    _fields_ = [(n, ctypes.c_int32) for n in (
+        "march_rows", "pair", "halo_overlap", "halo_peer", "pair_tile", "fused_tile",
+        "transport_march", "graph")] + [("reserved", ctypes.c_int32 * 8)]
+
+    PAIR_TILES = ("16x16", "32x8", "32x16", "16x16m3", "16x8", "16x12")
+    FUSED_TILES = ("32x8", "64x4", "32x16", "64x8", "16x16")
+
+
 # every symbol include/nsdg_gpu.h declares: name -> (restype, argtypes)
 _ctx = ctypes.c_void_p
 _i32, _i64, _dbl = ctypes.c_int32, ctypes.c_int64, ctypes.c_double
@@ -82,6 +92,7 @@ SYMBOLS = {
     "nsdg_profile_kernel_name": (ctypes.c_char_p, [_i32]),
     "nsdg_thermo_default_params": (None, [ctypes.POINTER(ThermoParams)]),
     "nsdg_thermo_init": (ctypes.c_int, [_ctx, _i64, _i32]),
+    "nsdg_thermo_release": (ctypes.c_int, [_ctx]),
     "nsdg_thermo_set_params": (ctypes.c_int, [_ctx, ctypes.POINTER(ThermoParams)]),
     "nsdg_thermo_upload_prognostic": (ctypes.c_int, [_ctx] + [c_double_p] * 6),
     "nsdg_thermo_upload_forcing": (ctypes.c_int, [_ctx] + [c_double_p] * 8),
@@ -98,6 +109,9 @@ SYMBOLS = {
     "nsdg_thermo_run_host": (ctypes.c_int, [_ctx, _dbl, _i32] + [c_double_p] * 14),
     "nsdg_mevp_default_params": (None, [ctypes.POINTER(MevpParams)]),
     "nsdg_dyn_init": (ctypes.c_int, [_ctx, ctypes.POINTER(DynConfig)]),
+    "nsdg_dyn_release": (ctypes.c_int, [_ctx]),
+    "nsdg_dyn_set_tuning": (ctypes.c_int, [_ctx, ctypes.POINTER(DynTuning)]),
+    "nsdg_dyn_get_tuning": (ctypes.c_int, [_ctx, ctypes.POINTER(DynTuning)]),
     "nsdg_dyn_set_mevp_params": (ctypes.c_int, [_ctx, ctypes.POINTER(MevpParams)]),
     "nsdg_dyn_upload": (ctypes.c_int, [_ctx, _i32, c_double_p]),
     "nsdg_dyn_download": (ctypes.c_int, [_ctx, _i32, c_double_p]),
@@ -120,6 +134,7 @@ SYMBOLS = {
     "nsdg_comm_init": (ctypes.c_int, [_ctx, ctypes.c_void_p, _i32, _i32]),
     "nsdg_comm_rank": (ctypes.c_int, [_ctx, ctypes.POINTER(_i32), ctypes.POINTER(_i32)]),
     "nsdg_comm_bytes_sent": (_i64, [_ctx]),
+    "nsdg_comm_halo_peer": (ctypes.c_int, [_ctx]),
 }
 
 _lib = None

@@ -18,6 +18,7 @@ struct CommState {
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
     ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*GroupStart)() = nullptr;
     ncclResult_t (*GroupEnd)() = nullptr;
     const char* (*GetErrorString)(ncclResult_t) = nullptr;
@@ -33,7 +34,8 @@ void* open_nccl(std::string& err)
         if (h)
             return h;
     }
-    err = dlerror() ? dlerror() : "libnccl.so.2 not found";
+    const char* e = dlerror(); // one call: dlerror() clears the state it returns
+    err = e ? e : "libnccl.so.2 not found";
     return nullptr;
 }
 
@@ -159,6 +161,106 @@ int nsdg_halo_exchange(nsdg_ctx* ctx, const HaloSpec* specs, int nspecs, cudaStr
     return NSDG_OK;
 }
 
+// ---- peer halo: map the ring neighbours' slabs with CUDA IPC --------------------------------
+namespace {
+struct PeerInfo { // what a rank tells its ring neighbours (travels through NCCL as bytes)
+    cudaIpcMemHandle_t handle;
+    int64_t nyl, plane, nflagw;
+    int32_t ok, device;
+    char pad[128 - sizeof(cudaIpcMemHandle_t) - 3 * 8 - 2 * 4];
+};
+static_assert(sizeof(PeerInfo) == 128, "PeerInfo is a 128-byte message");
+} // namespace
+
+void nsdg_comm_unmap_peers(nsdg_ctx* ctx)
+{
+    DynState* d = ctx->dyn;
+    if (!d)
+        return;
+    if (d->ipc_up)
+        cudaIpcCloseMemHandle(d->ipc_up);
+    if (d->ipc_dn && d->ipc_dn != d->ipc_up)
+        cudaIpcCloseMemHandle(d->ipc_dn);
+    d->ipc_up = d->ipc_dn = nullptr;
+    d->up = d->dn = PeerMap {};
+    d->peer_ok = false;
+}
+
+int nsdg_comm_map_peers(nsdg_ctx* ctx)
+{
+    CommState* c = ctx->comm;
+    DynState* d = ctx->dyn;
+    d->peer_ok = false;
+    if (!nsdg_comm_active(ctx) || !d->slab)
+        return NSDG_OK;
+    const int up = (c->rank + 1) % c->nranks, down = (c->rank + c->nranks - 1) % c->nranks;
+    PeerInfo mine = {}, from_up = {}, from_dn = {};
+    mine.nyl = d->nyl;
+    mine.plane = d->plane;
+    mine.nflagw = d->nflagw;
+    mine.device = ctx->device;
+    mine.ok = cudaIpcGetMemHandle(&mine.handle, d->slab) == cudaSuccess;
+    (void)cudaGetLastError();
+    PeerInfo* dev = nullptr; // [0] mine, [1] from the rank above, [2] from the rank below
+    NSDG_CUDA(ctx, cudaMalloc(&dev, 3 * sizeof(PeerInfo) + 2 * sizeof(int)));
+    int* agree = reinterpret_cast<int*>(dev + 3);
+    NSDG_CUDA(ctx, cudaMemcpyAsync(dev, &mine, sizeof mine, cudaMemcpyHostToDevice, ctx->stream));
+    NSDG_NCCL(ctx, c, c->GroupStart());
+    NSDG_NCCL(ctx, c, c->Send(dev, sizeof(PeerInfo), ncclChar, up, c->comm, ctx->stream));
+    NSDG_NCCL(ctx, c, c->Recv(dev + 2, sizeof(PeerInfo), ncclChar, down, c->comm, ctx->stream));
+    NSDG_NCCL(ctx, c, c->Send(dev, sizeof(PeerInfo), ncclChar, down, c->comm, ctx->stream));
+    NSDG_NCCL(ctx, c, c->Recv(dev + 1, sizeof(PeerInfo), ncclChar, up, c->comm, ctx->stream));
+    NSDG_NCCL(ctx, c, c->GroupEnd());
+    NSDG_CUDA(ctx, cudaMemcpyAsync(&from_up, dev + 1, sizeof from_up, cudaMemcpyDeviceToHost, ctx->stream));
+    NSDG_CUDA(ctx, cudaMemcpyAsync(&from_dn, dev + 2, sizeof from_dn, cudaMemcpyDeviceToHost, ctx->stream));
+    NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    int ok = mine.ok && from_up.ok && from_dn.ok && from_up.nflagw == d->nflagw && from_dn.nflagw == d->nflagw;
+    auto open = [&](const PeerInfo& pi, void** out) {
+        if (cudaIpcOpenMemHandle(out, pi.handle, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+            (void)cudaGetLastError();
+            *out = nullptr;
+            return false;
+        }
+        return true;
+    };
+    if (ok) {
+        ok = open(from_up, &d->ipc_up);
+        if (ok) {
+            if (up == down) // two ranks: both neighbours are the same process, one mapping
+                d->ipc_dn = d->ipc_up;
+            else
+                ok = open(from_dn, &d->ipc_dn);
+        }
+    }
+    // every rank must take the same path: the minimum over all ranks decides
+    NSDG_CUDA(ctx, cudaMemcpyAsync(agree, &ok, sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    NSDG_NCCL(ctx, c, c->AllReduce(agree, agree + 1, 1, ncclInt32, ncclMin, c->comm, ctx->stream));
+    int all = 0;
+    NSDG_CUDA(ctx, cudaMemcpyAsync(&all, agree + 1, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    cudaFree(dev);
+    if (!all) {
+        nsdg_comm_unmap_peers(ctx);
+        return NSDG_OK;
+    }
+    auto fill = [&](PeerMap& m, void* base, const PeerInfo& pi) {
+        m.slab = static_cast<double*>(base);
+        m.nyl = pi.nyl;
+        m.plane = pi.plane;
+        m.flags = reinterpret_cast<unsigned*>(m.slab + (size_t)NSDG_SLAB_PLANES * pi.plane);
+    };
+    fill(d->up, d->ipc_up, from_up);
+    fill(d->dn, d->ipc_dn, from_dn);
+    d->peer_ok = true;
+    return NSDG_OK;
+}
+
+void nsdg_comm_count_bytes(nsdg_ctx* ctx, int64_t bytes)
+{
+    if (ctx->comm)
+        ctx->comm->bytes_sent += bytes;
+}
+
 int nsdg_halo_exchange(nsdg_ctx* ctx, const PlaneSet& planes, int which)
 {
     HaloSpec h;
@@ -208,6 +310,7 @@ int nsdg_comm_init(nsdg_ctx* ctx, const void* id, int32_t rank, int32_t nranks)
     BIND(CommDestroy, "ncclCommDestroy");
     BIND(Send, "ncclSend");
     BIND(Recv, "ncclRecv");
+    BIND(AllReduce, "ncclAllReduce");
     BIND(GroupStart, "ncclGroupStart");
     BIND(GroupEnd, "ncclGroupEnd");
     BIND(GetErrorString, "ncclGetErrorString");
@@ -230,5 +333,10 @@ int nsdg_comm_rank(const nsdg_ctx* ctx, int32_t* rank, int32_t* nranks)
 }
 
 int64_t nsdg_comm_bytes_sent(const nsdg_ctx* ctx) { return (ctx && ctx->comm) ? ctx->comm->bytes_sent : 0; }
+
+int nsdg_comm_halo_peer(const nsdg_ctx* ctx)
+{
+    return (ctx && ctx->dyn && nsdg_mevp_peer_halo(const_cast<nsdg_ctx*>(ctx))) ? 1 : 0;
+}
 
 } // extern "C"

@@ -22,6 +22,28 @@ int field_ncomp(const DynState* d, int field)
     }
 }
 
+int env_int(const char* name, int dflt)
+{
+    const char* e = getenv(name);
+    return e ? atoi(e) : dflt;
+}
+int env_tile(const char* name, const char* const* names, int n)
+{
+    const char* e = getenv(name);
+    if (!e)
+        return 0;
+    for (int q = 0; q < n; ++q)
+        if (!strcmp(e, names[q]))
+            return q;
+    return 0;
+}
+// 0/1 environment switch -> tri-state knob (1 on, -1 off), unset -> 0 (default)
+int env_switch(const char* name)
+{
+    const char* e = getenv(name);
+    return e ? (atoi(e) != 0 ? 1 : -1) : 0;
+}
+
 int alloc_planes(nsdg_ctx* ctx, double** p, int nplanes)
 {
     DynState* d = ctx->dyn;
@@ -179,32 +201,31 @@ int mevp_cycle(nsdg_ctx* ctx, double dt, int nsub)
     double *u = d->f[NSDG_DF_U], *v = d->f[NSDG_DF_V], *u2 = d->u2, *v2 = d->v2;
     const int64_t s0 = multi ? G - 1 : G, r0 = G, r1 = G + d->nyl;
     const bool fused = !(d->cfg.flags & NSDG_DYN_SPLIT_MEVP);
-    static int pair_env = -1; // NSDG_MEVP_PAIR=0/1 overrides the default (tuning / A-B tests)
-    if (pair_env < 0) {
-        const char* e = getenv("NSDG_MEVP_PAIR");
-        pair_env = e ? (atoi(e) != 0) : 1;
-    }
     // two sub-iterations per launch (and per halo exchange) while at least two remain
-    const bool pair = pair_env && fused && !(d->cfg.flags & NSDG_DYN_SINGLE_MEVP);
+    const bool pair = d->tune.pair >= 0 && fused && !(d->cfg.flags & NSDG_DYN_SINGLE_MEVP);
     double* sa[3] = { d->f[NSDG_DF_S11], d->f[NSDG_DF_S12], d->f[NSDG_DF_S22] };
     double* sb[3] = { d->s2[0], d->s2[1], d->s2[2] };
     // Strips: the tile rows next to the ghost rows go first; their halo messages travel on the
     // communication stream while the interior tile rows compute (NSDG_HALO_OVERLAP=0 disables).
-    static int overlap_env = -1;
-    if (overlap_env < 0) {
-        const char* e = getenv("NSDG_HALO_OVERLAP");
-        overlap_env = e ? (atoi(e) != 0) : 1;
-    }
     const int ty = nsdg_mevp_pair_tile_rows(ctx);
     const int64_t ntr = (d->nyl + ty - 1) / ty; // tile rows of the strip
     // the two top interior rows are sent up: they must lie inside the last boundary launch
     const int64_t ntop = (d->nyl - (ntr - 1) * ty >= 2) ? 1 : 2;
-    const bool overlap = multi && pair && overlap_env && ntr >= ntop + 2 && ty >= 2;
+    // Peer halo: ONE launch per pair; the marching kernel's boundary bands store their rows into
+    // the neighbours' ghost rows over NVLink and the neighbours' boundary bands of the next pair
+    // poll a per-warp sequence number (mevp.cu).  No pack / NCCL / unpack, no second stream.
+    const bool peer = multi && pair && nsdg_mevp_peer_halo(ctx);
+    const bool overlap = multi && pair && !peer && d->tune.halo_overlap >= 0 && ntr >= ntop + 2 && ty >= 2;
     for (int p = 0; p < nsub; ++p) {
         bool paired = false;
         int64_t rest0 = r0, rest1 = r0; // interior rows that run beside the exchange
         if (pair && p + 1 < nsub) {
-            if (overlap) {
+            if (peer) {
+                if ((rc = nsdg_mevp_pair(ctx, dt, u, v, u2, v2, sa, sb, r0, r1, nullptr, ++d->halo_seq)))
+                    return rc;
+                // rows this rank stored into its neighbours: S 2 up + 1 down, u, v 2 + 2
+                nsdg_comm_count_bytes(ctx, (int64_t)(9 * 3 + 2 * 4) * d->nx * 8);
+            } else if (overlap) {
                 // boundary tile rows on the (high-priority) communication stream, behind
                 // everything issued so far
                 rest0 = r0 + ty;
@@ -232,7 +253,7 @@ int mevp_cycle(nsdg_ctx* ctx, double dt, int nsub)
             if ((rc = nsdg_mevp_velocity(ctx, dt, u, v, u2, v2, sa, r0, r1)))
                 return rc;
         }
-        if (multi) {
+        if (multi && !(peer && paired)) {
             // after a pair the next pair needs the new stress on its ghost cells as well; a single
             // sub-iteration keeps the first lower ghost row of S current by itself
             HaloSpec hs[2];
@@ -274,13 +295,120 @@ int mevp_cycle(nsdg_ctx* ctx, double dt, int nsub)
     return NSDG_OK;
 }
 
+void drop_graphs(DynState* d)
+{
+    for (auto& g : d->graphs)
+        cudaGraphExecDestroy(g.exec);
+    d->graphs.clear();
+}
+
+// Runs body() -- a sequence of launches on ctx->stream that depends only on (kind, field, dt,
+// nsub) and on which physical buffers currently play which role -- either directly or as a
+// captured CUDA graph that is replayed on later calls with the same key.  The body also swaps
+// host-side buffer roles (ping-pong); those are recorded with the graph and re-applied on replay.
+template <class Body> int graphed(nsdg_ctx* ctx, int kind, int field, double dt, int nsub, Body body)
+{
+    DynState* d = ctx->dyn;
+    const bool use = !nsdg_comm_active(ctx) && !ctx->prof.on
+        && (d->tune.graph > 0 || (d->tune.graph == 0 && d->nx * d->nyl < ((int64_t)1 << 20)));
+    if (!use)
+        return body();
+    uint64_t dtbits;
+    memcpy(&dtbits, &dt, 8);
+    const uint64_t key[7] = { (uint64_t)kind, (uint64_t)field, (uint64_t)nsub, dtbits,
+        (uint64_t)(uintptr_t)d->f[NSDG_DF_U], (uint64_t)(uintptr_t)d->f[NSDG_DF_S11],
+        // the forcing buffers swap with their alternates in deferred host steps
+        (uint64_t)(uintptr_t)d->f[NSDG_DF_UATM] ^ ((uint64_t)(uintptr_t)d->f[NSDG_DF_VATM] << 1)
+            ^ ((uint64_t)(uintptr_t)d->f[NSDG_DF_UOCN] << 2) ^ ((uint64_t)(uintptr_t)d->f[NSDG_DF_VOCN] << 3) };
+    auto roles = [&](double** r) {
+        r[0] = d->f[NSDG_DF_U];
+        r[1] = d->f[NSDG_DF_V];
+        r[2] = d->u2;
+        r[3] = d->v2;
+        r[4] = d->f[NSDG_DF_S11];
+        r[5] = d->f[NSDG_DF_S12];
+        r[6] = d->f[NSDG_DF_S22];
+        r[7] = d->s2[0];
+        r[8] = d->s2[1];
+        r[9] = d->s2[2];
+    };
+    for (auto& g : d->graphs)
+        if (!memcmp(g.key, key, sizeof key)) {
+            NSDG_CUDA(ctx, cudaGraphLaunch(g.exec, ctx->stream));
+            ctx->launches += g.launches;
+            d->f[NSDG_DF_U] = g.after[0];
+            d->f[NSDG_DF_V] = g.after[1];
+            d->u2 = g.after[2];
+            d->v2 = g.after[3];
+            d->f[NSDG_DF_S11] = g.after[4];
+            d->f[NSDG_DF_S12] = g.after[5];
+            d->f[NSDG_DF_S22] = g.after[6];
+            d->s2[0] = g.after[7];
+            d->s2[1] = g.after[8];
+            d->s2[2] = g.after[9];
+            return NSDG_OK;
+        }
+    const int64_t l0 = ctx->launches;
+    NSDG_CUDA(ctx, cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal));
+    const int rc = body();
+    cudaGraph_t graph = nullptr;
+    const cudaError_t e = cudaStreamEndCapture(ctx->stream, &graph);
+    if (rc || e != cudaSuccess) {
+        if (graph)
+            cudaGraphDestroy(graph);
+        (void)cudaGetLastError();
+        return rc ? rc : nsdg_fail(ctx, NSDG_ECUDA, "graph capture failed: %s", cudaGetErrorString(e));
+    }
+    DynState::Graph g = {};
+    memcpy(g.key, key, sizeof key);
+    g.launches = ctx->launches - l0;
+    roles(g.after);
+    const cudaError_t ei = cudaGraphInstantiate(&g.exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (ei != cudaSuccess)
+        return nsdg_fail(ctx, NSDG_ECUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(ei));
+    if (d->graphs.size() >= 16) // a time loop needs one or two; anything else is churn
+        drop_graphs(d);
+    d->graphs.push_back(g);
+    NSDG_CUDA(ctx, cudaGraphLaunch(g.exec, ctx->stream)); // capture records, it does not run
+    return NSDG_OK;
+}
+
 } // namespace
+
+void nsdg_dyn_tuning_defaults(nsdg_dyn_tuning* t)
+{
+    static const char* const pair_tiles[] = { "16x16", "32x8", "32x16", "16x16m3", "16x8", "16x12" };
+    static const char* const fused_tiles[] = { "32x8", "64x4", "32x16", "64x8", "16x16" };
+    *t = nsdg_dyn_tuning {};
+    const int m = env_int("NSDG_MEVP_MARCH", -1);
+    t->march_rows = (m < 0 || m > 4096) ? 0 : (m == 0 ? -1 : m);
+    t->pair = env_switch("NSDG_MEVP_PAIR");
+    t->halo_overlap = env_switch("NSDG_HALO_OVERLAP");
+    t->halo_peer = env_switch("NSDG_HALO_PEER");
+    t->pair_tile = env_tile("NSDG_PAIR_TILE", pair_tiles, 6);
+    t->fused_tile = env_tile("NSDG_FUSED_TILE", fused_tiles, 5);
+    t->transport_march = env_switch("NSDG_TRANSPORT_MARCH");
+    t->graph = env_switch("NSDG_DYN_GRAPH");
+}
 
 void nsdg_dyn_free(nsdg_ctx* ctx)
 {
     DynState* d = ctx->dyn;
     if (!d)
         return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    cudaStreamSynchronize(ctx->comm_stream);
+    drop_graphs(d);
+    if (d->slab) { // the slab owns S, its partners, u, v and their partners
+        nsdg_comm_unmap_peers(ctx);
+        for (int q : { NSDG_DF_U, NSDG_DF_V, NSDG_DF_S11, NSDG_DF_S12, NSDG_DF_S22 })
+            d->f[q] = nullptr;
+        d->u2 = d->v2 = nullptr;
+        d->s2[0] = d->s2[1] = d->s2[2] = nullptr;
+        cudaFree(d->slab);
+    }
     for (int q = 0; q < NSDG_DF_COUNT; ++q)
         cudaFree(d->f[q]);
     cudaFree(d->snap);
@@ -349,10 +477,12 @@ int nsdg_dyn_init(nsdg_ctx* ctx, const nsdg_dyn_config* cfg)
     const bool multi = nsdg_comm_active(ctx);
     NSDG_REQUIRE(ctx, multi || cfg->ny_local == cfg->ny_global, NSDG_EINVAL,
         "a strip (ny_local < ny_global) needs nsdg_comm_init before nsdg_dyn_init");
-    nsdg_dyn_free(ctx);
+    NSDG_REQUIRE(ctx, !ctx->dyn, NSDG_ESTATE,
+        "this context already holds a dynamics state: call nsdg_dyn_release first");
     DynState* d = new DynState;
     ctx->dyn = d;
     d->cfg = *cfg;
+    nsdg_dyn_tuning_defaults(&d->tune);
     nsdg_mevp_default_params(&d->mp);
     d->nx = cfg->nx;
     d->nyl = cfg->ny_local;
@@ -362,9 +492,32 @@ int nsdg_dyn_init(nsdg_ctx* ctx, const nsdg_dyn_config* cfg)
     d->rk = cfg->rk_order ? cfg->rk_order : (d->nc == 1 ? 1 : (d->nc == 3 ? 2 : 3));
     d->wrap = !multi;
     int rc;
+    const bool fused_bufs = !(cfg->flags & NSDG_DYN_SPLIT_MEVP);
+    if (multi) {
+        // one allocation (= one IPC handle) for everything the sub-cycle exchanges, then the flags
+        d->nflagw = (int)((d->nx + 27) / 28);
+        const size_t bytes = sizeof(double) * (size_t)NSDG_SLAB_PLANES * d->plane + sizeof(unsigned) * 2 * (size_t)d->nflagw;
+        NSDG_CUDA(ctx, cudaMalloc(&d->slab, bytes));
+        NSDG_CUDA(ctx, cudaMemsetAsync(d->slab, 0, bytes, ctx->stream));
+        d->flags = reinterpret_cast<unsigned*>(d->slab + (size_t)NSDG_SLAB_PLANES * d->plane);
+        double* q = d->slab;
+        for (int f : { NSDG_DF_S11, NSDG_DF_S12, NSDG_DF_S22 }) {
+            d->f[f] = q;
+            q += 3 * d->plane;
+        }
+        for (int k = 0; k < 3; ++k) {
+            if (fused_bufs)
+                d->s2[k] = q;
+            q += 3 * d->plane;
+        }
+        d->f[NSDG_DF_U] = q;
+        d->f[NSDG_DF_V] = q + d->plane;
+        d->u2 = q + 2 * d->plane;
+        d->v2 = q + 3 * d->plane;
+    }
     for (int q = 0; q < NSDG_DF_COUNT; ++q) {
         d->ncomp[q] = field_ncomp(d, q);
-        if ((rc = alloc_planes(ctx, &d->f[q], d->ncomp[q])))
+        if (!d->f[q] && (rc = alloc_planes(ctx, &d->f[q], d->ncomp[q])))
             return rc;
     }
     for (int f = 0; f < 2; ++f) {
@@ -375,13 +528,13 @@ int nsdg_dyn_init(nsdg_ctx* ctx, const nsdg_dyn_config* cfg)
     }
     double** one[] = { &d->u2, &d->v2 };
     for (double** p : one)
-        if ((rc = alloc_planes(ctx, p, 1)))
+        if (!*p && (rc = alloc_planes(ctx, p, 1)))
             return rc;
     if ((rc = alloc_planes(ctx, &d->pg, 4)) || (rc = alloc_planes(ctx, &d->nd, 4)))
         return rc;
-    if (!(cfg->flags & NSDG_DYN_SPLIT_MEVP))
+    if (fused_bufs)
         for (int q = 0; q < 3; ++q)
-            if ((rc = alloc_planes(ctx, &d->s2[q], 3)))
+            if (!d->s2[q] && (rc = alloc_planes(ctx, &d->s2[q], 3)))
                 return rc;
     NSDG_CUDA(ctx, cudaMalloc(&d->scratch, 64));
     if (multi) {
@@ -391,6 +544,45 @@ int nsdg_dyn_init(nsdg_ctx* ctx, const nsdg_dyn_config* cfg)
             NSDG_CUDA(ctx, cudaMalloc(p, sizeof(double) * d->halo_capacity));
     }
     NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (multi && (rc = nsdg_comm_map_peers(ctx)))
+        return rc;
+    return NSDG_OK;
+}
+
+int nsdg_dyn_release(nsdg_ctx* ctx)
+{
+    NSDG_ENTER(ctx);
+    nsdg_dyn_free(ctx);
+    return NSDG_OK;
+}
+
+int nsdg_dyn_set_tuning(nsdg_ctx* ctx, const nsdg_dyn_tuning* t)
+{
+    NSDG_ENTER(ctx);
+    DynState* d = ctx->dyn;
+    NSDG_REQUIRE(ctx, d, NSDG_ESTATE, "nsdg_dyn_init has not been called");
+    if (!t) {
+        nsdg_dyn_tuning_defaults(&d->tune);
+        return NSDG_OK;
+    }
+    NSDG_REQUIRE(ctx, t->march_rows >= -1 && t->march_rows <= 4096, NSDG_EINVAL, "march_rows in -1..4096");
+    NSDG_REQUIRE(ctx, t->pair_tile >= 0 && t->pair_tile <= 5 && t->fused_tile >= 0 && t->fused_tile <= 4,
+        NSDG_EINVAL, "unknown tile id");
+    for (int q : { t->pair, t->halo_overlap, t->halo_peer, t->transport_march, t->graph })
+        NSDG_REQUIRE(ctx, q >= -1 && q <= 1, NSDG_EINVAL, "switches take -1, 0 or 1");
+    for (int q : t->reserved)
+        NSDG_REQUIRE(ctx, q == 0, NSDG_EINVAL, "reserved fields must be 0");
+    NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->stream)); // knobs never change under work in flight
+    drop_graphs(d);
+    d->tune = *t;
+    return NSDG_OK;
+}
+
+int nsdg_dyn_get_tuning(const nsdg_ctx* ctx, nsdg_dyn_tuning* t)
+{
+    if (!ctx || !ctx->dyn || !t)
+        return NSDG_EINVAL;
+    *t = ctx->dyn->tune;
     return NSDG_OK;
 }
 
@@ -403,6 +595,8 @@ int nsdg_dyn_set_mevp_params(nsdg_ctx* ctx, const nsdg_mevp_params* p)
         "unknown boundary condition %d", p->bc);
     NSDG_REQUIRE(ctx, p->alpha > 0 && p->beta >= 0 && p->ellipse_e > 0 && p->delta_min > 0,
         NSDG_EINVAL, "alpha, ellipse_e, delta_min must be positive");
+    NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    drop_graphs(ctx->dyn); // kernel arguments are baked into captured launches
     ctx->dyn->mp = *p;
     return NSDG_OK;
 }
@@ -458,11 +652,13 @@ int nsdg_transport_step(nsdg_ctx* ctx, int32_t field, double dt)
     NSDG_REQUIRE(ctx, d, NSDG_ESTATE, "nsdg_dyn_init has not been called");
     NSDG_REQUIRE(ctx, field == NSDG_DF_H || field == NSDG_DF_A, NSDG_EINVAL,
         "only the tracers H and A can be transported");
-    double* phi[1] = { d->f[field] };
-    double* s1[1] = { d->stage1[0] };
-    double* s2[1] = { d->stage2[0] };
-    const double lo[1] = { 0. }, hi[1] = { field == NSDG_DF_A ? 1. : 1e300 };
-    return transport_fields(ctx, 1, phi, s1, s2, lo, hi, dt);
+    return graphed(ctx, 1, field, dt, 0, [&]() {
+        double* phi[1] = { d->f[field] };
+        double* s1[1] = { d->stage1[0] };
+        double* s2[1] = { d->stage2[0] };
+        const double lo[1] = { 0. }, hi[1] = { field == NSDG_DF_A ? 1. : 1e300 };
+        return transport_fields(ctx, 1, phi, s1, s2, lo, hi, dt);
+    });
 }
 
 int nsdg_transport_step_HA(nsdg_ctx* ctx, double dt)
@@ -470,9 +666,11 @@ int nsdg_transport_step_HA(nsdg_ctx* ctx, double dt)
     NSDG_ENTER(ctx);
     DynState* d = ctx->dyn;
     NSDG_REQUIRE(ctx, d, NSDG_ESTATE, "nsdg_dyn_init has not been called");
-    double* phi[2] = { d->f[NSDG_DF_H], d->f[NSDG_DF_A] };
-    const double lo[2] = { 0., 0. }, hi[2] = { 1e300, 1. };
-    return transport_fields(ctx, 2, phi, d->stage1, d->stage2, lo, hi, dt);
+    return graphed(ctx, 0, 0, dt, 0, [&]() {
+        double* phi[2] = { d->f[NSDG_DF_H], d->f[NSDG_DF_A] };
+        const double lo[2] = { 0., 0. }, hi[2] = { 1e300, 1. };
+        return transport_fields(ctx, 2, phi, d->stage1, d->stage2, lo, hi, dt);
+    });
 }
 
 int nsdg_mevp_step(nsdg_ctx* ctx, double dt, int32_t nsub)
@@ -480,7 +678,7 @@ int nsdg_mevp_step(nsdg_ctx* ctx, double dt, int32_t nsub)
     NSDG_ENTER(ctx);
     NSDG_REQUIRE(ctx, ctx->dyn, NSDG_ESTATE, "nsdg_dyn_init has not been called");
     NSDG_REQUIRE(ctx, dt > 0 && nsub >= 0, NSDG_EINVAL, "dt > 0 and nsub >= 0 required");
-    return mevp_cycle(ctx, dt, nsub);
+    return graphed(ctx, 2, 0, dt, nsub, [&]() { return mevp_cycle(ctx, dt, nsub); });
 }
 
 int nsdg_dyn_step(nsdg_ctx* ctx, double dt, int32_t nsub)
@@ -512,11 +710,24 @@ static int step_host_impl(nsdg_ctx* ctx, double dt, int32_t nsub, const double* 
     const int snapoff[5] = { 0, 1, 2, 5, 8 };
     int rc;
     if (deferred) {
-        if (out && !d->snap && (rc = alloc_planes(ctx, &d->snap, 11)))
-            return rc;
-        for (int q = 0; q < 4; ++q)
-            if (in && in[forcing[q]] && !d->falt[q] && (rc = alloc_planes(ctx, &d->falt[q], 1)))
+        bool fresh = false;
+        if (out && !d->snap) {
+            if ((rc = alloc_planes(ctx, &d->snap, 11)))
                 return rc;
+            fresh = true;
+        }
+        for (int q = 0; q < 4; ++q)
+            if (in && in[forcing[q]] && !d->falt[q]) {
+                if ((rc = alloc_planes(ctx, &d->falt[q], 1)))
+                    return rc;
+                fresh = true;
+            }
+        if (fresh) {
+            // alloc_planes clears the new buffers on the compute stream; the forcing upload below
+            // goes on the copy stream and must not overtake that memset (it would be zeroed)
+            NSDG_CUDA(ctx, cudaEventRecord(ctx->ev_pipe[0], ctx->stream));
+            NSDG_CUDA(ctx, cudaStreamWaitEvent(ctx->h2d_stream, ctx->ev_pipe[0], 0));
+        }
     }
     auto upload = [&](int f, double* devbase) -> cudaError_t {
         for (int c = 0; c < d->ncomp[f]; ++c) {

@@ -12,9 +12,17 @@
 
 constexpr int NSDG_GHOST = 2;
 
+// Ring neighbour whose planes are mapped into this process with CUDA IPC (peer halo, comm.cu)
+struct PeerMap {
+    double* slab = nullptr; // neighbour's slab (22 planes of ITS plane size, then its flags)
+    unsigned* flags = nullptr; // neighbour's flag array [2][nwarps]
+    int64_t nyl = 0, plane = 0;
+};
+
 struct DynState {
     nsdg_dyn_config cfg;
     nsdg_mevp_params mp;
+    nsdg_dyn_tuning tune = {}; // effective knobs (defaults + environment overrides + set_tuning)
     int64_t nx = 0, nyl = 0, rows = 0, plane = 0; // rows = nyl + 2*NSDG_GHOST, plane = rows*nx
     int nc = 0; // tracer components
     int rk = 0; // RK order actually used
@@ -49,7 +57,30 @@ struct DynState {
     double* recv_lo = nullptr; // from rank-1
     double* recv_hi = nullptr; // from rank+1
     size_t halo_capacity = 0; // doubles per buffer
+    // Strips: the arrays the sub-cycle exchanges (S and its ping-pong partner, u, v and their
+    // partners: NSDG_SLAB_PLANES planes) live in ONE allocation, followed by the halo flags, so
+    // that a single CUDA IPC handle maps them into the neighbours' processes.  The marching
+    // kernel's boundary bands then store their rows straight into the neighbour's ghost rows
+    // over NVLink and publish a per-warp sequence number; the neighbour's boundary bands poll it.
+    double* slab = nullptr;
+    unsigned* flags = nullptr; // [2][nwarps]: [0] written by the rank below, [1] by the rank above
+    int nflagw = 0; // warps per band row = ceil(nx / 28)
+    unsigned halo_seq = 0; // pairs launched in peer mode (same on every rank)
+    PeerMap up, dn;
+    void* ipc_up = nullptr; // pointers returned by cudaIpcOpenMemHandle (dn may alias up)
+    void* ipc_dn = nullptr;
+    bool peer_ok = false; // every rank mapped both neighbours
+    // CUDA-graph replay of the launch sequences of one step (single rank; dyn.cu): on small grids
+    // a step is launch bound (100 sub-iterations = 50 pair launches of a few microseconds)
+    struct Graph {
+        uint64_t key[7];
+        cudaGraphExec_t exec;
+        int64_t launches; // kernels in the graph (nsdg_launch_count keeps counting)
+        double* after[12]; // f[U], f[V], u2, v2, f[S11..S22], s2[0..2], pad: buffer roles after the body
+    };
+    std::vector<Graph> graphs;
 };
+constexpr int NSDG_SLAB_PLANES = 22;
 
 struct PlaneSet { // planes handled together by one halo exchange
     double* p[12];
@@ -82,10 +113,16 @@ int nsdg_mevp_fused(nsdg_ctx* ctx, double dt, const double* u, const double* v, 
     double* vnew, double* const* Sold, double* const* Snew, int64_t r0, int64_t r1);
 // two sub-iterations in one launch (temporal blocking) on the owned rows [r0,r1); r0 must sit on
 // a tile-row boundary (NSDG_GHOST + k * nsdg_mevp_pair_tile_rows(ctx))
+// peer_seq != 0 (strips, marching kernel, [r0,r1) = the whole strip): the boundary bands store
+// the rows the neighbours need straight into their ghost rows and publish peer_seq; before
+// touching their own ghost rows they wait for the neighbours' peer_seq - 1
 int nsdg_mevp_pair(nsdg_ctx* ctx, double dt, const double* u, const double* v, double* unew,
     double* vnew, double* const* Sold, double* const* Snew, int64_t r0, int64_t r1,
-    cudaStream_t st = nullptr);
+    cudaStream_t st = nullptr, unsigned peer_seq = 0);
 int nsdg_mevp_pair_tile_rows(nsdg_ctx* ctx);
+// true when the sub-cycle of this strip exchanges its halo by peer stores (mapping exists, the
+// marching kernel is selected and the knob is not off)
+bool nsdg_mevp_peer_halo(nsdg_ctx* ctx);
 
 // comm.cu -----------------------------------------------------------------------------------
 // Ring halo exchange of up to 3 plane groups in ONE message per neighbour.  No-op on a single
@@ -95,3 +132,11 @@ int nsdg_halo_exchange(nsdg_ctx* ctx, const HaloSpec* specs, int nspecs, cudaStr
 // one group: which = 1 lower ghost row only, 2 upper ghost row only, 3 both (one row each)
 int nsdg_halo_exchange(nsdg_ctx* ctx, const PlaneSet& planes, int which);
 bool nsdg_comm_active(const nsdg_ctx* ctx);
+// after the slab of a strip has been allocated: exchange IPC handles with the ring neighbours,
+// map their slabs, agree on peer_ok over all ranks.  Never fails the init for want of peer
+// access: peer_ok stays false and the NCCL path is used.
+int nsdg_comm_map_peers(nsdg_ctx* ctx);
+void nsdg_comm_unmap_peers(nsdg_ctx* ctx);
+void nsdg_comm_count_bytes(nsdg_ctx* ctx, int64_t bytes);
+// effective knobs -----------------------------------------------------------------------------
+void nsdg_dyn_tuning_defaults(nsdg_dyn_tuning* t); // zeros + environment overrides

@@ -60,6 +60,15 @@ struct MevpArgs {
     double* S22n;
     double* out0;
     double* out1;
+    // peer halo (strips, marching kernel): the neighbours' copies of S11n, S12n, S22n, out0, out1
+    // and their flag arrays, mapped with CUDA IPC (comm.cu); flag layout [2][nflagw]
+    double* up[5];
+    double* dn[5];
+    int plane_up, plane_dn, nyl_dn, nflagw;
+    const unsigned* flag_mine;
+    unsigned* flag_up;
+    unsigned* flag_dn;
+    unsigned seq;
 };
 
 __device__ __forceinline__ int row_below(const MevpArgs& A, int r)
@@ -662,6 +671,15 @@ struct MarchRow {
     bool act; // node (column, r) is not a Dirichlet node
 };
 
+// PEER: the ghost rows of S, u, v are written by the neighbour GPU while this kernel runs, so the
+// loads must not go through the (non-coherent) L1 / read-only path: ld.global.cg reads at L2, the
+// point of coherence for peer stores arriving over NVLink.  Every value is loaded once anyway.
+template <bool PEER> __device__ __forceinline__ double ldm(const double* p)
+{
+    return PEER ? __ldcg(p) : __ldg(p);
+}
+
+template <bool PEER>
 __device__ __forceinline__ void march_load(const MevpArgs& A, int r, int gi, int gip, int lane, MarchRow& R)
 {
     const int gr = plane_row(A, r), grp = plane_row(A, r + 1);
@@ -669,19 +687,19 @@ __device__ __forceinline__ void march_load(const MevpArgs& A, int r, int gi, int
     R.k = k;
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
-        R.s11[c] = __ldg(A.S11 + c * A.plane + k);
-        R.s12[c] = __ldg(A.S12 + c * A.plane + k);
-        R.s22[c] = __ldg(A.S22 + c * A.plane + k);
+        R.s11[c] = ldm<PEER>(A.S11 + c * A.plane + k);
+        R.s12[c] = ldm<PEER>(A.S12 + c * A.plane + k);
+        R.s22[c] = ldm<PEER>(A.S22 + c * A.plane + k);
     }
 #pragma unroll
     for (int g = 0; g < 4; ++g)
         R.pg[g] = __ldg(A.pg + g * A.plane + k);
-    R.un = __ldg(A.u + grp * A.nx + gi);
-    R.vn = __ldg(A.v + grp * A.nx + gi);
+    R.un = ldm<PEER>(A.u + grp * A.nx + gi);
+    R.vn = ldm<PEER>(A.v + grp * A.nx + gi);
     R.unr = R.vnr = 0.;
     if (lane == 31) { // the other lanes take it from their right neighbour (from_right)
-        R.unr = __ldg(A.u + grp * A.nx + gip);
-        R.vnr = __ldg(A.v + grp * A.nx + gip);
+        R.unr = ldm<PEER>(A.u + grp * A.nx + gip);
+        R.vnr = ldm<PEER>(A.v + grp * A.nx + gip);
     }
     R.uo = __ldg(A.uo + k);
     R.vo = __ldg(A.vo + k);
@@ -690,6 +708,31 @@ __device__ __forceinline__ void march_load(const MevpArgs& A, int r, int gi, int
     R.mdt = __ldg(A.nd + 2 * A.plane + k);
     R.acd = __ldg(A.nd + 3 * A.plane + k);
     R.act = !dirichlet(A, gi, gr - NSDG_GHOST);
+}
+
+// ---- peer halo: flags ----------------------------------------------------------------------
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p)
+{
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v)
+{
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// wait until the warps w-1, w, w+1 (ring in x) of the neighbour's boundary band have published
+// `need`: they produced the ghost columns this warp reads, and they have finished reading the
+// ghost columns this warp is about to overwrite in the other buffer set
+__device__ __forceinline__ void halo_wait(const unsigned* f, int w, int nw, unsigned need, int lane)
+{
+    if (lane < 3) {
+        int q = w - 1 + lane;
+        q = q < 0 ? q + nw : (q >= nw ? q - nw : q);
+        while ((int)(ld_acquire_sys(f + q) - need) < 0)
+            __nanosleep(64);
+    }
+    __syncwarp();
 }
 
 __device__ __forceinline__ double from_right(double x, double edge, int lane)
@@ -725,10 +768,11 @@ constexpr int MARCH_OWN = 28, MARCH_OFF = 2, MARCH_WPB = 4;
 // un/vn/unr/vnr are u^p of node row ra), Y: the loaded data of row ra, Z: target of the loads of
 // row ra+1.  d2p: divergence coefficients of S^{p+2}, cell row ra-2.  own: this lane stores row
 // ra-1.
+template <bool PEER>
 __device__ __forceinline__ void march_step(const MevpArgs& A, int ra, int gi, int gip, int lane, bool own,
     MarchRow& X, MarchRow& Y, MarchRow& Z, double (&d2p)[7])
 {
-    march_load(A, ra + 1, gi, gip, lane, Z); // consumed by the next step (wasted on the last one)
+    march_load<PEER>(A, ra + 1, gi, gip, lane, Z); // consumed by the next step (wasted on the last one)
 
     // ---- A: stress p+1 of cell row ra
     Y.unr = from_right(Y.un, Y.unr, lane);
@@ -770,39 +814,83 @@ __device__ __forceinline__ void march_step(const MevpArgs& A, int ra, int gi, in
         A.out0[X.k] = u2;
         A.out1[X.k] = v2;
     }
+    if (PEER && own) {
+        // rows the ring neighbours need as ghost rows go straight into their planes over NVLink:
+        // the two top rows (S, u, v) to the rank above, the bottom row (S) / two rows (u, v) to
+        // the rank below.  Strips never wrap, so the stored row ra-1 is a plane row.
+        const int rs = ra - 1;
+        if (rs >= NSDG_GHOST + A.nyl - 2) {
+            const int q = (rs - A.nyl) * A.nx + gi;
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                A.up[0][c * A.plane_up + q] = X.s11[c];
+                A.up[1][c * A.plane_up + q] = X.s12[c];
+                A.up[2][c * A.plane_up + q] = X.s22[c];
+            }
+            A.up[3][q] = u2;
+            A.up[4][q] = v2;
+        }
+        if (rs < NSDG_GHOST + 2) {
+            const int q = (rs + A.nyl_dn) * A.nx + gi;
+            if (rs == NSDG_GHOST) {
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    A.dn[0][c * A.plane_dn + q] = X.s11[c];
+                    A.dn[1][c * A.plane_dn + q] = X.s12[c];
+                    A.dn[2][c * A.plane_dn + q] = X.s22[c];
+                }
+            }
+            A.dn[3][q] = u2;
+            A.dn[4][q] = v2;
+        }
+    }
 #pragma unroll
     for (int c = 0; c < 7; ++c)
         d2p[c] = hi[c];
 }
 
+template <bool PEER>
 __global__ void __launch_bounds__(MARCH_WPB * 32, 2) mevp_march_kernel(const __grid_constant__ MevpArgs A)
 {
     const int lane = threadIdx.x & 31;
-    const int cb = (blockIdx.x * MARCH_WPB + (threadIdx.x >> 5)) * MARCH_OWN; // first owned column
+    const int wg = blockIdx.x * MARCH_WPB + (threadIdx.x >> 5); // warp's column block
+    const int cb = wg * MARCH_OWN; // first owned column
     if (cb >= A.nx)
         return; // whole warp
     const int cu = cb - MARCH_OFF + lane; // unwrapped column of this lane
     const int gi = wrap_idx(cu, A.nx);
     const int gip = (gi == A.nx - 1) ? 0 : gi + 1;
     const bool own_col = lane >= MARCH_OFF && lane < MARCH_OFF + MARCH_OWN && cu < A.nx;
-    const int b0 = A.r0 + blockIdx.y * A.band; // owned node/cell rows [b0, b1)
+    // PEER: the two boundary bands go first (blockIdx.y 0 and 1), their rows travel to the
+    // neighbours while the interior bands compute
+    int band = blockIdx.y;
+    if (PEER && band > 0)
+        band = (band == 1) ? (int)gridDim.y - 1 : band - 1;
+    const int b0 = A.r0 + band * A.band; // owned node/cell rows [b0, b1)
     const int b1 = min(b0 + A.band, A.r1);
     const int nsteps = b1 - b0 + 3;
+    if (PEER) {
+        // ghost rows below / above this band: produced by the neighbours' previous pair
+        if (b0 == A.r0)
+            halo_wait(A.flag_mine, wg, A.nflagw, A.seq - 1, lane);
+        if (b1 == A.r1)
+            halo_wait(A.flag_mine + A.nflagw, wg, A.nflagw, A.seq - 1, lane);
+    }
 
     MarchRow X = {}, Y, Z;
     X.mdt = 1.;
     double d2p[7] = { 0., 0., 0., 0., 0., 0., 0. };
     {
         const int g0 = plane_row(A, b0 - 2);
-        X.un = __ldg(A.u + g0 * A.nx + gi);
-        X.vn = __ldg(A.v + g0 * A.nx + gi);
-        X.unr = from_right(X.un, __ldg(A.u + g0 * A.nx + gip), lane);
-        X.vnr = from_right(X.vn, __ldg(A.v + g0 * A.nx + gip), lane);
+        X.un = ldm<PEER>(A.u + g0 * A.nx + gi);
+        X.vn = ldm<PEER>(A.v + g0 * A.nx + gi);
+        X.unr = from_right(X.un, ldm<PEER>(A.u + g0 * A.nx + gip), lane);
+        X.vnr = from_right(X.vn, ldm<PEER>(A.v + g0 * A.nx + gip), lane);
     }
-    march_load(A, b0 - 2, gi, gip, lane, Y);
+    march_load<PEER>(A, b0 - 2, gi, gip, lane, Y);
     // step s works on row ra = b0 - 2 + s and stores the owned row ra - 1 when 3 <= s; the first
     // steps run phases C / D on the zero-initialised records (finite values, never stored)
-#define NSDG_STEP(s, X, Y, Z) march_step(A, b0 - 2 + (s), gi, gip, lane, own_col && (s) >= 3, X, Y, Z, d2p)
+#define NSDG_STEP(s, X, Y, Z) march_step<PEER>(A, b0 - 2 + (s), gi, gip, lane, own_col && (s) >= 3, X, Y, Z, d2p)
     int s = 0;
 #pragma unroll 1
     for (; s + 2 < nsteps; s += 3) {
@@ -816,6 +904,18 @@ __global__ void __launch_bounds__(MARCH_WPB * 32, 2) mevp_march_kernel(const __g
             NSDG_STEP(s + 1, Y, Z, X);
     }
 #undef NSDG_STEP
+    if (PEER && (b0 == A.r0 || b1 == A.r1)) {
+        // publish: every lane's peer stores are ordered before the flag (fence by each storing
+        // lane, warp barrier, release store by lane 0)
+        __threadfence_system();
+        __syncwarp();
+        if (lane == 0) {
+            if (b1 == A.r1)
+                st_release_sys(A.flag_up + wg, A.seq); // slot [0] of the rank above: "from below"
+            if (b0 == A.r0)
+                st_release_sys(A.flag_dn + A.nflagw + wg, A.seq); // slot [1] of the rank below
+        }
+    }
 }
 
 MevpArgs base_args(DynState* d, double dt)
@@ -960,13 +1060,8 @@ int nsdg_mevp_fused(nsdg_ctx* ctx, double dt, const double* u, const double* v, 
     set_stress(A, Sold, Snew);
     A.r0 = (int)r0;
     A.r1 = (int)r1;
-    // tile shape: 32x8 by default; NSDG_FUSED_TILE=WxH selects another compiled variant (tuning)
-    static int tile = -1;
-    if (tile < 0) {
-        const char* e = getenv("NSDG_FUSED_TILE");
-        std::string t = e ? e : "32x8";
-        tile = t == "64x4" ? 1 : t == "32x16" ? 2 : t == "64x8" ? 3 : t == "16x16" ? 4 : 0;
-    }
+    // tile shape: 32x8 by default; nsdg_dyn_tuning.fused_tile selects another compiled variant
+    const int tile = d->tune.fused_tile;
 #define NSDG_FUSED_LAUNCH(TX, TY)                                                                 \
     do {                                                                                          \
         dim3 block(FusedCfg<TX, TY>::NT),                                                         \
@@ -996,32 +1091,6 @@ int nsdg_mevp_fused(nsdg_ctx* ctx, double dt, const double* u, const double* v, 
 
 // two fused sub-iterations: (u,v,S) at p -> (unew,vnew,Snew) at p+2; single rank (wrap) only
 namespace {
-int pair_tile()
-{
-    static int tile = -1;
-    if (tile < 0) {
-        const char* e = getenv("NSDG_PAIR_TILE");
-        std::string t = e ? e : "16x16";
-        tile = t == "32x8" ? 1 : t == "32x16" ? 2 : t == "16x16m3" ? 3 : t == "16x8" ? 4 : t == "16x12" ? 5 : 0;
-    }
-    return tile;
-}
-} // namespace
-
-namespace {
-// NSDG_MEVP_MARCH=<rows per band> of the marching pair kernel; 0 selects the tiled pair kernel;
-// unset (-1): the band height is chosen per strip by march_auto_rows
-int march_env()
-{
-    static int ry = -2;
-    if (ry == -2) {
-        const char* e = getenv("NSDG_MEVP_MARCH");
-        ry = e ? atoi(e) : -1;
-        if (ry < -1 || ry > 4096)
-            ry = -1;
-    }
-    return ry;
-}
 
 // Band height of the marching kernel for a strip of nrows x nx cells.  All CTAs of a launch cost
 // the same (rows + 3 march steps) except those of the last, shorter band, and 2 CTAs are resident
@@ -1060,16 +1129,21 @@ int march_auto_rows(int64_t nrows, int64_t nx, int sm_count, bool multi)
     return std::max(best, 1);
 }
 
+// peer halo possible for this strip (mapping exists, knob not off)
+bool peer_possible(const DynState* d) { return !d->wrap && d->peer_ok && d->tune.halo_peer >= 0; }
+
+// rows per band of the marching kernel; 0 = tiled pair kernel (nsdg_dyn_tuning.march_rows)
 int march_rows(nsdg_ctx* ctx)
 {
-    const int e = march_env();
-    if (e >= 0)
-        return e;
     DynState* d = ctx->dyn;
+    if (d->tune.march_rows != 0)
+        return d->tune.march_rows > 0 ? d->tune.march_rows : 0;
     // cached for the last geometry asked for (pure function of these four numbers)
     static thread_local int64_t c_ny = -1, c_nx = -1;
     static thread_local int c_sm = -1, c_strip = -1, c_ry = 64;
-    const int strip = d->wrap ? 0 : 1;
+    // the "at least four waves" rule of strips exists for the NCCL exchange beside the interior
+    // launch; with peer stores a strip takes the same band height as a single rank
+    const int strip = (d->wrap || peer_possible(d)) ? 0 : 1;
     if (c_ny != d->nyl || c_nx != d->nx || c_sm != ctx->sm_count || c_strip != strip) {
         c_ny = d->nyl;
         c_nx = d->nx;
@@ -1092,11 +1166,14 @@ int nsdg_mevp_pair_tile_rows(nsdg_ctx* ctx)
 {
     static const int ty[6] = { 16, 8, 16, 16, 8, 12 };
     const int ry = march_rows(ctx);
-    return ry ? ry : ty[pair_tile()];
+    return ry ? ry : ty[ctx->dyn->tune.pair_tile];
 }
 
+bool nsdg_mevp_peer_halo(nsdg_ctx* ctx) { return ctx->dyn && peer_possible(ctx->dyn) && march_rows(ctx) > 0; }
+
 int nsdg_mevp_pair(nsdg_ctx* ctx, double dt, const double* u, const double* v, double* unew,
-    double* vnew, double* const* Sold, double* const* Snew, int64_t r0, int64_t r1, cudaStream_t st)
+    double* vnew, double* const* Sold, double* const* Snew, int64_t r0, int64_t r1, cudaStream_t st,
+    unsigned peer_seq)
 {
     DynState* d = ctx->dyn;
     if (!st)
@@ -1109,7 +1186,7 @@ int nsdg_mevp_pair(nsdg_ctx* ctx, double dt, const double* u, const double* v, d
     set_stress(A, Sold, Snew);
     A.r0 = (int)r0;
     A.r1 = (int)r1;
-    const int tile = pair_tile();
+    const int tile = d->tune.pair_tile;
     const int nrows = (int)(r1 - r0);
     if (nrows <= 0)
         return NSDG_OK;
@@ -1117,10 +1194,31 @@ int nsdg_mevp_pair(nsdg_ctx* ctx, double dt, const double* u, const double* v, d
         const int nwarps = (int)((d->nx + MARCH_OWN - 1) / MARCH_OWN);
         A.band = ry;
         dim3 block(MARCH_WPB * 32), grid((unsigned)((nwarps + MARCH_WPB - 1) / MARCH_WPB), (unsigned)((nrows + ry - 1) / ry));
-        if (st == ctx->stream) {
-            NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<<<grid, block, 0, st>>>(A)));
+        if (peer_seq) {
+            NSDG_REQUIRE(ctx, peer_possible(d) && r0 == NSDG_GHOST && r1 == NSDG_GHOST + d->nyl && nwarps == d->nflagw,
+                NSDG_ESTATE, "peer halo launch needs the mapped neighbours and the whole strip");
+            // the neighbours' copies of the five output arrays sit at the same plane offsets of
+            // their slabs (every rank performs the same buffer swaps)
+            double* const outs[5] = { A.S11n, A.S12n, A.S22n, A.out0, A.out1 };
+            for (int q = 0; q < 5; ++q) {
+                const int64_t off = (outs[q] - d->slab) / d->plane;
+                NSDG_REQUIRE(ctx, outs[q] >= d->slab && off < NSDG_SLAB_PLANES, NSDG_ESTATE, "output array outside the slab");
+                A.up[q] = d->up.slab + off * d->up.plane;
+                A.dn[q] = d->dn.slab + off * d->dn.plane;
+            }
+            A.plane_up = (int)d->up.plane;
+            A.plane_dn = (int)d->dn.plane;
+            A.nyl_dn = (int)d->dn.nyl;
+            A.nflagw = d->nflagw;
+            A.flag_mine = d->flags;
+            A.flag_up = d->up.flags;
+            A.flag_dn = d->dn.flags;
+            A.seq = peer_seq;
+            NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<true><<<grid, block, 0, st>>>(A)));
+        } else if (st == ctx->stream) {
+            NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<false><<<grid, block, 0, st>>>(A)));
         } else { /* the per-kernel profiler brackets the compute stream only */
-            mevp_march_kernel<<<grid, block, 0, st>>>(A);
+            mevp_march_kernel<false><<<grid, block, 0, st>>>(A);
             NSDG_LAUNCHED(ctx);
         }
         return NSDG_OK;

@@ -91,7 +91,7 @@ struct CellOut {
 };
 
 // idt = 1/dt
-template <bool DIAG>
+template <bool DIAG, bool SLAB>
 __device__ __forceinline__ CellOut thermo_cell(
     const nsdg_thermo_params& P, double dt, double idt, const CellIn& in, double* diag)
 {
@@ -232,11 +232,17 @@ __device__ __forceinline__ CellOut thermo_cell(
     }
     { // newIceFormation :228-254
         double coolingFlux = Qow;
-        double deltaTml = -coolingFlux * rcp_pos(mlBulkCp) * dt;
+        // IEEE division: a cell with mld == 0 must give deltaTml = -/+inf (and take the new-ice
+        // branch with finite results) exactly as the reference does, not the NaN of the
+        // Newton reciprocal
+        double deltaTml = -coolingFlux / mlBulkCp * dt;
         double t1 = sst + deltaTml;
         if (t1 < tf) {
             // (tf - sst)/deltaTml * coolingFlux == (sst - tf) mlBulkCp / dt: the flux that takes
-            // the mixed layer exactly to the freezing point
+            // the mixed layer exactly to the freezing point.  KNOWN DIVERGENCE from the reference:
+            // with Qow == 0 exactly and sst < tf the reference evaluates (tf - sst)/(-0) * 0 = NaN
+            // (NextsimPhysics.cpp:244-247) and poisons the cell; the closed form stays finite
+            // (tests/test_gpu_thermo.py::test_zero_cooling_flux_below_freezing documents it).
             double sensibleFlux = Qio0;
             double latentFlux = coolingFlux - sensibleFlux;
             Qow = sensibleFlux;
@@ -294,7 +300,10 @@ __device__ __forceinline__ CellOut thermo_cell(
     o.tice0 = t_new;
     o.newice = newice;
     // slab-ocean closure (opt-in): the two fluxes the reference drops
-    o.sst = sst - dt * ((1 - cice) * Qow + cice * Qio) * rcp_pos(mlBulkCp);
+    if (SLAB)
+        o.sst = sst - dt * ((1 - cice) * Qow + cice * Qio) / mlBulkCp;
+    else
+        o.sst = sst;
     return o;
 }
 
@@ -317,7 +326,7 @@ __global__ void __launch_bounds__(256) thermo_kernel(const __grid_constant__ nsd
         v[q] = __ldg(ptr.f[q] + k);
     const CellIn a = { v[0], v[1], v[2], v[3], v[4], v[5], v[6], v[7], v[8], v[9], v[10], v[11], v[12], v[13], v[14] };
     double da[NSDG_THERMO_NDIAG];
-    const CellOut o = thermo_cell<DIAG>(P, dt, idt, a, da);
+    const CellOut o = thermo_cell<DIAG, SLAB>(P, dt, idt, a, da);
     ptr.f[NSDG_TF_HICE][k] = o.hice;
     ptr.f[NSDG_TF_CICE][k] = o.cice;
     ptr.f[NSDG_TF_HSNOW][k] = o.hsnow;
@@ -442,7 +451,8 @@ int nsdg_thermo_init(nsdg_ctx* ctx, int64_t ncells, int32_t nlayers)
 {
     NSDG_ENTER(ctx);
     NSDG_REQUIRE(ctx, ncells >= 0 && nlayers >= 1, NSDG_EINVAL, "ncells >= 0 and nlayers >= 1");
-    nsdg_thermo_free(ctx);
+    NSDG_REQUIRE(ctx, !ctx->thermo, NSDG_ESTATE,
+        "this context already holds a thermodynamics state: call nsdg_thermo_release first");
     ThermoState* t = new ThermoState;
     ctx->thermo = t;
     t->n = ncells;
@@ -459,6 +469,14 @@ int nsdg_thermo_init(nsdg_ctx* ctx, int64_t ncells, int32_t nlayers)
     return NSDG_OK;
 }
 
+int nsdg_thermo_release(nsdg_ctx* ctx)
+{
+    NSDG_ENTER(ctx);
+    NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    nsdg_thermo_free(ctx);
+    return NSDG_OK;
+}
+
 int nsdg_thermo_set_params(nsdg_ctx* ctx, const nsdg_thermo_params* p)
 {
     NSDG_ENTER(ctx);
@@ -472,6 +490,11 @@ int nsdg_thermo_set_params(nsdg_ctx* ctx, const nsdg_thermo_params* p)
     NSDG_REQUIRE(ctx, p->ocean_flux_kind == NSDG_OCEANFLUX_BASIC, NSDG_EINVAL,
         "unknown IIceOceanHeatFlux implementation id %d", p->ocean_flux_kind);
     NSDG_REQUIRE(ctx, p->h0 != 0., NSDG_EINVAL, "Hibler.h0 must be non-zero");
+    // the kernel takes 1/c_new by a Newton reciprocal without special-case paths: c_new >= min_conc
+    // must be strictly positive there
+    NSDG_REQUIRE(ctx, p->min_conc > 0. && p->min_thick >= 0., NSDG_EINVAL,
+        "min_conc must be > 0 and min_thick >= 0 (got %g, %g)", p->min_conc, p->min_thick);
+    NSDG_REQUIRE(ctx, p->ks > 0., NSDG_EINVAL, "thermoice0.ks must be > 0 (got %g)", p->ks);
     ctx->thermo->params = *p;
     return NSDG_OK;
 }

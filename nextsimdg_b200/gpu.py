@@ -9,8 +9,8 @@ import ctypes
 import numpy as np
 
 from . import _abi
-from ._abi import (DYN_FIELDS, THERMO_DIAG, THERMO_FIELDS, DynConfig, MevpParams, ThermoParams,
-                   c_double_p, check)
+from ._abi import (DYN_FIELDS, THERMO_DIAG, THERMO_FIELDS, DynConfig, DynTuning, MevpParams,
+                   ThermoParams, c_double_p, check)
 
 PROGNOSTIC = ("hice", "cice", "hsnow", "sst", "sss", "tice")
 FORCING = ("tair", "tdew", "slp", "qsw", "qlw", "mld", "snowfall", "wind")
@@ -39,9 +39,22 @@ class Context:
                                      "this package has no CPU path")
         self.h = h
         self.device = device
+        # the one thermodynamics / dynamics state this context holds (C ABI: a second *_init on a
+        # live state is NSDG_ESTATE); the Python classes hand the slot over explicitly
+        self._owner = {"thermo": None, "dyn": None}
+
+    def _take(self, kind, obj):
+        prev = self._owner[kind]
+        if prev is not None and prev is not obj:
+            prev.close()
+        self._owner[kind] = obj
 
     def close(self):
         if getattr(self, "h", None):
+            for kind in ("thermo", "dyn"):
+                if self._owner[kind] is not None:
+                    self._owner[kind]._released = True
+                    self._owner[kind] = None
             self.lib.nsdg_destroy(self.h)
             self.h = None
 
@@ -102,8 +115,38 @@ class Context:
     def comm_bytes_sent(self):
         return int(self.lib.nsdg_comm_bytes_sent(self.h))
 
+    @property
+    def halo_peer(self):
+        """True when the sub-cycle's halo goes through NVLink peer stores (no NCCL in the loop)."""
+        return bool(self.lib.nsdg_comm_halo_peer(self.h))
 
-class GpuStep:
+
+class _State:
+    """A state object of a context.  Creating another one of the same kind on the context
+    releases this one (explicitly, through nsdg_*_release); a released object raises on use."""
+    _kind = None
+    _released = False
+
+    @property
+    def h(self):
+        if self._released:
+            raise RuntimeError(f"{type(self).__name__}: this state was released (a newer "
+                               f"{type(self).__name__} took over its context, or close() was called)")
+        return self._h
+
+    def close(self):
+        if self._released:
+            return
+        self._released = True
+        ctx = self.ctx
+        if ctx._owner.get(self._kind) is self:
+            ctx._owner[self._kind] = None
+        if getattr(ctx, "h", None):
+            fn = ctx.lib.nsdg_thermo_release if self._kind == "thermo" else ctx.lib.nsdg_dyn_release
+            check(ctx.h, fn(ctx.h))
+
+
+class GpuStep(_State):
     """Drop-in for the reference's DevStep (core/src/DevStep.cpp:14-23) over SoA arrays.
 
     setInitialData gathers/uploads, iterate(dt) launches the fused kernel on device-resident
@@ -111,10 +154,14 @@ class GpuStep:
     (DevGrid: index i*nx + j, core/src/DevGridIO.cpp:107-109); tice is [cell][layer].
     """
 
+    _kind = "thermo"
+
     def __init__(self, ctx, ncells, nlayers=1, params=None):
-        self.ctx, self.lib, self.h = ctx, ctx.lib, ctx.h
+        self.ctx, self.lib, self._h = ctx, ctx.lib, ctx.h
         self.n, self.nlayers = int(ncells), int(nlayers)
+        ctx._take("thermo", None)
         check(self.h, self.lib.nsdg_thermo_init(self.h, self.n, self.nlayers))
+        ctx._take("thermo", self)
         self.set_params(params if params is not None else ThermoParams.defaults())
 
     def set_params(self, params):
@@ -220,19 +267,45 @@ class GpuStep:
         return pr
 
 
-class GpuDynamics:
+class GpuDynamics(_State):
     """DG transport (dG0/1/2) + mEVP on one strip of a structured periodic grid."""
 
+    _kind = "dyn"
+
     def __init__(self, ctx, nx, ny_global, hx, hy, ncomp=6, ny_local=None, j0=0, rk_order=0,
-                 limiter=0, mevp=None, flags=0):
-        self.ctx, self.lib, self.h = ctx, ctx.lib, ctx.h
+                 limiter=0, mevp=None, flags=0, tuning=None):
+        self.ctx, self.lib, self._h = ctx, ctx.lib, ctx.h
         self.nx, self.ny_global = int(nx), int(ny_global)
         self.ny = int(ny_local if ny_local is not None else ny_global)
         self.ncomp = int(ncomp)
         self.cfg = DynConfig(self.nx, self.ny_global, self.ny, int(j0), float(hx), float(hy),
                              self.ncomp, int(rk_order), int(limiter), int(flags))
+        ctx._take("dyn", None)
         check(self.h, self.lib.nsdg_dyn_init(self.h, ctypes.byref(self.cfg)))
+        ctx._take("dyn", self)
         self.set_mevp_params(mevp if mevp is not None else MevpParams.defaults())
+        if tuning:
+            self.set_tuning(**tuning)
+
+    def set_tuning(self, **knobs):
+        """nsdg_dyn_set_tuning on top of what is in effect: march_rows (0 auto, -1 tiled kernel),
+        pair, halo_overlap, halo_peer, transport_march, graph (-1 off / 0 default / 1 on),
+        pair_tile / fused_tile (id or "WxH")."""
+        t = self.get_tuning()
+        for k, v in knobs.items():
+            if k == "pair_tile" and isinstance(v, str):
+                v = DynTuning.PAIR_TILES.index(v)
+            if k == "fused_tile" and isinstance(v, str):
+                v = DynTuning.FUSED_TILES.index(v)
+            if k not in dict(DynTuning._fields_) or k == "reserved":
+                raise KeyError(k)
+            setattr(t, k, int(v))
+        check(self.h, self.lib.nsdg_dyn_set_tuning(self.h, ctypes.byref(t)))
+
+    def get_tuning(self):
+        t = DynTuning()
+        check(self.h, self.lib.nsdg_dyn_get_tuning(self.h, ctypes.byref(t)))
+        return t
 
     def set_mevp_params(self, p):
         self.mevp = p

@@ -186,8 +186,11 @@ def test_step_host_equals_resident_path(ctx):
 def test_deferred_host_steps_equal_resident_path(ctx):
     """nsdg_dyn_step_host_async: downloads of step k overlap step k+1, forcing of step k+1 goes
     up into alternate buffers while step k computes; every step's output must equal the resident
-    path's, with a forcing that changes from step to step."""
-    nx, ny, nsteps = 80, 48, 5
+    path's, with a forcing that changes from step to step.  Resident steps are enqueued right
+    before the first deferred call, so the compute stream has a backlog when the alternate
+    forcing buffers are created: their clearing must be ordered before the forcing upload on the
+    copy stream (it would zero the wind otherwise)."""
+    nx, ny, nsteps = 320, 256, 5
     F, hx, hy = S.box_case(nx, ny, 6)
     F["U"], F["V"] = random_velocity(nx, ny, 5, 0.05)
     mp = MevpParams.defaults()
@@ -195,8 +198,14 @@ def test_deferred_host_steps_equal_resident_path(ctx):
     names = ("H", "A", "U", "V", "S11", "S12", "S22")
     forcing = ("UATM", "VATM", "UOCN", "VOCN")
     fk = [{k: np.ascontiguousarray(F[k] * (1.0 + 0.1 * s)) for k in forcing} for s in range(nsteps)]
+
+    def preamble(d):
+        d.upload_all(F)
+        for _ in range(2):
+            d.step(120.0, 100)
+
     a = GpuDynamics(ctx, nx, ny, hx, hy, 6, mevp=mp)
-    a.upload_all(F)
+    preamble(a)
     ref = []
     for s in range(nsteps):
         for k in forcing:
@@ -205,8 +214,8 @@ def test_deferred_host_steps_equal_resident_path(ctx):
         ref.append({k: a.download(k) for k in names})
     a.step(120.0, 7)  # one more with the last forcing
     ref_last = {k: a.download(k) for k in names}
-    b = GpuDynamics(ctx, nx, ny, hx, hy, 6, mevp=mp)  # (one dynamics state per context: a is gone)
-    b.upload_all(F)
+    b = GpuDynamics(ctx, nx, ny, hx, hy, 6, mevp=mp)  # takes the context's dynamics slot over from a
+    preamble(b)  # still running when the first deferred step is enqueued
     outs = [{k: np.full(b.field_shape(k), np.nan) for k in names} for _ in range(nsteps)]
     for s in range(nsteps):
         b.step_host(120.0, 7, fk[s], outs[s], deferred=True)
@@ -397,23 +406,49 @@ def test_error_behaviour(ctx):
         dyn.upload("H", np.zeros((3, 16, 15)))
 
 
-def test_pair_kernel_variants_bit_identical():
+def test_pair_kernel_variants_bit_identical(ctx):
     """The sub-iteration kernels share their arithmetic: the marching pair kernel (default, band
-    heights chosen per grid / 64 / 16 / 5 rows) and the tiled pair kernel give the same bits on periodic and box
-    grids, ragged sizes and a grid narrower than the halo (tools/dyn_digest.py; the variant is
-    chosen per process by NSDG_MEVP_MARCH)."""
+    heights chosen per grid / 64 / 16 / 5 rows), the tiled pair kernel in two tile shapes and
+    single fused sub-iterations give the same bits on periodic and box grids, ragged sizes and a
+    grid narrower than the halo.  The variant is a per-context knob of the C ABI
+    (nsdg_dyn_set_tuning), so all of them run in this one process."""
     import os
-    import subprocess
     import sys
-    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    digests = {}
-    for march in ("auto", "64", "16", "5", "0"):
-        env = dict(os.environ)
-        env.pop("NSDG_MEVP_MARCH", None)  # auto: band height chosen per grid (march_auto_rows)
-        if march != "auto":
-            env["NSDG_MEVP_MARCH"] = march
-        r = subprocess.run([sys.executable, os.path.join(root, "tools", "dyn_digest.py")], env=env,
-                           capture_output=True, text=True, timeout=600)
-        assert r.returncode == 0, r.stderr[-2000:]
-        digests[march] = [ln for ln in r.stdout.splitlines() if ln.startswith("digest")][-1]
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+    import dyn_digest
+    variants = {"auto": {}, "march64": {"march_rows": 64}, "march16": {"march_rows": 16},
+                "march5": {"march_rows": 5}, "tiled": {"march_rows": -1},
+                "tiled32x8": {"march_rows": -1, "pair_tile": "32x8"}, "single": {"pair": -1},
+                "graph": {"graph": 1}, "nograph": {"graph": -1}}
+    digests = {k: dyn_digest.digest(ctx, v) for k, v in variants.items()}
     assert len(set(digests.values())) == 1, digests
+
+
+def test_tuning_roundtrip_and_state_ownership(ctx):
+    """nsdg_dyn_set_tuning / get_tuning; a second nsdg_dyn_init on a live context is NSDG_ESTATE
+    until nsdg_dyn_release; the Python classes hand the context's slot over explicitly and a
+    released object raises instead of touching its successor's state."""
+    import ctypes
+    from nextsimdg_b200._abi import NSDG_ESTATE, DynConfig
+    a = GpuDynamics(ctx, 32, 16, 1.0, 1.0, 3, tuning={"march_rows": 16, "halo_overlap": -1})
+    t = a.get_tuning()
+    assert (t.march_rows, t.halo_overlap, t.pair) == (16, -1, 0)
+    with pytest.raises(NsdgError):
+        a.set_tuning(march_rows=5000)
+    with pytest.raises(NsdgError):
+        a.set_tuning(pair=2)
+    cfg = DynConfig(32, 16, 16, 0, 1.0, 1.0, 3, 0, 0, 0)
+    assert ctx.lib.nsdg_dyn_init(ctx.h, ctypes.byref(cfg)) == NSDG_ESTATE
+    assert ctx.lib.nsdg_dyn_release(ctx.h) == 0
+    assert ctx.lib.nsdg_dyn_init(ctx.h, ctypes.byref(cfg)) == 0
+    assert ctx.lib.nsdg_dyn_release(ctx.h) == 0
+    a._released = True  # its state is gone (released behind its back above)
+    b = GpuDynamics(ctx, 32, 16, 1.0, 1.0, 3)
+    c = GpuDynamics(ctx, 32, 16, 1.0, 1.0, 3)  # takes the slot over: b is released explicitly
+    with pytest.raises(RuntimeError):
+        b.download("H")
+    assert c.download("H").shape == (3, 16, 32)
+    assert ctx.lib.nsdg_thermo_release(ctx.h) == 0
+    assert ctx.lib.nsdg_thermo_init(ctx.h, 10, 1) == 0
+    assert ctx.lib.nsdg_thermo_init(ctx.h, 10, 1) == NSDG_ESTATE
+    assert ctx.lib.nsdg_thermo_release(ctx.h) == 0

@@ -21,7 +21,7 @@ def test_library_exports_every_declared_symbol():
     declared -= {"nsdg_ctx"}
     assert declared == set(_abi.SYMBOLS), declared ^ set(_abi.SYMBOLS)
     lib = _abi.load()  # raises AttributeError on a missing export
-    assert lib.nsdg_abi_version() == 2
+    assert lib.nsdg_abi_version() == 3
     for name in declared:
         assert hasattr(lib, name)
 
