@@ -258,6 +258,10 @@ int nsdg_dyn_set_mevp_params(nsdg_ctx* ctx, const nsdg_mevp_params* p);
 /* interior of this rank's strip, host layout [ncomp_of_field][ny_local][nx] */
 int nsdg_dyn_upload(nsdg_ctx* ctx, int32_t field, const double* host);
 int nsdg_dyn_download(nsdg_ctx* ctx, int32_t field, double* host);
+/* a range of interior rows [row0, row0 + nrows) of the strip, host layout [ncomp][nrows][nx]:
+ * chunked I/O of strips too large to stage on the host in one piece */
+int nsdg_dyn_upload_rows(nsdg_ctx* ctx, int32_t field, int64_t row0, int64_t nrows, const double* host);
+int nsdg_dyn_download_rows(nsdg_ctx* ctx, int32_t field, int64_t row0, int64_t nrows, double* host);
 int nsdg_dyn_field_ncomp(const nsdg_ctx* ctx, int32_t field);
 /* device pointer of component 0, row 0 of the padded array: ny_local+4 rows, of which rows
  * 0,1 and ny_local+2, ny_local+3 are ghost rows of the strip decomposition and rows

@@ -115,6 +115,8 @@ SYMBOLS = {
     "nsdg_dyn_set_mevp_params": (ctypes.c_int, [_ctx, ctypes.POINTER(MevpParams)]),
     "nsdg_dyn_upload": (ctypes.c_int, [_ctx, _i32, c_double_p]),
     "nsdg_dyn_download": (ctypes.c_int, [_ctx, _i32, c_double_p]),
+    "nsdg_dyn_upload_rows": (ctypes.c_int, [_ctx, _i32, _i64, _i64, c_double_p]),
+    "nsdg_dyn_download_rows": (ctypes.c_int, [_ctx, _i32, _i64, _i64, c_double_p]),
     "nsdg_dyn_field_ncomp": (ctypes.c_int, [_ctx, _i32]),
     "nsdg_dyn_field_ptr": (ctypes.c_int, [_ctx, _i32, ctypes.POINTER(ctypes.c_void_p)]),
     "nsdg_transport_step": (ctypes.c_int, [_ctx, _i32, _dbl]),

@@ -636,6 +636,39 @@ int nsdg_dyn_download(nsdg_ctx* ctx, int32_t field, double* host)
     return NSDG_OK;
 }
 
+// rows [row0, row0 + nrows) of the strip's interior; host layout [ncomp][nrows][nx]
+int nsdg_dyn_upload_rows(nsdg_ctx* ctx, int32_t field, int64_t row0, int64_t nrows, const double* host)
+{
+    NSDG_ENTER(ctx);
+    DynState* d = ctx->dyn;
+    NSDG_REQUIRE(ctx, d, NSDG_ESTATE, "nsdg_dyn_init has not been called");
+    NSDG_REQUIRE(ctx, field >= 0 && field < NSDG_DF_COUNT && host, NSDG_EINVAL, "bad field/host");
+    NSDG_REQUIRE(ctx, row0 >= 0 && nrows >= 0 && row0 + nrows <= d->nyl, NSDG_EINVAL,
+        "rows [%lld, %lld) outside the strip of %lld rows", (long long)row0, (long long)(row0 + nrows), (long long)d->nyl);
+    const size_t chunk = (size_t)d->nx * nrows;
+    for (int c = 0; c < d->ncomp[field] && chunk; ++c)
+        NSDG_CUDA(ctx, cudaMemcpyAsync(d->f[field] + (size_t)c * d->plane + (NSDG_GHOST + row0) * d->nx, host + c * chunk,
+                           sizeof(double) * chunk, cudaMemcpyHostToDevice, ctx->stream));
+    NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return NSDG_OK;
+}
+
+int nsdg_dyn_download_rows(nsdg_ctx* ctx, int32_t field, int64_t row0, int64_t nrows, double* host)
+{
+    NSDG_ENTER(ctx);
+    DynState* d = ctx->dyn;
+    NSDG_REQUIRE(ctx, d, NSDG_ESTATE, "nsdg_dyn_init has not been called");
+    NSDG_REQUIRE(ctx, field >= 0 && field < NSDG_DF_COUNT && host, NSDG_EINVAL, "bad field/host");
+    NSDG_REQUIRE(ctx, row0 >= 0 && nrows >= 0 && row0 + nrows <= d->nyl, NSDG_EINVAL,
+        "rows [%lld, %lld) outside the strip of %lld rows", (long long)row0, (long long)(row0 + nrows), (long long)d->nyl);
+    const size_t chunk = (size_t)d->nx * nrows;
+    for (int c = 0; c < d->ncomp[field] && chunk; ++c)
+        NSDG_CUDA(ctx, cudaMemcpyAsync(host + c * chunk, d->f[field] + (size_t)c * d->plane + (NSDG_GHOST + row0) * d->nx,
+                           sizeof(double) * chunk, cudaMemcpyDeviceToHost, ctx->stream));
+    NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return NSDG_OK;
+}
+
 int nsdg_dyn_field_ptr(nsdg_ctx* ctx, int32_t field, void** device_ptr)
 {
     NSDG_ENTER(ctx);

@@ -325,6 +325,21 @@ class GpuDynamics(_State):
         check(self.h, self.lib.nsdg_dyn_download(self.h, DYN_FIELDS.index(name), _p(out)))
         return out
 
+    def upload_rows(self, name, row0, host):
+        """rows [row0, row0 + host.shape[-2]) of the strip; host is [ncomp][nrows][nx]"""
+        nc = self.field_shape(name)[0] if len(self.field_shape(name)) == 3 else 1
+        a = _f64(host)
+        nrows = a.size // (nc * self.nx)
+        if a.size != nc * nrows * self.nx:
+            raise ValueError(f"{name}: {a.size} values are not whole rows of {nc} x {self.nx}")
+        check(self.h, self.lib.nsdg_dyn_upload_rows(self.h, DYN_FIELDS.index(name), int(row0), nrows, _p(a)))
+
+    def download_rows(self, name, row0, nrows):
+        shp = self.field_shape(name)
+        out = np.empty(shp[:-2] + (int(nrows), self.nx))
+        check(self.h, self.lib.nsdg_dyn_download_rows(self.h, DYN_FIELDS.index(name), int(row0), int(nrows), _p(out)))
+        return out
+
     def upload_all(self, fields):
         for k, v in fields.items():
             self.upload(k, v)

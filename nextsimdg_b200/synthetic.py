@@ -103,16 +103,24 @@ def cone_case(nx, ny, ncomp):
     return project(f0, nx, ny, hx, hy, ncomp), u, v, hx, hy, f0
 
 
-def box_case(nx, ny, ncomp, L=512e3, t=0.0, rows=None, Ly=None):
+def box_case(nx, ny, ncomp, L=512e3, t=0.0, rows=None, Ly=None, separable=False, state=True):
     """Configs 3/5: Mehlmann et al. (2021)-style box test scaled to the grid: 512 km square,
     H = 0.3 + 0.005 (sin(6e-5 x) + sin(3e-5 y)), A = 1, anticyclonic ocean gyre, moving
     cyclone wind; closed box (NSDG_BC_BOX).  `rows=(j0, nl)` returns only that strip of the
-    global nx x ny grid.  Returns dict of fields + hx, hy."""
+    global nx x ny grid.  Returns dict of fields + hx, hy.
+    separable=True projects the x- and the y-part of H in 1-D and adds them (the projection is
+    linear; equal to the 2-D projection to rounding, ~30x faster: the 16384^2 bench grid);
+    state=False leaves out the all-zero U, V, S arrays (device buffers start zeroed)."""
     Ly = L if Ly is None else Ly
     hx, hy = L / nx, Ly / ny
     j0, nl = (0, ny) if rows is None else rows
-    H = project(lambda x, y: 0.3 + 0.005 * (np.sin(6e-5 * x) + np.sin(3e-5 * y)),
-                nx, nl, hx, hy, ncomp, nq=3, j0=j0)
+    if separable:
+        hx_part = project(lambda x, y: 0.3 + 0.005 * np.sin(6e-5 * x), nx, 1, hx, hy, ncomp, nq=3)
+        hy_part = project(lambda x, y: 0.005 * np.sin(3e-5 * y), 1, nl, hx, hy, ncomp, nq=3, j0=j0)
+        H = hx_part + hy_part
+    else:
+        H = project(lambda x, y: 0.3 + 0.005 * (np.sin(6e-5 * x) + np.sin(3e-5 * y)),
+                    nx, nl, hx, hy, ncomp, nq=3, j0=j0)
     A = np.zeros_like(H)
     A[0] = 1.0
     xn = (np.arange(nx) * hx)[None, :] + 0.0 * np.arange(nl)[:, None]
@@ -129,6 +137,8 @@ def box_case(nx, ny, ncomp, L=512e3, t=0.0, rows=None, Ly=None):
     s = 15.0 * np.e / 100.0 * np.exp(-rr / 100e3) / 1e3  # [1/s] per metre of distance
     uatm = -s * (np.cos(alpha) * (xn - cx) + np.sin(alpha) * (yn - cy))
     vatm = -s * (-np.sin(alpha) * (xn - cx) + np.cos(alpha) * (yn - cy))
+    if not state:
+        return dict(H=H, A=A, UATM=uatm, VATM=vatm, UOCN=uocn, VOCN=vocn), hx, hy
     z = np.zeros((ny, nx))
     return dict(H=H, A=A, U=z.copy(), V=z.copy(), S11=np.zeros((3, ny, nx)),
                 S12=np.zeros((3, ny, nx)), S22=np.zeros((3, ny, nx)), UATM=uatm, VATM=vatm,
