@@ -333,6 +333,7 @@ def kernel_table(prof, ms, cells_local, steps, peak):
         "mevp_march_kernel": BYTES_FUSED * cells_local * pairs,
         "mevp_pair_kernel": BYTES_FUSED * cells_local * pairs,
         "transport_stage_kernel": BYTES_TRANSPORT_STEP * cells_local * steps,
+        "transport_march_kernel": BYTES_TRANSPORT_STEP * cells_local * steps,
         "pressure_kernel": (12 + 4) * 8 * cells_local * steps,
         "nodal_kernel": (8 + 4) * 8 * cells_local * steps,
     }

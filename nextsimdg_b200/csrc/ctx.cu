@@ -59,7 +59,7 @@ void nsdg_prof_end(nsdg_ctx* ctx)
 }
 
 static const char* const KERNEL_NAMES[NSDG_K_COUNT] = { "thermo_kernel", "transport_stage_kernel",
-    "limit_kernel", "pressure_kernel", "nodal_kernel", "stress_kernel", "velocity_kernel",
+    "transport_march_kernel", "limit_kernel", "pressure_kernel", "nodal_kernel", "stress_kernel", "velocity_kernel",
     "mevp_fused_kernel", "mevp_pair_kernel", "mevp_march_kernel", "pack_rows", "unpack_rows", "blend_kernel", "other" };
 
 extern "C" {

@@ -27,6 +27,7 @@ struct ThermoState {
 enum NsdgKernelId {
     NSDG_K_THERMO = 0,
     NSDG_K_TRANSPORT,
+    NSDG_K_TRANSPORT_MARCH,
     NSDG_K_LIMIT,
     NSDG_K_PRESSURE,
     NSDG_K_NODAL,

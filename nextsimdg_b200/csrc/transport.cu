@@ -13,6 +13,7 @@
 // are free).  Algorithmic bytes per cell per stage: (NC src + NC base + NC dst)*NF*8 + 2*8
 // (the velocity reads of the second tracer's CTAs hit L2).
 #include "dyn.h"
+#include <algorithm>
 #include <cstdlib>
 
 namespace {
@@ -71,6 +72,151 @@ template <int NC> __device__ __forceinline__ void load_cell(double (&c)[NC], con
         c[q] = __ldg(p + q * plane + k);
 }
 
+// ---- dG2 cell arithmetic shared by the tiled and the marching stage kernels ------------------
+// Three-point Gauss rule, written out in tensor-product form (same integrals as the generic
+// quadrature loops, ~45 % fewer FP64 instructions): with a = xi - 1/2, b = eta - 1/2
+//   phi(a, b) = (c0 + c2 b + c4 (b^2 - 1/12)) + (c1 + c5 b) a + c3 (a^2 - 1/12)
+// is evaluated row by row, the velocity at a volume point is a lerp of the edge point
+// velocities, an edge trace is a 1-D quadratic trace(t) = T0 + T1 t + T2 (t^2 - 1/12) along the
+// edge, and the moments against psi are taken from row / column sums.  Gauss abscissae -g, 0, +g
+// with g^2 = 3/20: g^2 - 1/12 = 1/15.
+struct EdgeVel { // edge-normal velocities times weight / cell size at the edge Gauss points
+    double uL[3], uR[3], vB[3], vT[3];
+};
+struct Traces { // a cell's own traces on its four edges
+    double l[3], r[3], b[3], t[3]; // xi = 0, xi = 1, eta = 0, eta = 1
+};
+__device__ __forceinline__ void dg2_traces(const double (&c)[6], Traces& T)
+{
+    const double m0 = c[0] + c[3] * (1. / 6.), n0 = c[0] + c[4] * (1. / 6.);
+    T.l[0] = m0 - 0.5 * c[1];
+    T.l[1] = c[2] - 0.5 * c[5];
+    T.l[2] = c[4];
+    T.r[0] = m0 + 0.5 * c[1];
+    T.r[1] = c[2] + 0.5 * c[5];
+    T.r[2] = c[4];
+    T.b[0] = n0 - 0.5 * c[2];
+    T.b[1] = c[1] - 0.5 * c[5];
+    T.b[2] = c[3];
+    T.t[0] = n0 + 0.5 * c[2];
+    T.t[1] = c[1] + 0.5 * c[5];
+    T.t[2] = c[3];
+}
+// flux moments of one edge: M0 = sum F, M1 = sum F t, M2 = sum F (t^2 - 1/12); `minus` is the
+// trace on the side the normal velocity points away from
+__device__ __forceinline__ void dg2_edge(const double (&vn)[3], const double (&minus)[3], const double (&plus)[3],
+    double& M0, double& M1, double& M2)
+{
+    constexpr double g = 0.3872983346207417;
+    const double em = minus[0] + minus[2] * (1. / 15.), om = minus[1] * g;
+    const double ep = plus[0] + plus[2] * (1. / 15.), op = plus[1] * g;
+    const double F0 = vn[0] * (vn[0] > 0. ? em - om : ep - op);
+    const double F1 = vn[1] * (vn[1] > 0. ? minus[0] - minus[2] * (1. / 12.) : plus[0] - plus[2] * (1. / 12.));
+    const double F2 = vn[2] * (vn[2] > 0. ? em + om : ep + op);
+    const double s02 = F0 + F2;
+    M0 = s02 + F1;
+    M1 = g * (F2 - F0);
+    M2 = s02 * (1. / 15.) - F1 * (1. / 12.);
+}
+// rr = int_K phi (v . grad psi) - sum_e int_e (v.n) phi^ psi for one cell; nbL / nbR / nbB / nbT
+// are the NEIGHBOURS' traces on the shared edges (the left neighbour's xi = 1 trace, ...)
+__device__ __forceinline__ void dg2_cell(const double (&c)[6], const EdgeVel& V, const Traces& T,
+    const double (&nbL)[3], const double (&nbR)[3], const double (&nbB)[3], const double (&nbT)[3], double (&rr)[6])
+{
+    constexpr double g = 0.3872983346207417, W0 = 5. / 18., W1 = 8. / 18.;
+    constexpr double XI[3] = { 0.5 - g, 0.5, 0.5 + g };
+    constexpr double WQ[3] = { W0, W1, W0 };
+    double r0 = 0., r1 = 0., r2 = 0., r3 = 0., r4 = 0., r5 = 0.;
+    { // ---- volume term: int phi (u/hx dpsi/dxi + v/hy dpsi/deta)
+        // fx[b][a] = w_a w_b phi u/hx, fy[b][a] = w_a w_b phi v/hy (uL.. carry w_b/hx, vB.. w_a/hy)
+        double sx0 = 0., sx2 = 0., sxa = 0.; // sum_a fx of row b = 0, 2; sum over all of fx a/g
+        double sy_a0 = 0., sy_a2 = 0., syb = 0.; // sum_b fy of column a = 0, 2; sum of fy b/g
+#pragma unroll
+        for (int b = 0; b < 3; ++b) {
+            const double bb = XI[b] - 0.5;
+            const double p0 = (b == 1) ? c[0] - c[4] * (1. / 12.) : c[0] + c[2] * bb + c[4] * (1. / 15.);
+            const double p1 = (b == 1) ? c[1] : c[1] + c[5] * bb;
+            const double e = p0 + c[3] * (1. / 15.), o = p1 * g;
+            const double ph[3] = { e - o, p0 - c[3] * (1. / 12.), e + o };
+            const double du = V.uR[b] - V.uL[b];
+            double fxr[3], fyr[3];
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                const double uu = V.uL[b] + du * XI[a]; // w_b u / hx
+                const double vv = V.vB[a] + (V.vT[a] - V.vB[a]) * XI[b]; // w_a v / hy
+                fxr[a] = (ph[a] * WQ[a]) * uu;
+                fyr[a] = (ph[a] * WQ[b]) * vv;
+            }
+            const double sx = fxr[0] + fxr[1] + fxr[2], sy = fyr[0] + fyr[1] + fyr[2];
+            r1 += sx;
+            r2 += sy;
+            sxa += fxr[2] - fxr[0];
+            if (b == 0) {
+                sx0 = sx;
+                sy_a0 = fyr[0];
+                sy_a2 = fyr[2];
+                syb -= sy;
+            } else if (b == 2) {
+                sx2 = sx;
+                sy_a0 += fyr[0];
+                sy_a2 += fyr[2];
+                syb += sy;
+            } else {
+                sy_a0 += fyr[0];
+                sy_a2 += fyr[2];
+            }
+        }
+        r3 = (2. * g) * sxa; // sum fx 2a
+        r4 = (2. * g) * syb; // sum fy 2b
+        r5 = g * ((sx2 - sx0) + (sy_a2 - sy_a0)); // sum fx b + fy a
+    }
+    double L0, L1, L2, R0, R1, R2;
+    dg2_edge(V.uL, nbL, T.l, L0, L1, L2);
+    dg2_edge(V.uR, T.r, nbR, R0, R1, R2);
+    // psi on xi = 0 / 1: (1, -+1/2, t, 1/6, t^2 - 1/12, -+t/2); inflow through the left edge
+    // adds, outflow through the right edge subtracts
+    {
+        const double d0 = L0 - R0, s0 = L0 + R0, d1 = L1 - R1, s1 = L1 + R1;
+        r0 += d0;
+        r1 -= 0.5 * s0;
+        r2 += d1;
+        r3 += d0 * (1. / 6.);
+        r4 += L2 - R2;
+        r5 -= 0.5 * s1;
+    }
+    dg2_edge(V.vB, nbB, T.b, L0, L1, L2);
+    dg2_edge(V.vT, T.t, nbT, R0, R1, R2);
+    // psi on eta = 0 / 1: (1, t, -+1/2, t^2 - 1/12, 1/6, -+t/2)
+    {
+        const double d0 = L0 - R0, s0 = L0 + R0, d1 = L1 - R1, s1 = L1 + R1;
+        r0 += d0;
+        r1 += d1;
+        r2 -= 0.5 * s0;
+        r3 += L2 - R2;
+        r4 += d0 * (1. / 6.);
+        r5 -= 0.5 * s1;
+    }
+    rr[0] = r0;
+    rr[1] = r1;
+    rr[2] = r2;
+    rr[3] = r3;
+    rr[4] = r4;
+    rr[5] = r5;
+}
+__device__ __forceinline__ void edge_velocities(double u00, double u10, double u01, double u11, double v00,
+    double v10, double v01, double v11, double ihx, double ihy, EdgeVel& V)
+{
+    using G = Gauss<3>;
+#pragma unroll
+    for (int g = 0; g < 3; ++g) {
+        const double s = G::x(g), w = G::w(g);
+        V.uL[g] = (u00 * (1 - s) + u01 * s) * ihx * w;
+        V.uR[g] = (u10 * (1 - s) + u11 * s) * ihx * w;
+        V.vB[g] = (v00 * (1 - s) + v10 * s) * ihy * w;
+        V.vT[g] = (v01 * (1 - s) + v11 * s) * ihy * w;
+    }
+}
+
 struct StageArgs {
     const double* src[2];
     const double* base[2];
@@ -80,6 +226,7 @@ struct StageArgs {
     double a, b, dt, ihx, ihy;
     int nx, nyl, plane, r0, r1;
     int wrap, prefetch;
+    int band; // rows per band of the marching kernel
 };
 
 __device__ __forceinline__ void prefetch_line(const double* p)
@@ -145,126 +292,42 @@ __global__ void __launch_bounds__(256, MINB) transport_stage_kernel(const __grid
     }
 
     if constexpr (NC == 6) {
-        // dG2, three-point Gauss rule, written out in tensor-product form (same integrals as the
-        // generic branch below, ~45 % fewer FP64 instructions): with a = xi - 1/2, b = eta - 1/2
-        //   phi(a, b) = (c0 + c2 b + c4 (b^2 - 1/12)) + (c1 + c5 b) a + c3 (a^2 - 1/12)
-        // is evaluated row by row, the velocity at a volume point is a lerp of the edge point
-        // velocities, an edge trace is a 1-D quadratic, and the moments against psi are taken
-        // from row / column sums.  Gauss abscissae -g, 0, +g with g^2 = 3/20: g^2 - 1/12 = 1/15.
-        constexpr double g = 0.3872983346207417, W0 = 5. / 18., W1 = 8. / 18.;
-        constexpr double XI[3] = { 0.5 - g, 0.5, 0.5 + g };
-        constexpr double WQ[3] = { W0, W1, W0 };
-        double c[NC];
+        // dG2: written-out tensor-product form (dg2_cell); the neighbours' traces are evaluated
+        // from their coefficients with the expressions of dg2_traces
+        double c[NC], cn[NC], rr[NC];
         load_cell<NC>(c, A.src[f], A.plane, k);
-        double r0 = 0., r1 = 0., r2 = 0., r3 = 0., r4 = 0., r5 = 0.;
-        { // ---- volume term: int phi (u/hx dpsi/dxi + v/hy dpsi/deta)
-            // fx[b][a] = w_a w_b phi u/hx, fy[b][a] = w_a w_b phi v/hy (uL.. carry w_b/hx, vB.. w_a/hy)
-            double sx0 = 0., sx2 = 0., sxa = 0.; // sum_a fx of row b = 0, 2; sum over all of fx a/g
-            double sy_a0 = 0., sy_a2 = 0., syb = 0.; // sum_b fy of column a = 0, 2; sum of fy b/g
+        EdgeVel V;
 #pragma unroll
-            for (int b = 0; b < 3; ++b) {
-                const double bb = XI[b] - 0.5;
-                const double p0 = (b == 1) ? c[0] - c[4] * (1. / 12.) : c[0] + c[2] * bb + c[4] * (1. / 15.);
-                const double p1 = (b == 1) ? c[1] : c[1] + c[5] * bb;
-                const double e = p0 + c[3] * (1. / 15.), o = p1 * g;
-                const double ph[3] = { e - o, p0 - c[3] * (1. / 12.), e + o };
-                const double du = uR[b] - uL[b];
-                double fxr[3], fyr[3];
-#pragma unroll
-                for (int a = 0; a < 3; ++a) {
-                    const double uu = uL[b] + du * XI[a]; // w_b u / hx
-                    const double vv = vB[a] + (vT[a] - vB[a]) * XI[b]; // w_a v / hy
-                    fxr[a] = (ph[a] * WQ[a]) * uu;
-                    fyr[a] = (ph[a] * WQ[b]) * vv;
-                }
-                const double sx = fxr[0] + fxr[1] + fxr[2], sy = fyr[0] + fyr[1] + fyr[2];
-                r1 += sx;
-                r2 += sy;
-                sxa += fxr[2] - fxr[0];
-                if (b == 0) {
-                    sx0 = sx;
-                    sy_a0 = fyr[0];
-                    sy_a2 = fyr[2];
-                    syb -= sy;
-                } else if (b == 2) {
-                    sx2 = sx;
-                    sy_a0 += fyr[0];
-                    sy_a2 += fyr[2];
-                    syb += sy;
-                } else {
-                    sy_a0 += fyr[0];
-                    sy_a2 += fyr[2];
-                }
-            }
-            r3 = (2. * g) * sxa; // sum fx 2a
-            r4 = (2. * g) * syb; // sum fy 2b
-            r5 = g * ((sx2 - sx0) + (sy_a2 - sy_a0)); // sum fx b + fy a
+        for (int g = 0; g < 3; ++g) {
+            V.uL[g] = uL[g];
+            V.uR[g] = uR[g];
+            V.vB[g] = vB[g];
+            V.vT[g] = vT[g];
         }
-        // ---- edges: trace(t) = T0 + T1 t + T2 (t^2 - 1/12) along the edge, t = -g, 0, +g
-        // own traces
-        const double m0 = c[0] + c[3] * (1. / 6.), n0 = c[0] + c[4] * (1. / 6.);
-        const double tl[3] = { m0 - 0.5 * c[1], c[2] - 0.5 * c[5], c[4] }; // xi = 0
-        const double tr[3] = { m0 + 0.5 * c[1], c[2] + 0.5 * c[5], c[4] }; // xi = 1
-        const double tb[3] = { n0 - 0.5 * c[2], c[1] - 0.5 * c[5], c[3] }; // eta = 0
-        const double tt[3] = { n0 + 0.5 * c[2], c[1] + 0.5 * c[5], c[3] }; // eta = 1
-        // flux moments of one edge: M0 = sum F, M1 = sum F t, M2 = sum F (t^2 - 1/12); `minus` is
-        // the trace on the side the normal velocity points away from
-        auto edge = [&](const double (&vn)[3], const double (&minus)[3], const double (&plus)[3], double& M0,
-                        double& M1, double& M2) {
-            const double em = minus[0] + minus[2] * (1. / 15.), om = minus[1] * g;
-            const double ep = plus[0] + plus[2] * (1. / 15.), op = plus[1] * g;
-            const double F0 = vn[0] * (vn[0] > 0. ? em - om : ep - op);
-            const double F1 = vn[1] * (vn[1] > 0. ? minus[0] - minus[2] * (1. / 12.) : plus[0] - plus[2] * (1. / 12.));
-            const double F2 = vn[2] * (vn[2] > 0. ? em + om : ep + op);
-            const double s02 = F0 + F2;
-            M0 = s02 + F1;
-            M1 = g * (F2 - F0);
-            M2 = s02 * (1. / 15.) - F1 * (1. / 12.);
-        };
-        double cn[NC];
-        double L0, L1, L2, R0, R1, R2;
+        Traces T, N;
+        dg2_traces(c, T);
+        double nbL[3], nbR[3], nbB[3], nbT[3];
         load_cell<NC>(cn, A.src[f], A.plane, r * A.nx + im); // left neighbour: its xi = 1 trace
-        {
-            const double nb[3] = { cn[0] + cn[3] * (1. / 6.) + 0.5 * cn[1], cn[2] + 0.5 * cn[5], cn[4] };
-            edge(uL, nb, tl, L0, L1, L2);
-        }
+        dg2_traces(cn, N);
+#pragma unroll
+        for (int q = 0; q < 3; ++q)
+            nbL[q] = N.r[q];
         load_cell<NC>(cn, A.src[f], A.plane, r * A.nx + ip); // right neighbour: its xi = 0 trace
-        {
-            const double nb[3] = { cn[0] + cn[3] * (1. / 6.) - 0.5 * cn[1], cn[2] - 0.5 * cn[5], cn[4] };
-            edge(uR, tr, nb, R0, R1, R2);
-        }
-        // psi on xi = 0 / 1: (1, -+1/2, t, 1/6, t^2 - 1/12, -+t/2); inflow through the left edge
-        // adds, outflow through the right edge subtracts
-        {
-            const double d0 = L0 - R0, s0 = L0 + R0, d1 = L1 - R1, s1 = L1 + R1;
-            r0 += d0;
-            r1 -= 0.5 * s0;
-            r2 += d1;
-            r3 += d0 * (1. / 6.);
-            r4 += L2 - R2;
-            r5 -= 0.5 * s1;
-        }
+        dg2_traces(cn, N);
+#pragma unroll
+        for (int q = 0; q < 3; ++q)
+            nbR[q] = N.l[q];
         load_cell<NC>(cn, A.src[f], A.plane, rm * A.nx + i); // lower neighbour: its eta = 1 trace
-        {
-            const double nb[3] = { cn[0] + cn[4] * (1. / 6.) + 0.5 * cn[2], cn[1] + 0.5 * cn[5], cn[3] };
-            edge(vB, nb, tb, L0, L1, L2);
-        }
+        dg2_traces(cn, N);
+#pragma unroll
+        for (int q = 0; q < 3; ++q)
+            nbB[q] = N.t[q];
         load_cell<NC>(cn, A.src[f], A.plane, rp * A.nx + i); // upper neighbour: its eta = 0 trace
-        {
-            const double nb[3] = { cn[0] + cn[4] * (1. / 6.) - 0.5 * cn[2], cn[1] - 0.5 * cn[5], cn[3] };
-            edge(vT, tt, nb, R0, R1, R2);
-        }
-        // psi on eta = 0 / 1: (1, t, -+1/2, t^2 - 1/12, 1/6, -+t/2)
-        {
-            const double d0 = L0 - R0, s0 = L0 + R0, d1 = L1 - R1, s1 = L1 + R1;
-            r0 += d0;
-            r1 += d1;
-            r2 -= 0.5 * s0;
-            r3 += L2 - R2;
-            r4 += d0 * (1. / 6.);
-            r5 -= 0.5 * s1;
-        }
-        const double rr[NC] = { r0, r1, r2, r3, r4, r5 };
+        dg2_traces(cn, N);
+#pragma unroll
+        for (int q = 0; q < 3; ++q)
+            nbT[q] = N.b[q];
+        dg2_cell(c, V, T, nbL, nbR, nbB, nbT, rr);
         constexpr double IM[6] = { 1., 12., 12., 180., 180., 144. };
 #pragma unroll
         for (int q = 0; q < NC; ++q) {
@@ -376,6 +439,166 @@ __global__ void limit_kernel(double* phi, int64_t nx, int64_t nyl, int64_t plane
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Marching stage kernel (dG2): a WARP owns 28 columns and marches up a band of rows; a lane is a
+// column.  The neighbours' edge traces come from the lanes next door (6 shuffles per row) and
+// from the lane's own registers (the row below: kept from the previous step; the row above:
+// already loaded, because it is the next row to be processed), so every coefficient is loaded
+// ONCE per stage (plus a 2-column / 2-row halo per warp and band) instead of five times through
+// L1/L2, and the loads of row r+2 are issued at the top of step r: a register software pipeline
+// two rows deep.  Three row records rotate through the roles current / next / being loaded (loop
+// unrolled by three), so a register that is the target of a load in flight is never copied.
+// The per-cell arithmetic is dg2_cell, shared with the tiled kernel: results are bit-identical.
+constexpr int TM_OWN = 28, TM_OFF = 2, TM_WPB = 4;
+
+struct TRow {
+    double c[6]; // src coefficients of cell row r
+    double u, v; // velocity at node row r, own column
+    double base[6]; // RK base of cell row r
+    int k; // plane index of (row r, own column)
+};
+
+__device__ __forceinline__ int t_wrap(int i, int n)
+{
+    if (i < 0)
+        i += n;
+    else if (i >= n)
+        i -= n;
+    if (i < 0 || i >= n) { // grids narrower than the halo
+        i %= n;
+        if (i < 0)
+            i += n;
+    }
+    return i;
+}
+__device__ __forceinline__ int t_plane_row(const StageArgs& A, int r)
+{
+    if (A.wrap)
+        return NSDG_GHOST + t_wrap(r - NSDG_GHOST, A.nyl);
+    return max(0, min(r, A.nyl + 2 * NSDG_GHOST - 1));
+}
+__device__ __forceinline__ void tm_load_src(const StageArgs& A, int f, int r, int gi, TRow& R)
+{
+    const int k = t_plane_row(A, r) * A.nx + gi;
+    R.k = k;
+#pragma unroll
+    for (int q = 0; q < 6; ++q)
+        R.c[q] = __ldg(A.src[f] + q * A.plane + k);
+    R.u = __ldg(A.u + k);
+    R.v = __ldg(A.v + k);
+}
+__device__ __forceinline__ void tm_load_base(const StageArgs& A, int f, TRow& R)
+{
+#pragma unroll
+    for (int q = 0; q < 6; ++q)
+        R.base[q] = __ldg(A.base[f] + q * A.plane + R.k);
+}
+
+// one step of the march: X = row r (coefficients, velocity, base all arrived), Y = row r+1
+// (coefficients and velocity arrived, base requested here), Z = target of the loads of row r+2;
+// ttp = eta = 1 trace of row r-1
+template <bool HAS_BASE>
+__device__ __forceinline__ void tm_step(const StageArgs& A, int f, int r, int gi, bool own, TRow& X, TRow& Y,
+    TRow& Z, double (&ttp)[3])
+{
+    tm_load_src(A, f, r + 2, gi, Z);
+    if (HAS_BASE)
+        tm_load_base(A, f, Y);
+    EdgeVel V;
+    {
+        const double u10 = __shfl_down_sync(0xffffffffu, X.u, 1), u11 = __shfl_down_sync(0xffffffffu, Y.u, 1);
+        const double v10 = __shfl_down_sync(0xffffffffu, X.v, 1), v11 = __shfl_down_sync(0xffffffffu, Y.v, 1);
+        edge_velocities(X.u, u10, Y.u, u11, X.v, v10, Y.v, v11, A.ihx, A.ihy, V);
+    }
+    Traces T, TY;
+    dg2_traces(X.c, T);
+    dg2_traces(Y.c, TY);
+    double nbL[3], nbR[3], rr[6];
+#pragma unroll
+    for (int q = 0; q < 3; ++q) {
+        nbL[q] = __shfl_up_sync(0xffffffffu, T.r[q], 1); // left neighbour's xi = 1 trace
+        nbR[q] = __shfl_down_sync(0xffffffffu, T.l[q], 1); // right neighbour's xi = 0 trace
+    }
+    dg2_cell(X.c, V, T, nbL, nbR, ttp, TY.b, rr);
+    constexpr double IM[6] = { 1., 12., 12., 180., 180., 144. };
+    if (own) {
+#pragma unroll
+        for (int q = 0; q < 6; ++q) {
+            double val = X.c[q] + A.dt * IM[q] * rr[q];
+            if (HAS_BASE)
+                val = A.a * X.base[q] + A.b * val;
+            A.dst[f][q * A.plane + X.k] = val;
+        }
+    }
+#pragma unroll
+    for (int q = 0; q < 3; ++q)
+        ttp[q] = T.t[q];
+}
+
+template <bool HAS_BASE>
+__global__ void __launch_bounds__(TM_WPB * 32, 3) transport_march_kernel(const __grid_constant__ StageArgs A)
+{
+    const int lane = threadIdx.x & 31;
+    const int cb = (blockIdx.x * TM_WPB + (threadIdx.x >> 5)) * TM_OWN; // first owned column
+    if (cb >= A.nx)
+        return; // whole warp
+    const int cu = cb - TM_OFF + lane; // unwrapped column of this lane
+    const int gi = t_wrap(cu, A.nx);
+    const bool own = lane >= TM_OFF && lane < TM_OFF + TM_OWN && cu < A.nx;
+    const int f = blockIdx.z;
+    const int b0 = A.r0 + blockIdx.y * A.band; // owned rows [b0, b1)
+    const int b1 = min(b0 + A.band, A.r1);
+    double ttp[3];
+    TRow X, Y, Z;
+    {
+        tm_load_src(A, f, b0 - 1, gi, Z);
+        tm_load_src(A, f, b0, gi, X);
+        if (HAS_BASE)
+            tm_load_base(A, f, X);
+        tm_load_src(A, f, b0 + 1, gi, Y);
+        Traces T;
+        dg2_traces(Z.c, T);
+#pragma unroll
+        for (int q = 0; q < 3; ++q)
+            ttp[q] = T.t[q];
+    }
+    int r = b0;
+#pragma unroll 1
+    for (; r + 2 < b1; r += 3) {
+        tm_step<HAS_BASE>(A, f, r, gi, own, X, Y, Z, ttp);
+        tm_step<HAS_BASE>(A, f, r + 1, gi, own, Y, Z, X, ttp);
+        tm_step<HAS_BASE>(A, f, r + 2, gi, own, Z, X, Y, ttp);
+    }
+    if (r < b1) {
+        tm_step<HAS_BASE>(A, f, r, gi, own, X, Y, Z, ttp);
+        if (r + 1 < b1)
+            tm_step<HAS_BASE>(A, f, r + 1, gi, own, Y, Z, X, ttp);
+    }
+}
+
+// rows per band: all CTAs of a launch cost rows + 3 steps and `slots` are resident at a time, so
+// the launch takes whole waves; taller bands have fewer halo rows (cf. march_auto_rows, mevp.cu)
+int transport_band_rows(int64_t nrows, int64_t ctas_per_band, int64_t slots)
+{
+    int best = (int)std::min<int64_t>(nrows, 64);
+    double best_t = 1e300;
+    for (int64_t nb = 1; nb <= nrows; ++nb) {
+        const int64_t ry = (nrows + nb - 1) / nb;
+        if (ry > 2048)
+            continue;
+        if (ry < 24)
+            break;
+        const int64_t nbands = (nrows + ry - 1) / ry;
+        const int64_t waves = (nbands * ctas_per_band + slots - 1) / slots;
+        const double t = (double)waves * (double)(ry + 3);
+        if (t < best_t) {
+            best_t = t;
+            best = (int)ry;
+        }
+    }
+    return std::max(best, 1);
+}
+
 template <int NC, int MINB>
 void launch_stage(const StageArgs& A, bool has_base, dim3 grid, dim3 block, cudaStream_t s)
 {
@@ -418,9 +641,25 @@ int nsdg_transport_stage(nsdg_ctx* ctx, int nfields, double* const* src, double*
         pf = e ? atoi(e) : 1;
     }
     A.prefetch = pf;
+    const bool hb = base != nullptr;
+    // dG2 on grids that do not live in L2: the marching kernel (nsdg_dyn_tuning.transport_march:
+    // 1 forces it on any grid, -1 selects the one-thread-per-cell kernel)
+    const int tm = d->tune.transport_march;
+    if (d->nc == 6 && tm >= 0 && (tm > 0 || d->nx * d->nyl >= ((int64_t)1 << 20))) {
+        const int64_t nwarps = (d->nx + TM_OWN - 1) / TM_OWN, gx = (nwarps + TM_WPB - 1) / TM_WPB;
+        A.band = transport_band_rows(r1 - r0, gx * nfields, 3 * (int64_t)ctx->sm_count);
+        dim3 mblock(TM_WPB * 32), mgrid((unsigned)gx, (unsigned)((r1 - r0 + A.band - 1) / A.band), (unsigned)nfields);
+        nsdg_prof_begin(ctx, NSDG_K_TRANSPORT_MARCH);
+        if (hb)
+            transport_march_kernel<true><<<mgrid, mblock, 0, ctx->stream>>>(A);
+        else
+            transport_march_kernel<false><<<mgrid, mblock, 0, ctx->stream>>>(A);
+        nsdg_prof_end(ctx);
+        NSDG_LAUNCHED(ctx);
+        return NSDG_OK;
+    }
     dim3 block(64, 4);
     dim3 grid((unsigned)((d->nx + 63) / 64), (unsigned)((r1 - r0 + 3) / 4), (unsigned)nfields);
-    const bool hb = base != nullptr;
     nsdg_prof_begin(ctx, NSDG_K_TRANSPORT);
     static int minb = 0; // NSDG_TRANSPORT_MINB: resident-CTA target of the dG2 register budget (tuning)
     if (!minb) {

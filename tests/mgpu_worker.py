@@ -25,7 +25,9 @@ VARIANTS = (("peer", {}),
             ("nccl-overlap-rows16", {"halo_peer": -1, "march_rows": 16}),
             ("nccl-serial", {"halo_peer": -1, "halo_overlap": -1}),
             ("nccl-rows64", {"halo_peer": -1, "march_rows": 64}),
-            ("tiled", {"march_rows": -1}))
+            ("tiled", {"march_rows": -1}),
+            ("transport-march", {"transport_march": 1}),
+            ("transport-tiled", {"transport_march": -1}))
 
 
 def all_cases(world):
