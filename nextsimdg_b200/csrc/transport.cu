@@ -118,10 +118,11 @@ __device__ __forceinline__ void dg2_edge(const double (&vn)[3], const double (&m
     M1 = g * (F2 - F0);
     M2 = s02 * (1. / 15.) - F1 * (1. / 12.);
 }
-// rr = int_K phi (v . grad psi) - sum_e int_e (v.n) phi^ psi for one cell; nbL / nbR / nbB / nbT
-// are the NEIGHBOURS' traces on the shared edges (the left neighbour's xi = 1 trace, ...)
-__device__ __forceinline__ void dg2_cell(const double (&c)[6], const EdgeVel& V, const Traces& T,
-    const double (&nbL)[3], const double (&nbR)[3], const double (&nbB)[3], const double (&nbT)[3], double (&rr)[6])
+// rr = int_K phi (v . grad psi) - sum_e int_e (v.n) phi^ psi for one cell from
+// lm / rm / bm / tm: the flux moments (M0, M1, M2 of dg2_edge) of the left, right, bottom and top
+// edge.  The flux through an edge is the same number whichever of its two cells computes it.
+__device__ __forceinline__ void dg2_cell_m(const double (&c)[6], const EdgeVel& V, const double (&lm)[3],
+    const double (&rm)[3], const double (&bm)[3], const double (&tm)[3], double (&rr)[6])
 {
     constexpr double g = 0.3872983346207417, W0 = 5. / 18., W1 = 8. / 18.;
     constexpr double XI[3] = { 0.5 - g, 0.5, 0.5 + g };
@@ -170,29 +171,24 @@ __device__ __forceinline__ void dg2_cell(const double (&c)[6], const EdgeVel& V,
         r4 = (2. * g) * syb; // sum fy 2b
         r5 = g * ((sx2 - sx0) + (sy_a2 - sy_a0)); // sum fx b + fy a
     }
-    double L0, L1, L2, R0, R1, R2;
-    dg2_edge(V.uL, nbL, T.l, L0, L1, L2);
-    dg2_edge(V.uR, T.r, nbR, R0, R1, R2);
     // psi on xi = 0 / 1: (1, -+1/2, t, 1/6, t^2 - 1/12, -+t/2); inflow through the left edge
     // adds, outflow through the right edge subtracts
     {
-        const double d0 = L0 - R0, s0 = L0 + R0, d1 = L1 - R1, s1 = L1 + R1;
+        const double d0 = lm[0] - rm[0], s0 = lm[0] + rm[0], d1 = lm[1] - rm[1], s1 = lm[1] + rm[1];
         r0 += d0;
         r1 -= 0.5 * s0;
         r2 += d1;
         r3 += d0 * (1. / 6.);
-        r4 += L2 - R2;
+        r4 += lm[2] - rm[2];
         r5 -= 0.5 * s1;
     }
-    dg2_edge(V.vB, nbB, T.b, L0, L1, L2);
-    dg2_edge(V.vT, T.t, nbT, R0, R1, R2);
     // psi on eta = 0 / 1: (1, t, -+1/2, t^2 - 1/12, 1/6, -+t/2)
     {
-        const double d0 = L0 - R0, s0 = L0 + R0, d1 = L1 - R1, s1 = L1 + R1;
+        const double d0 = bm[0] - tm[0], s0 = bm[0] + tm[0], d1 = bm[1] - tm[1], s1 = bm[1] + tm[1];
         r0 += d0;
         r1 += d1;
         r2 -= 0.5 * s0;
-        r3 += L2 - R2;
+        r3 += bm[2] - tm[2];
         r4 += d0 * (1. / 6.);
         r5 -= 0.5 * s1;
     }
@@ -202,6 +198,18 @@ __device__ __forceinline__ void dg2_cell(const double (&c)[6], const EdgeVel& V,
     rr[3] = r3;
     rr[4] = r4;
     rr[5] = r5;
+}
+// rr = int_K phi (v . grad psi) - sum_e int_e (v.n) phi^ psi for one cell; nbL / nbR / nbB / nbT
+// are the NEIGHBOURS' traces on the shared edges (the left neighbour's xi = 1 trace, ...)
+__device__ __forceinline__ void dg2_cell(const double (&c)[6], const EdgeVel& V, const Traces& T,
+    const double (&nbL)[3], const double (&nbR)[3], const double (&nbB)[3], const double (&nbT)[3], double (&rr)[6])
+{
+    double lm[3], rm[3], bm[3], tm[3];
+    dg2_edge(V.uL, nbL, T.l, lm[0], lm[1], lm[2]);
+    dg2_edge(V.uR, T.r, nbR, rm[0], rm[1], rm[2]);
+    dg2_edge(V.vB, nbB, T.b, bm[0], bm[1], bm[2]);
+    dg2_edge(V.vT, T.t, nbT, tm[0], tm[1], tm[2]);
+    dg2_cell_m(c, V, lm, rm, bm, tm, rr);
 }
 __device__ __forceinline__ void edge_velocities(double u00, double u10, double u01, double u11, double v00,
     double v10, double v01, double v11, double ihx, double ihy, EdgeVel& V)
@@ -495,11 +503,13 @@ __device__ __forceinline__ void tm_load_base(const StageArgs& A, int f, TRow& R)
 }
 
 // one step of the march: X = row r (coefficients, velocity, base all arrived), Y = row r+1
-// (coefficients and velocity arrived, base requested here), Z = target of the loads of row r+2;
-// ttp = eta = 1 trace of row r-1
+// (coefficients and velocity arrived, base requested here), Z = target of the loads of row r+2.
+// Every edge flux is computed ONCE: a lane computes the flux through its left edge and takes the
+// one through its right edge from the lane on its right; the flux through the top edge is kept
+// (bm) as the next row's bottom flux, and so are the top edge's normal velocities (vb).
 template <bool HAS_BASE>
 __device__ __forceinline__ void tm_step(const StageArgs& A, int f, int r, int gi, bool own, TRow& X, TRow& Y,
-    TRow& Z, double (&ttp)[3])
+    TRow& Z, double (&bm)[3], double (&vb)[3])
 {
     tm_load_src(A, f, r + 2, gi, Z);
     if (HAS_BASE)
@@ -509,17 +519,23 @@ __device__ __forceinline__ void tm_step(const StageArgs& A, int f, int r, int gi
         const double u10 = __shfl_down_sync(0xffffffffu, X.u, 1), u11 = __shfl_down_sync(0xffffffffu, Y.u, 1);
         const double v10 = __shfl_down_sync(0xffffffffu, X.v, 1), v11 = __shfl_down_sync(0xffffffffu, Y.v, 1);
         edge_velocities(X.u, u10, Y.u, u11, X.v, v10, Y.v, v11, A.ihx, A.ihy, V);
+#pragma unroll
+        for (int q = 0; q < 3; ++q)
+            V.vB[q] = vb[q]; // == the previous row's vT (same nodes, same expression)
     }
     Traces T, TY;
     dg2_traces(X.c, T);
     dg2_traces(Y.c, TY);
-    double nbL[3], nbR[3], rr[6];
+    double nbL[3], lm[3], rm[3], tm[3], rr[6];
 #pragma unroll
-    for (int q = 0; q < 3; ++q) {
+    for (int q = 0; q < 3; ++q)
         nbL[q] = __shfl_up_sync(0xffffffffu, T.r[q], 1); // left neighbour's xi = 1 trace
-        nbR[q] = __shfl_down_sync(0xffffffffu, T.l[q], 1); // right neighbour's xi = 0 trace
-    }
-    dg2_cell(X.c, V, T, nbL, nbR, ttp, TY.b, rr);
+    dg2_edge(V.uL, nbL, T.l, lm[0], lm[1], lm[2]);
+#pragma unroll
+    for (int q = 0; q < 3; ++q)
+        rm[q] = __shfl_down_sync(0xffffffffu, lm[q], 1); // right edge = the right neighbour's left edge
+    dg2_edge(V.vT, T.t, TY.b, tm[0], tm[1], tm[2]);
+    dg2_cell_m(X.c, V, lm, rm, bm, tm, rr);
     constexpr double IM[6] = { 1., 12., 12., 180., 180., 144. };
     if (own) {
 #pragma unroll
@@ -531,8 +547,10 @@ __device__ __forceinline__ void tm_step(const StageArgs& A, int f, int r, int gi
         }
     }
 #pragma unroll
-    for (int q = 0; q < 3; ++q)
-        ttp[q] = T.t[q];
+    for (int q = 0; q < 3; ++q) {
+        bm[q] = tm[q];
+        vb[q] = V.vT[q];
+    }
 }
 
 template <bool HAS_BASE>
@@ -548,31 +566,28 @@ __global__ void __launch_bounds__(TM_WPB * 32, 3) transport_march_kernel(const _
     const int f = blockIdx.z;
     const int b0 = A.r0 + blockIdx.y * A.band; // owned rows [b0, b1)
     const int b1 = min(b0 + A.band, A.r1);
-    double ttp[3];
+    // The march starts one row below the band: that step computes the flux through the bottom
+    // edge of the band's first row (its own top edge) with the SAME instruction sequence every
+    // other row goes through, so a cell's result does not depend on where the band boundaries
+    // fall (no separately compiled prologue arithmetic); nothing is stored for it.
+    double bm[3] = { 0., 0., 0. }, vb[3] = { 0., 0., 0. };
     TRow X, Y, Z;
-    {
-        tm_load_src(A, f, b0 - 1, gi, Z);
-        tm_load_src(A, f, b0, gi, X);
-        if (HAS_BASE)
-            tm_load_base(A, f, X);
-        tm_load_src(A, f, b0 + 1, gi, Y);
-        Traces T;
-        dg2_traces(Z.c, T);
-#pragma unroll
-        for (int q = 0; q < 3; ++q)
-            ttp[q] = T.t[q];
-    }
-    int r = b0;
+    tm_load_src(A, f, b0 - 1, gi, X);
+    tm_load_src(A, f, b0, gi, Y);
+    X.base[0] = X.base[1] = X.base[2] = X.base[3] = X.base[4] = X.base[5] = 0.;
+    int r = b0 - 1;
+    tm_step<HAS_BASE>(A, f, r, gi, false, X, Y, Z, bm, vb);
+    ++r;
 #pragma unroll 1
     for (; r + 2 < b1; r += 3) {
-        tm_step<HAS_BASE>(A, f, r, gi, own, X, Y, Z, ttp);
-        tm_step<HAS_BASE>(A, f, r + 1, gi, own, Y, Z, X, ttp);
-        tm_step<HAS_BASE>(A, f, r + 2, gi, own, Z, X, Y, ttp);
+        tm_step<HAS_BASE>(A, f, r, gi, own, Y, Z, X, bm, vb);
+        tm_step<HAS_BASE>(A, f, r + 1, gi, own, Z, X, Y, bm, vb);
+        tm_step<HAS_BASE>(A, f, r + 2, gi, own, X, Y, Z, bm, vb);
     }
     if (r < b1) {
-        tm_step<HAS_BASE>(A, f, r, gi, own, X, Y, Z, ttp);
+        tm_step<HAS_BASE>(A, f, r, gi, own, Y, Z, X, bm, vb);
         if (r + 1 < b1)
-            tm_step<HAS_BASE>(A, f, r + 1, gi, own, Y, Z, X, ttp);
+            tm_step<HAS_BASE>(A, f, r + 1, gi, own, Z, X, Y, bm, vb);
     }
 }
 

@@ -374,7 +374,8 @@ def test_full_size_4096sq_is_the_tiled_small_problem(ctx):
     mp = MevpParams.defaults()
     mp.bc = BC_PERIODIC
     names = ("H", "A", "U", "V", "S11", "S12", "S22")
-    small = GpuDynamics(ctx, m, m, hx, hy, 6, mevp=mp)
+    # the same stage kernel on both grids (the default picks the marching kernel from 2^20 cells)
+    small = GpuDynamics(ctx, m, m, hx, hy, 6, mevp=mp, tuning={"transport_march": 1})
     small.upload_all(F)
     small.step(120.0, nsub)
     got_small = {k: small.download(k) for k in names}
@@ -382,7 +383,7 @@ def test_full_size_4096sq_is_the_tiled_small_problem(ctx):
                      120.0, nsub)
     for k, a in zip(names, ref):
         assert maxrel(got_small[k], a) < RTOL, k
-    big = GpuDynamics(ctx, n, n, hx, hy, 6, mevp=mp)
+    big = GpuDynamics(ctx, n, n, hx, hy, 6, mevp=mp, tuning={"transport_march": 1})
     big.upload_all({k: np.tile(v, (1, reps, reps) if v.ndim == 3 else (reps, reps)) for k, v in F.items()})
     big.step(120.0, nsub)
     for k in names:
@@ -420,10 +421,50 @@ def test_pair_kernel_variants_bit_identical(ctx):
     variants = {"auto": {}, "march64": {"march_rows": 64}, "march16": {"march_rows": 16},
                 "march5": {"march_rows": 5}, "tiled": {"march_rows": -1},
                 "tiled32x8": {"march_rows": -1, "pair_tile": "32x8"}, "single": {"pair": -1},
-                "graph": {"graph": 1}, "nograph": {"graph": -1},
-                "transport-march": {"transport_march": 1}, "transport-tiled": {"transport_march": -1}}
-    digests = {k: dyn_digest.digest(ctx, v) for k, v in variants.items()}
+                "graph": {"graph": 1}, "nograph": {"graph": -1}}
+    # the transport kernel is pinned: the marching and the one-thread-per-cell stage kernels share
+    # their arithmetic but not the compiler's FMA contraction choices (last-bit differences, below)
+    digests = {k: dyn_digest.digest(ctx, dict(v, transport_march=-1)) for k, v in variants.items()}
     assert len(set(digests.values())) == 1, digests
+    digests = {k: dyn_digest.digest(ctx, dict(variants[k], transport_march=1)) for k in ("auto", "march16", "tiled", "graph")}
+    assert len(set(digests.values())) == 1, digests
+
+
+@pytest.mark.parametrize("shape,bc", [((300, 211), BC_PERIODIC), ((64, 48), BC_BOX), ((17, 5), BC_PERIODIC),
+                                      ((1024, 1024), BC_BOX), ((29, 70), BC_BOX)])
+def test_transport_marching_kernel_against_tiled_kernel_and_oracle(ctx, shape, bc):
+    """The marching dG2 stage kernel (every edge flux computed once, neighbours by shuffle and
+    from registers) against the one-thread-per-cell kernel: same integrals, agreement to the last
+    bits (1e-14 of the field's max norm after three SSP-RK3 steps; the difference is the
+    compiler's FMA contraction), and both within 1e-11 of the oracle.  Ragged sizes, a grid
+    narrower than a warp's 28 columns, fewer rows than the pipeline depth."""
+    nx, ny = shape
+    F, hx, hy = S.box_case(nx, ny, 6)
+    r = np.random.default_rng(9)
+    for k in range(1, 6):
+        F["H"][k] = 0.02 * r.standard_normal((ny, nx))
+        F["A"][k] = 0.01 * r.standard_normal((ny, nx))
+    F["U"], F["V"] = random_velocity(nx, ny, 3, 0.3)
+    if bc == BC_BOX:
+        F["U"][0, :] = F["U"][:, 0] = F["V"][0, :] = F["V"][:, 0] = 0.0
+    mp = MevpParams.defaults()
+    mp.bc = bc
+    dt = 0.1 * min(hx, hy) / 1.5
+    out = {}
+    for name, tm in (("march", 1), ("tiled", -1)):
+        dyn = GpuDynamics(ctx, nx, ny, hx, hy, 6, mevp=mp, tuning={"transport_march": tm})
+        dyn.upload_all(F)
+        for _ in range(3):
+            dyn.transport_step(dt)
+        out[name] = {k: dyn.download(k) for k in ("H", "A")}
+        dyn.close()
+    for k in ("H", "A"):
+        assert maxrel(out["march"][k], out["tiled"][k]) < 1e-14, k
+        if nx * ny <= 300 * 211:
+            ref = F[k]
+            for _ in range(3):
+                ref = O.transport_step(ref, F["U"], F["V"], hx, hy, dt)
+            assert maxrel(out["march"][k], ref) < RTOL, k
 
 
 def test_tuning_roundtrip_and_state_ownership(ctx):
