@@ -19,7 +19,9 @@ COMMON = ["-std=c++17", "-O3", "-lineinfo", "-Xcompiler", "-fPIC"]
 SOURCES = {
     "ctx.cu": [],
     "thermo.cu": [],
-    "transport.cu": [],
+    # no automatic FMA contraction: every fused multiply-add of the transport arithmetic is written
+    # out, so that all kernels and all unrolled loop copies round alike (see transport.cu)
+    "transport.cu": ["-fmad=false"],
     "mevp.cu": [],
     "dyn.cu": [],
     "comm.cu": [],

@@ -216,8 +216,15 @@ int mevp_cycle(nsdg_ctx* ctx, double dt, int nsub)
     // poll a per-warp sequence number (mevp.cu).  No pack / NCCL / unpack, no second stream.
     const bool peer = multi && pair && nsdg_mevp_peer_halo(ctx);
     const bool overlap = multi && pair && !peer && d->tune.halo_overlap >= 0 && ntr >= ntop + 2 && ty >= 2;
+    bool peer_pending = false; // neighbours may still be storing into this rank's ghost rows
     for (int p = 0; p < nsub; ++p) {
         bool paired = false;
+        if (peer_pending && !(pair && p + 1 < nsub)) {
+            // the next kernel is not a peer pair (which polls the flags itself)
+            if ((rc = nsdg_mevp_peer_drain(ctx)))
+                return rc;
+            peer_pending = false;
+        }
         int64_t rest0 = r0, rest1 = r0; // interior rows that run beside the exchange
         if (pair && p + 1 < nsub) {
             if (peer) {
@@ -225,6 +232,7 @@ int mevp_cycle(nsdg_ctx* ctx, double dt, int nsub)
                     return rc;
                 // rows this rank stored into its neighbours: S 2 up + 1 down, u, v 2 + 2
                 nsdg_comm_count_bytes(ctx, (int64_t)(9 * 3 + 2 * 4) * d->nx * 8);
+                peer_pending = true;
             } else if (overlap) {
                 // boundary tile rows on the (high-priority) communication stream, behind
                 // everything issued so far
@@ -283,6 +291,8 @@ int mevp_cycle(nsdg_ctx* ctx, double dt, int nsub)
         std::swap(u, u2);
         std::swap(v, v2);
     }
+    if (peer_pending && (rc = nsdg_mevp_peer_drain(ctx)))
+        return rc;
     d->f[NSDG_DF_U] = u;
     d->f[NSDG_DF_V] = v;
     d->u2 = u2;

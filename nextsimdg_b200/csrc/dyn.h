@@ -123,6 +123,7 @@ int nsdg_mevp_pair_tile_rows(nsdg_ctx* ctx);
 // true when the sub-cycle of this strip exchanges its halo by peer stores (mapping exists, the
 // marching kernel is selected and the knob is not off)
 bool nsdg_mevp_peer_halo(nsdg_ctx* ctx);
+int nsdg_mevp_peer_drain(nsdg_ctx* ctx);
 
 // comm.cu -----------------------------------------------------------------------------------
 // Ring halo exchange of up to 3 plane groups in ONE message per neighbour.  No-op on a single

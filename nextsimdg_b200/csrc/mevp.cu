@@ -674,12 +674,12 @@ struct MarchRow {
 // PEER: the ghost rows of S, u, v are written by the neighbour GPU while this kernel runs, so the
 // loads must not go through the (non-coherent) L1 / read-only path: ld.global.cg reads at L2, the
 // point of coherence for peer stores arriving over NVLink.  Every value is loaded once anyway.
-template <bool PEER> __device__ __forceinline__ double ldm(const double* p)
+template <bool CG> __device__ __forceinline__ double ldm(const double* p)
 {
-    return PEER ? __ldcg(p) : __ldg(p);
+    return CG ? __ldcg(p) : __ldg(p);
 }
 
-template <bool PEER>
+template <bool CG>
 __device__ __forceinline__ void march_load(const MevpArgs& A, int r, int gi, int gip, int lane, MarchRow& R)
 {
     const int gr = plane_row(A, r), grp = plane_row(A, r + 1);
@@ -687,19 +687,19 @@ __device__ __forceinline__ void march_load(const MevpArgs& A, int r, int gi, int
     R.k = k;
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
-        R.s11[c] = ldm<PEER>(A.S11 + c * A.plane + k);
-        R.s12[c] = ldm<PEER>(A.S12 + c * A.plane + k);
-        R.s22[c] = ldm<PEER>(A.S22 + c * A.plane + k);
+        R.s11[c] = ldm<CG>(A.S11 + c * A.plane + k);
+        R.s12[c] = ldm<CG>(A.S12 + c * A.plane + k);
+        R.s22[c] = ldm<CG>(A.S22 + c * A.plane + k);
     }
 #pragma unroll
     for (int g = 0; g < 4; ++g)
         R.pg[g] = __ldg(A.pg + g * A.plane + k);
-    R.un = ldm<PEER>(A.u + grp * A.nx + gi);
-    R.vn = ldm<PEER>(A.v + grp * A.nx + gi);
+    R.un = ldm<CG>(A.u + grp * A.nx + gi);
+    R.vn = ldm<CG>(A.v + grp * A.nx + gi);
     R.unr = R.vnr = 0.;
     if (lane == 31) { // the other lanes take it from their right neighbour (from_right)
-        R.unr = ldm<PEER>(A.u + grp * A.nx + gip);
-        R.vnr = ldm<PEER>(A.v + grp * A.nx + gip);
+        R.unr = ldm<CG>(A.u + grp * A.nx + gip);
+        R.vnr = ldm<CG>(A.v + grp * A.nx + gip);
     }
     R.uo = __ldg(A.uo + k);
     R.vo = __ldg(A.vo + k);
@@ -724,15 +724,14 @@ __device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v)
 // wait until the warps w-1, w, w+1 (ring in x) of the neighbour's boundary band have published
 // `need`: they produced the ghost columns this warp reads, and they have finished reading the
 // ghost columns this warp is about to overwrite in the other buffer set
+// (all lanes poll and the loop exits on a warp vote: control flow stays warp-uniform, so the
+// compiler keeps treating the warp as converged for the shuffles of the march)
 __device__ __forceinline__ void halo_wait(const unsigned* f, int w, int nw, unsigned need, int lane)
 {
-    if (lane < 3) {
-        int q = w - 1 + lane;
-        q = q < 0 ? q + nw : (q >= nw ? q - nw : q);
-        while ((int)(ld_acquire_sys(f + q) - need) < 0)
-            __nanosleep(64);
-    }
-    __syncwarp();
+    int q = w - 1 + min(lane, 2);
+    q = q < 0 ? q + nw : (q >= nw ? q - nw : q);
+    while (!__all_sync(0xffffffffu, (int)(ld_acquire_sys(f + q) - need) >= 0))
+        __nanosleep(64);
 }
 
 __device__ __forceinline__ double from_right(double x, double edge, int lane)
@@ -764,15 +763,46 @@ __device__ __forceinline__ void march_div(const MevpArgs& A, const double (&lo)[
 
 constexpr int MARCH_OWN = 28, MARCH_OFF = 2, MARCH_WPB = 4;
 
+__device__ __forceinline__ void peer_store(const MevpArgs& A, int rs, int gi, bool own, bool up, bool dn,
+    const double (&s11)[3], const double (&s12)[3], const double (&s22)[3], double u2, double v2)
+{
+    if (!own)
+        return;
+    if (up) {
+        const int q = (rs - A.nyl) * A.nx + gi;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            A.up[0][c * A.plane_up + q] = s11[c];
+            A.up[1][c * A.plane_up + q] = s12[c];
+            A.up[2][c * A.plane_up + q] = s22[c];
+        }
+        A.up[3][q] = u2;
+        A.up[4][q] = v2;
+    }
+    if (dn) {
+        const int q = (rs + A.nyl_dn) * A.nx + gi;
+        if (rs == NSDG_GHOST) {
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                A.dn[0][c * A.plane_dn + q] = s11[c];
+                A.dn[1][c * A.plane_dn + q] = s12[c];
+                A.dn[2][c * A.plane_dn + q] = s22[c];
+            }
+        }
+        A.dn[3][q] = u2;
+        A.dn[4][q] = v2;
+    }
+}
+
 // One step of the march at row ra.  X: row ra-1 (S^{p+1}, P_g, node constants, u^{p+1}; its
 // un/vn/unr/vnr are u^p of node row ra), Y: the loaded data of row ra, Z: target of the loads of
 // row ra+1.  d2p: divergence coefficients of S^{p+2}, cell row ra-2.  own: this lane stores row
 // ra-1.
-template <bool PEER>
+template <bool PEER, bool CG>
 __device__ __forceinline__ void march_step(const MevpArgs& A, int ra, int gi, int gip, int lane, bool own,
     MarchRow& X, MarchRow& Y, MarchRow& Z, double (&d2p)[7])
 {
-    march_load<PEER>(A, ra + 1, gi, gip, lane, Z); // consumed by the next step (wasted on the last one)
+    march_load<CG>(A, ra + 1, gi, gip, lane, Z); // consumed by the next step (wasted on the last one)
 
     // ---- A: stress p+1 of cell row ra
     Y.unr = from_right(Y.un, Y.unr, lane);
@@ -814,42 +844,23 @@ __device__ __forceinline__ void march_step(const MevpArgs& A, int ra, int gi, in
         A.out0[X.k] = u2;
         A.out1[X.k] = v2;
     }
-    if (PEER && own) {
+    if (PEER) {
         // rows the ring neighbours need as ghost rows go straight into their planes over NVLink:
         // the two top rows (S, u, v) to the rank above, the bottom row (S) / two rows (u, v) to
-        // the rank below.  Strips never wrap, so the stored row ra-1 is a plane row.
+        // the rank below.  Strips never wrap, so the stored row ra-1 is a plane row.  The row
+        // tests are warp-uniform and almost never true: one uniform branch keeps the stores out
+        // of the march's instruction stream.
         const int rs = ra - 1;
-        if (rs >= NSDG_GHOST + A.nyl - 2) {
-            const int q = (rs - A.nyl) * A.nx + gi;
-#pragma unroll
-            for (int c = 0; c < 3; ++c) {
-                A.up[0][c * A.plane_up + q] = X.s11[c];
-                A.up[1][c * A.plane_up + q] = X.s12[c];
-                A.up[2][c * A.plane_up + q] = X.s22[c];
-            }
-            A.up[3][q] = u2;
-            A.up[4][q] = v2;
-        }
-        if (rs < NSDG_GHOST + 2) {
-            const int q = (rs + A.nyl_dn) * A.nx + gi;
-            if (rs == NSDG_GHOST) {
-#pragma unroll
-                for (int c = 0; c < 3; ++c) {
-                    A.dn[0][c * A.plane_dn + q] = X.s11[c];
-                    A.dn[1][c * A.plane_dn + q] = X.s12[c];
-                    A.dn[2][c * A.plane_dn + q] = X.s22[c];
-                }
-            }
-            A.dn[3][q] = u2;
-            A.dn[4][q] = v2;
-        }
+        const bool up = rs >= NSDG_GHOST + A.nyl - 2, dn = rs < NSDG_GHOST + 2;
+        if (up || dn)
+            peer_store(A, rs, gi, own, up, dn, X.s11, X.s12, X.s22, u2, v2);
     }
 #pragma unroll
     for (int c = 0; c < 7; ++c)
         d2p[c] = hi[c];
 }
 
-template <bool PEER>
+template <bool PEER, bool CG>
 __global__ void __launch_bounds__(MARCH_WPB * 32, 2) mevp_march_kernel(const __grid_constant__ MevpArgs A)
 {
     const int lane = threadIdx.x & 31;
@@ -882,15 +893,15 @@ __global__ void __launch_bounds__(MARCH_WPB * 32, 2) mevp_march_kernel(const __g
     double d2p[7] = { 0., 0., 0., 0., 0., 0., 0. };
     {
         const int g0 = plane_row(A, b0 - 2);
-        X.un = ldm<PEER>(A.u + g0 * A.nx + gi);
-        X.vn = ldm<PEER>(A.v + g0 * A.nx + gi);
-        X.unr = from_right(X.un, ldm<PEER>(A.u + g0 * A.nx + gip), lane);
-        X.vnr = from_right(X.vn, ldm<PEER>(A.v + g0 * A.nx + gip), lane);
+        X.un = ldm<CG>(A.u + g0 * A.nx + gi);
+        X.vn = ldm<CG>(A.v + g0 * A.nx + gi);
+        X.unr = from_right(X.un, ldm<CG>(A.u + g0 * A.nx + gip), lane);
+        X.vnr = from_right(X.vn, ldm<CG>(A.v + g0 * A.nx + gip), lane);
     }
-    march_load<PEER>(A, b0 - 2, gi, gip, lane, Y);
+    march_load<CG>(A, b0 - 2, gi, gip, lane, Y);
     // step s works on row ra = b0 - 2 + s and stores the owned row ra - 1 when 3 <= s; the first
     // steps run phases C / D on the zero-initialised records (finite values, never stored)
-#define NSDG_STEP(s, X, Y, Z) march_step<PEER>(A, b0 - 2 + (s), gi, gip, lane, own_col && (s) >= 3, X, Y, Z, d2p)
+#define NSDG_STEP(s, X, Y, Z) march_step<PEER, CG>(A, b0 - 2 + (s), gi, gip, lane, own_col && (s) >= 3, X, Y, Z, d2p)
     int s = 0;
 #pragma unroll 1
     for (; s + 2 < nsteps; s += 3) {
@@ -1169,6 +1180,29 @@ int nsdg_mevp_pair_tile_rows(nsdg_ctx* ctx)
     return ry ? ry : ty[ctx->dyn->tune.pair_tile];
 }
 
+namespace {
+// one warp: returns when every flag of this rank (both directions) has reached `need`, i.e. all
+// rows the ring neighbours store into this rank's ghost rows for pair `need` have landed
+__global__ void halo_drain_kernel(const unsigned* flags, int n, unsigned need)
+{
+    const int lane = threadIdx.x;
+    for (int base = 0; base < n; base += 32) {
+        const int q = min(base + lane, n - 1);
+        while (!__all_sync(0xffffffffu, (int)(ld_acquire_sys(flags + q) - need) >= 0))
+            __nanosleep(128);
+    }
+}
+} // namespace
+
+// After the last peer pair of a sub-cycle: whatever follows on the stream (a fused sub-iteration of
+// an odd count, a download, the release of the slab) must not overtake the neighbours' stores.
+int nsdg_mevp_peer_drain(nsdg_ctx* ctx)
+{
+    DynState* d = ctx->dyn;
+    NSDG_KERNEL(ctx, NSDG_K_OTHER, (halo_drain_kernel<<<1, 32, 0, ctx->stream>>>(d->flags, 2 * d->nflagw, d->halo_seq)));
+    return NSDG_OK;
+}
+
 bool nsdg_mevp_peer_halo(nsdg_ctx* ctx) { return ctx->dyn && peer_possible(ctx->dyn) && march_rows(ctx) > 0; }
 
 int nsdg_mevp_pair(nsdg_ctx* ctx, double dt, const double* u, const double* v, double* unew,
@@ -1214,11 +1248,15 @@ int nsdg_mevp_pair(nsdg_ctx* ctx, double dt, const double* u, const double* v, d
             A.flag_up = d->up.flags;
             A.flag_dn = d->dn.flags;
             A.seq = peer_seq;
-            NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<true><<<grid, block, 0, st>>>(A)));
+            static const bool nc = getenv("NSDG_PEER_LDNC") && atoi(getenv("NSDG_PEER_LDNC")); // experiment
+            if (nc)
+                NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<true, false><<<grid, block, 0, st>>>(A)));
+            else
+                NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<true, true><<<grid, block, 0, st>>>(A)));
         } else if (st == ctx->stream) {
-            NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<false><<<grid, block, 0, st>>>(A)));
+            NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<false, false><<<grid, block, 0, st>>>(A)));
         } else { /* the per-kernel profiler brackets the compute stream only */
-            mevp_march_kernel<false><<<grid, block, 0, st>>>(A);
+            mevp_march_kernel<false, false><<<grid, block, 0, st>>>(A);
             NSDG_LAUNCHED(ctx);
         }
         return NSDG_OK;

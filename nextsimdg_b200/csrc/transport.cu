@@ -38,14 +38,22 @@ template <> struct Gauss<3> {
     static __device__ __forceinline__ double w(int k) { return k == 1 ? 8. / 18. : 5. / 18.; }
 };
 
+// ---- floating-point reproducibility --------------------------------------------------------
+// This translation unit is compiled with -fmad=false (build.py): the compiler never contracts a
+// multiplication and an addition on its own, every fused multiply-add below is written out.
+// Which products get fused is therefore the same in every kernel, in every unrolled copy of a
+// loop body and for every tile / band layout, and a cell's result does not depend on which of
+// them computed it: the marching kernel, the one-thread-per-cell kernel and any decomposition
+// of the grid give the same bits (with automatic contraction the three unrolled copies of the
+// marching step differed in the last bit, profiles/r2g_transport_tile_probe.txt).
 template <int NC> __device__ __forceinline__ double eval(const double (&c)[NC], double xi, double eta)
 {
     double a = xi - 0.5, b = eta - 0.5;
     double s = c[0];
     if (NC >= 3)
-        s += c[1] * a + c[2] * b;
+        s = fma(c[2], b, fma(c[1], a, s));
     if (NC >= 6)
-        s += c[3] * (a * a - 1. / 12.) + c[4] * (b * b - 1. / 12.) + c[5] * a * b;
+        s = fma(c[5], a * b, fma(c[4], b * b - 1. / 12., fma(c[3], a * a - 1. / 12., s)));
     return s;
 }
 
@@ -55,13 +63,13 @@ template <int NC> __device__ __forceinline__ void add_psi(double (&r)[NC], doubl
     double a = xi - 0.5, b = eta - 0.5;
     r[0] += F;
     if (NC >= 3) {
-        r[1] += F * a;
-        r[2] += F * b;
+        r[1] = fma(F, a, r[1]);
+        r[2] = fma(F, b, r[2]);
     }
     if (NC >= 6) {
-        r[3] += F * (a * a - 1. / 12.);
-        r[4] += F * (b * b - 1. / 12.);
-        r[5] += F * a * b;
+        r[3] = fma(F, a * a - 1. / 12., r[3]);
+        r[4] = fma(F, b * b - 1. / 12., r[4]);
+        r[5] = fma(F, a * b, r[5]);
     }
 }
 
@@ -88,18 +96,18 @@ struct Traces { // a cell's own traces on its four edges
 };
 __device__ __forceinline__ void dg2_traces(const double (&c)[6], Traces& T)
 {
-    const double m0 = c[0] + c[3] * (1. / 6.), n0 = c[0] + c[4] * (1. / 6.);
-    T.l[0] = m0 - 0.5 * c[1];
-    T.l[1] = c[2] - 0.5 * c[5];
+    const double m0 = fma(c[3], 1. / 6., c[0]), n0 = fma(c[4], 1. / 6., c[0]);
+    T.l[0] = fma(-0.5, c[1], m0);
+    T.l[1] = fma(-0.5, c[5], c[2]);
     T.l[2] = c[4];
-    T.r[0] = m0 + 0.5 * c[1];
-    T.r[1] = c[2] + 0.5 * c[5];
+    T.r[0] = fma(0.5, c[1], m0);
+    T.r[1] = fma(0.5, c[5], c[2]);
     T.r[2] = c[4];
-    T.b[0] = n0 - 0.5 * c[2];
-    T.b[1] = c[1] - 0.5 * c[5];
+    T.b[0] = fma(-0.5, c[2], n0);
+    T.b[1] = fma(-0.5, c[5], c[1]);
     T.b[2] = c[3];
-    T.t[0] = n0 + 0.5 * c[2];
-    T.t[1] = c[1] + 0.5 * c[5];
+    T.t[0] = fma(0.5, c[2], n0);
+    T.t[1] = fma(0.5, c[5], c[1]);
     T.t[2] = c[3];
 }
 // flux moments of one edge: M0 = sum F, M1 = sum F t, M2 = sum F (t^2 - 1/12); `minus` is the
@@ -108,15 +116,15 @@ __device__ __forceinline__ void dg2_edge(const double (&vn)[3], const double (&m
     double& M0, double& M1, double& M2)
 {
     constexpr double g = 0.3872983346207417;
-    const double em = minus[0] + minus[2] * (1. / 15.), om = minus[1] * g;
-    const double ep = plus[0] + plus[2] * (1. / 15.), op = plus[1] * g;
+    const double em = fma(minus[2], 1. / 15., minus[0]), om = minus[1] * g;
+    const double ep = fma(plus[2], 1. / 15., plus[0]), op = plus[1] * g;
     const double F0 = vn[0] * (vn[0] > 0. ? em - om : ep - op);
-    const double F1 = vn[1] * (vn[1] > 0. ? minus[0] - minus[2] * (1. / 12.) : plus[0] - plus[2] * (1. / 12.));
+    const double F1 = vn[1] * (vn[1] > 0. ? fma(minus[2], -1. / 12., minus[0]) : fma(plus[2], -1. / 12., plus[0]));
     const double F2 = vn[2] * (vn[2] > 0. ? em + om : ep + op);
     const double s02 = F0 + F2;
     M0 = s02 + F1;
     M1 = g * (F2 - F0);
-    M2 = s02 * (1. / 15.) - F1 * (1. / 12.);
+    M2 = fma(F1, -1. / 12., s02 * (1. / 15.));
 }
 // rr = int_K phi (v . grad psi) - sum_e int_e (v.n) phi^ psi for one cell from
 // lm / rm / bm / tm: the flux moments (M0, M1, M2 of dg2_edge) of the left, right, bottom and top
@@ -132,23 +140,31 @@ __device__ __forceinline__ void dg2_cell_m(const double (&c)[6], const EdgeVel& 
         // fx[b][a] = w_a w_b phi u/hx, fy[b][a] = w_a w_b phi v/hy (uL.. carry w_b/hx, vB.. w_a/hy)
         double sx0 = 0., sx2 = 0., sxa = 0.; // sum_a fx of row b = 0, 2; sum over all of fx a/g
         double sy_a0 = 0., sy_a2 = 0., syb = 0.; // sum_b fy of column a = 0, 2; sum of fy b/g
+        double dv[3];
+#pragma unroll
+        for (int a = 0; a < 3; ++a)
+            dv[a] = V.vT[a] - V.vB[a];
 #pragma unroll
         for (int b = 0; b < 3; ++b) {
             const double bb = XI[b] - 0.5;
-            const double p0 = (b == 1) ? c[0] - c[4] * (1. / 12.) : c[0] + c[2] * bb + c[4] * (1. / 15.);
-            const double p1 = (b == 1) ? c[1] : c[1] + c[5] * bb;
-            const double e = p0 + c[3] * (1. / 15.), o = p1 * g;
-            const double ph[3] = { e - o, p0 - c[3] * (1. / 12.), e + o };
+            const double p0 = (b == 1) ? fma(c[4], -1. / 12., c[0]) : fma(c[4], 1. / 15., fma(c[2], bb, c[0]));
+            const double p1 = (b == 1) ? c[1] : fma(c[5], bb, c[1]);
+            const double e = fma(c[3], 1. / 15., p0), o = p1 * g;
+            const double ph[3] = { e - o, fma(c[3], -1. / 12., p0), e + o };
             const double du = V.uR[b] - V.uL[b];
-            double fxr[3], fyr[3];
+            double fxr[3], fyr[3], uu[3], vv[3];
 #pragma unroll
             for (int a = 0; a < 3; ++a) {
-                const double uu = V.uL[b] + du * XI[a]; // w_b u / hx
-                const double vv = V.vB[a] + (V.vT[a] - V.vB[a]) * XI[b]; // w_a v / hy
-                fxr[a] = (ph[a] * WQ[a]) * uu;
-                fyr[a] = (ph[a] * WQ[b]) * vv;
+                uu[a] = fma(du, XI[a], V.uL[b]); // w_b u / hx
+                vv[a] = fma(dv[a], XI[b], V.vB[a]); // w_a v / hy
             }
-            const double sx = fxr[0] + fxr[1] + fxr[2], sy = fyr[0] + fyr[1] + fyr[2];
+            fxr[0] = (ph[0] * WQ[0]) * uu[0];
+            fxr[2] = (ph[2] * WQ[2]) * uu[2];
+            fyr[0] = (ph[0] * WQ[b]) * vv[0];
+            fyr[2] = (ph[2] * WQ[b]) * vv[2];
+            // the middle products are only ever summed: fused into the row sums
+            const double sx = fma(ph[1] * WQ[1], uu[1], fxr[0] + fxr[2]);
+            const double sy = fma(ph[1] * WQ[b], vv[1], fyr[0] + fyr[2]);
             r1 += sx;
             r2 += sy;
             sxa += fxr[2] - fxr[0];
@@ -176,21 +192,21 @@ __device__ __forceinline__ void dg2_cell_m(const double (&c)[6], const EdgeVel& 
     {
         const double d0 = lm[0] - rm[0], s0 = lm[0] + rm[0], d1 = lm[1] - rm[1], s1 = lm[1] + rm[1];
         r0 += d0;
-        r1 -= 0.5 * s0;
+        r1 = fma(-0.5, s0, r1);
         r2 += d1;
-        r3 += d0 * (1. / 6.);
+        r3 = fma(d0, 1. / 6., r3);
         r4 += lm[2] - rm[2];
-        r5 -= 0.5 * s1;
+        r5 = fma(-0.5, s1, r5);
     }
     // psi on eta = 0 / 1: (1, t, -+1/2, t^2 - 1/12, 1/6, -+t/2)
     {
         const double d0 = bm[0] - tm[0], s0 = bm[0] + tm[0], d1 = bm[1] - tm[1], s1 = bm[1] + tm[1];
         r0 += d0;
         r1 += d1;
-        r2 -= 0.5 * s0;
+        r2 = fma(-0.5, s0, r2);
         r3 += bm[2] - tm[2];
-        r4 += d0 * (1. / 6.);
-        r5 -= 0.5 * s1;
+        r4 = fma(d0, 1. / 6., r4);
+        r5 = fma(-0.5, s1, r5);
     }
     rr[0] = r0;
     rr[1] = r1;
@@ -199,8 +215,7 @@ __device__ __forceinline__ void dg2_cell_m(const double (&c)[6], const EdgeVel& 
     rr[4] = r4;
     rr[5] = r5;
 }
-// rr = int_K phi (v . grad psi) - sum_e int_e (v.n) phi^ psi for one cell; nbL / nbR / nbB / nbT
-// are the NEIGHBOURS' traces on the shared edges (the left neighbour's xi = 1 trace, ...)
+// the same from the NEIGHBOURS' traces on the shared edges (the left neighbour's xi = 1 trace, ...)
 __device__ __forceinline__ void dg2_cell(const double (&c)[6], const EdgeVel& V, const Traces& T,
     const double (&nbL)[3], const double (&nbR)[3], const double (&nbB)[3], const double (&nbT)[3], double (&rr)[6])
 {
@@ -211,18 +226,19 @@ __device__ __forceinline__ void dg2_cell(const double (&c)[6], const EdgeVel& V,
     dg2_edge(V.vT, T.t, nbT, tm[0], tm[1], tm[2]);
     dg2_cell_m(c, V, lm, rm, bm, tm, rr);
 }
-__device__ __forceinline__ void edge_velocities(double u00, double u10, double u01, double u11, double v00,
-    double v10, double v01, double v11, double ihx, double ihy, EdgeVel& V)
+// Normal velocity of the bilinear field at an edge Gauss point, times weight / cell size:
+// (a (1 - s) + b s) w / h = a k0 + b k1 with k0 = (1 - s) w / h, k1 = s w / h taken on the host
+// (StageArgs::ku0 ...: FP64 instructions read them straight from the constant bank).
+__device__ __forceinline__ double edge_lerp(double a, double b, double k0, double k1)
 {
-    using G = Gauss<3>;
-#pragma unroll
-    for (int g = 0; g < 3; ++g) {
-        const double s = G::x(g), w = G::w(g);
-        V.uL[g] = (u00 * (1 - s) + u01 * s) * ihx * w;
-        V.uR[g] = (u10 * (1 - s) + u11 * s) * ihx * w;
-        V.vB[g] = (v00 * (1 - s) + v10 * s) * ihy * w;
-        V.vT[g] = (v01 * (1 - s) + v11 * s) * ihy * w;
-    }
+    return fma(b, k1, a * k0);
+}
+// dst = a*base + b*(c + dt*IM*rr); dtim = dt * IM taken on the host
+template <bool HAS_BASE>
+__device__ __forceinline__ double stage_value(double c, double rr, double dtim, double a, double b, double base)
+{
+    const double val = fma(dtim, rr, c);
+    return HAS_BASE ? fma(a, base, b * val) : val;
 }
 
 struct StageArgs {
@@ -232,10 +248,24 @@ struct StageArgs {
     const double* u;
     const double* v;
     double a, b, dt, ihx, ihy;
+    double ku0[3], ku1[3], kv0[3], kv1[3]; // edge_lerp constants per Gauss point (x- / y-normal edges)
+    double dtim[6]; // dt times the inverse mass of each mode
     int nx, nyl, plane, r0, r1;
     int wrap, prefetch;
     int band; // rows per band of the marching kernel
 };
+
+__device__ __forceinline__ void edge_velocities(const StageArgs& A, double u00, double u10, double u01, double u11,
+    double v00, double v10, double v01, double v11, EdgeVel& V)
+{
+#pragma unroll
+    for (int g = 0; g < 3; ++g) {
+        V.uL[g] = edge_lerp(u00, u01, A.ku0[g], A.ku1[g]);
+        V.uR[g] = edge_lerp(u10, u11, A.ku0[g], A.ku1[g]);
+        V.vB[g] = edge_lerp(v00, v10, A.kv0[g], A.kv1[g]);
+        V.vT[g] = edge_lerp(v01, v11, A.kv0[g], A.kv1[g]);
+    }
+}
 
 __device__ __forceinline__ void prefetch_line(const double* p)
 {
@@ -292,11 +322,10 @@ __global__ void __launch_bounds__(256, MINB) transport_stage_kernel(const __grid
     double uL[NQ], uR[NQ], vB[NQ], vT[NQ];
 #pragma unroll
     for (int g = 0; g < NQ; ++g) {
-        const double s = G::x(g), w = G::w(g);
-        uL[g] = (u00 * (1 - s) + u01 * s) * A.ihx * w;
-        uR[g] = (u10 * (1 - s) + u11 * s) * A.ihx * w;
-        vB[g] = (v00 * (1 - s) + v10 * s) * A.ihy * w;
-        vT[g] = (v01 * (1 - s) + v11 * s) * A.ihy * w;
+        uL[g] = edge_lerp(u00, u01, A.ku0[g], A.ku1[g]);
+        uR[g] = edge_lerp(u10, u11, A.ku0[g], A.ku1[g]);
+        vB[g] = edge_lerp(v00, v10, A.kv0[g], A.kv1[g]);
+        vT[g] = edge_lerp(v01, v11, A.kv0[g], A.kv1[g]);
     }
 
     if constexpr (NC == 6) {
@@ -336,14 +365,10 @@ __global__ void __launch_bounds__(256, MINB) transport_stage_kernel(const __grid
         for (int q = 0; q < 3; ++q)
             nbT[q] = N.b[q];
         dg2_cell(c, V, T, nbL, nbR, nbB, nbT, rr);
-        constexpr double IM[6] = { 1., 12., 12., 180., 180., 144. };
 #pragma unroll
-        for (int q = 0; q < NC; ++q) {
-            double val = c[q] + A.dt * IM[q] * rr[q];
-            if (HAS_BASE)
-                val = A.a * __ldg(A.base[f] + q * A.plane + k) + A.b * val;
-            A.dst[f][q * A.plane + k] = val;
-        }
+        for (int q = 0; q < NC; ++q)
+            A.dst[f][q * A.plane + k] = stage_value<HAS_BASE>(c[q], rr[q], A.dtim[q], A.a, A.b,
+                HAS_BASE ? __ldg(A.base[f] + q * A.plane + k) : 0.);
     } else {
         double c[NC], cn[NC], rr[NC];
         load_cell<NC>(c, A.src[f], A.plane, k);
@@ -357,16 +382,16 @@ __global__ void __launch_bounds__(256, MINB) transport_stage_kernel(const __grid
 #pragma unroll
                 for (int gb = 0; gb < NQ; ++gb) {
                     const double xi = G::x(ga), eta = G::x(gb), w = G::w(ga) * G::w(gb);
-                    const double uu = (u00 * (1 - xi) + u10 * xi) * (1 - eta) + (u01 * (1 - xi) + u11 * xi) * eta;
-                    const double vv = (v00 * (1 - xi) + v10 * xi) * (1 - eta) + (v01 * (1 - xi) + v11 * xi) * eta;
+                    const double uu = fma(fma(u11, xi, u01 * (1 - xi)), eta, fma(u10, xi, u00 * (1 - xi)) * (1 - eta));
+                    const double vv = fma(fma(v11, xi, v01 * (1 - xi)), eta, fma(v10, xi, v00 * (1 - xi)) * (1 - eta));
                     const double p = w * eval<NC>(c, xi, eta);
-                    const double fx = p * uu * A.ihx, fy = p * vv * A.ihy;
+                    const double fx = (p * uu) * A.ihx, fy = (p * vv) * A.ihy;
                     rr[1] += fx;
                     rr[2] += fy;
                     if (NC >= 6) {
-                        rr[3] += fx * 2. * (xi - 0.5);
-                        rr[4] += fy * 2. * (eta - 0.5);
-                        rr[5] += fx * (eta - 0.5) + fy * (xi - 0.5);
+                        rr[3] = fma(fx, 2. * (xi - 0.5), rr[3]);
+                        rr[4] = fma(fy, 2. * (eta - 0.5), rr[4]);
+                        rr[5] = fma(fy, xi - 0.5, fma(fx, eta - 0.5, rr[5]));
                     }
                 }
         }
@@ -402,14 +427,10 @@ __global__ void __launch_bounds__(256, MINB) transport_stage_kernel(const __grid
             double F = vT[g] * (vT[g] > 0. ? eval<NC>(c, s, 1.) : eval<NC>(cn, s, 0.));
             add_psi<NC>(rr, -F, s, 1.);
         }
-        constexpr double IM[6] = { 1., 12., 12., 180., 180., 144. };
 #pragma unroll
-        for (int q = 0; q < NC; ++q) {
-            double val = c[q] + A.dt * IM[q] * rr[q];
-            if (HAS_BASE)
-                val = A.a * __ldg(A.base[f] + q * A.plane + k) + A.b * val;
-            A.dst[f][q * A.plane + k] = val;
-        }
+        for (int q = 0; q < NC; ++q)
+            A.dst[f][q * A.plane + k] = stage_value<HAS_BASE>(c[q], rr[q], A.dtim[q], A.a, A.b,
+                HAS_BASE ? __ldg(A.base[f] + q * A.plane + k) : 0.);
     }
 }
 
@@ -518,7 +539,7 @@ __device__ __forceinline__ void tm_step(const StageArgs& A, int f, int r, int gi
     {
         const double u10 = __shfl_down_sync(0xffffffffu, X.u, 1), u11 = __shfl_down_sync(0xffffffffu, Y.u, 1);
         const double v10 = __shfl_down_sync(0xffffffffu, X.v, 1), v11 = __shfl_down_sync(0xffffffffu, Y.v, 1);
-        edge_velocities(X.u, u10, Y.u, u11, X.v, v10, Y.v, v11, A.ihx, A.ihy, V);
+        edge_velocities(A, X.u, u10, Y.u, u11, X.v, v10, Y.v, v11, V);
 #pragma unroll
         for (int q = 0; q < 3; ++q)
             V.vB[q] = vb[q]; // == the previous row's vT (same nodes, same expression)
@@ -536,15 +557,10 @@ __device__ __forceinline__ void tm_step(const StageArgs& A, int f, int r, int gi
         rm[q] = __shfl_down_sync(0xffffffffu, lm[q], 1); // right edge = the right neighbour's left edge
     dg2_edge(V.vT, T.t, TY.b, tm[0], tm[1], tm[2]);
     dg2_cell_m(X.c, V, lm, rm, bm, tm, rr);
-    constexpr double IM[6] = { 1., 12., 12., 180., 180., 144. };
     if (own) {
 #pragma unroll
-        for (int q = 0; q < 6; ++q) {
-            double val = X.c[q] + A.dt * IM[q] * rr[q];
-            if (HAS_BASE)
-                val = A.a * X.base[q] + A.b * val;
-            A.dst[f][q * A.plane + X.k] = val;
-        }
+        for (int q = 0; q < 6; ++q)
+            A.dst[f][q * A.plane + X.k] = stage_value<HAS_BASE>(X.c[q], rr[q], A.dtim[q], A.a, A.b, HAS_BASE ? X.base[q] : 0.);
     }
 #pragma unroll
     for (int q = 0; q < 3; ++q) {
@@ -575,19 +591,19 @@ __global__ void __launch_bounds__(TM_WPB * 32, 3) transport_march_kernel(const _
     tm_load_src(A, f, b0 - 1, gi, X);
     tm_load_src(A, f, b0, gi, Y);
     X.base[0] = X.base[1] = X.base[2] = X.base[3] = X.base[4] = X.base[5] = 0.;
+    // (the not-stored first step is the loop's first iteration with a run-time predicate, not a
+    // separately specialised copy of the step)
     int r = b0 - 1;
-    tm_step<HAS_BASE>(A, f, r, gi, false, X, Y, Z, bm, vb);
-    ++r;
 #pragma unroll 1
     for (; r + 2 < b1; r += 3) {
-        tm_step<HAS_BASE>(A, f, r, gi, own, Y, Z, X, bm, vb);
-        tm_step<HAS_BASE>(A, f, r + 1, gi, own, Z, X, Y, bm, vb);
-        tm_step<HAS_BASE>(A, f, r + 2, gi, own, X, Y, Z, bm, vb);
+        tm_step<HAS_BASE>(A, f, r, gi, own && r >= b0, X, Y, Z, bm, vb);
+        tm_step<HAS_BASE>(A, f, r + 1, gi, own, Y, Z, X, bm, vb);
+        tm_step<HAS_BASE>(A, f, r + 2, gi, own, Z, X, Y, bm, vb);
     }
     if (r < b1) {
-        tm_step<HAS_BASE>(A, f, r, gi, own, Y, Z, X, bm, vb);
+        tm_step<HAS_BASE>(A, f, r, gi, own && r >= b0, X, Y, Z, bm, vb);
         if (r + 1 < b1)
-            tm_step<HAS_BASE>(A, f, r + 1, gi, own, Z, X, Y, bm, vb);
+            tm_step<HAS_BASE>(A, f, r + 1, gi, own, Y, Z, X, bm, vb);
     }
 }
 
@@ -650,6 +666,22 @@ int nsdg_transport_stage(nsdg_ctx* ctx, int nfields, double* const* src, double*
     A.r0 = (int)r0;
     A.r1 = (int)r1;
     A.wrap = d->wrap ? 1 : 0;
+    {
+        const int nq = d->nc == 1 ? 1 : (d->nc == 3 ? 2 : 3);
+        const double g2 = 0.28867513459481287, g3 = 0.3872983346207417;
+        const double xs[3][3] = { { 0.5, 0., 0. }, { 0.5 - g2, 0.5 + g2, 0. }, { 0.5 - g3, 0.5, 0.5 + g3 } };
+        const double ws[3][3] = { { 1., 0., 0. }, { 0.5, 0.5, 0. }, { 5. / 18., 8. / 18., 5. / 18. } };
+        for (int g = 0; g < 3; ++g) {
+            const double sx = xs[nq - 1][g], w = ws[nq - 1][g];
+            A.ku0[g] = (1. - sx) * w * A.ihx;
+            A.ku1[g] = sx * w * A.ihx;
+            A.kv0[g] = (1. - sx) * w * A.ihy;
+            A.kv1[g] = sx * w * A.ihy;
+        }
+        const double im[6] = { 1., 12., 12., 180., 180., 144. };
+        for (int q = 0; q < 6; ++q)
+            A.dtim[q] = dt * im[q];
+    }
     static int pf = -1; // NSDG_TRANSPORT_PREFETCH=0/1 (tuning)
     if (pf < 0) {
         const char* e = getenv("NSDG_TRANSPORT_PREFETCH");

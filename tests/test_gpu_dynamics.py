@@ -374,8 +374,9 @@ def test_full_size_4096sq_is_the_tiled_small_problem(ctx):
     mp = MevpParams.defaults()
     mp.bc = BC_PERIODIC
     names = ("H", "A", "U", "V", "S11", "S12", "S22")
-    # the same stage kernel on both grids (the default picks the marching kernel from 2^20 cells)
-    small = GpuDynamics(ctx, m, m, hx, hy, 6, mevp=mp, tuning={"transport_march": 1})
+    # (the default transport stage kernel differs between the two sizes: one thread per cell below
+    # 2^20 cells, marching above; they are bit-identical as well)
+    small = GpuDynamics(ctx, m, m, hx, hy, 6, mevp=mp)
     small.upload_all(F)
     small.step(120.0, nsub)
     got_small = {k: small.download(k) for k in names}
@@ -383,7 +384,7 @@ def test_full_size_4096sq_is_the_tiled_small_problem(ctx):
                      120.0, nsub)
     for k, a in zip(names, ref):
         assert maxrel(got_small[k], a) < RTOL, k
-    big = GpuDynamics(ctx, n, n, hx, hy, 6, mevp=mp, tuning={"transport_march": 1})
+    big = GpuDynamics(ctx, n, n, hx, hy, 6, mevp=mp)
     big.upload_all({k: np.tile(v, (1, reps, reps) if v.ndim == 3 else (reps, reps)) for k, v in F.items()})
     big.step(120.0, nsub)
     for k in names:
@@ -421,12 +422,10 @@ def test_pair_kernel_variants_bit_identical(ctx):
     variants = {"auto": {}, "march64": {"march_rows": 64}, "march16": {"march_rows": 16},
                 "march5": {"march_rows": 5}, "tiled": {"march_rows": -1},
                 "tiled32x8": {"march_rows": -1, "pair_tile": "32x8"}, "single": {"pair": -1},
-                "graph": {"graph": 1}, "nograph": {"graph": -1}}
-    # the transport kernel is pinned: the marching and the one-thread-per-cell stage kernels share
-    # their arithmetic but not the compiler's FMA contraction choices (last-bit differences, below)
-    digests = {k: dyn_digest.digest(ctx, dict(v, transport_march=-1)) for k, v in variants.items()}
-    assert len(set(digests.values())) == 1, digests
-    digests = {k: dyn_digest.digest(ctx, dict(variants[k], transport_march=1)) for k in ("auto", "march16", "tiled", "graph")}
+                "graph": {"graph": 1}, "nograph": {"graph": -1},
+                "transport-march": {"transport_march": 1}, "transport-tiled": {"transport_march": -1},
+                "transport-march-rows16": {"transport_march": 1, "march_rows": 16}}
+    digests = {k: dyn_digest.digest(ctx, v) for k, v in variants.items()}
     assert len(set(digests.values())) == 1, digests
 
 
@@ -434,10 +433,10 @@ def test_pair_kernel_variants_bit_identical(ctx):
                                       ((1024, 1024), BC_BOX), ((29, 70), BC_BOX)])
 def test_transport_marching_kernel_against_tiled_kernel_and_oracle(ctx, shape, bc):
     """The marching dG2 stage kernel (every edge flux computed once, neighbours by shuffle and
-    from registers) against the one-thread-per-cell kernel: same integrals, agreement to the last
-    bits (1e-14 of the field's max norm after three SSP-RK3 steps; the difference is the
-    compiler's FMA contraction), and both within 1e-11 of the oracle.  Ragged sizes, a grid
-    narrower than a warp's 28 columns, fewer rows than the pipeline depth."""
+    from registers) against the one-thread-per-cell kernel: same integrals with every fused
+    multiply-add written out (transport.cu is compiled without automatic contraction), so the
+    two agree BIT FOR BIT after three SSP-RK3 steps, and both are within 1e-11 of the oracle.
+    Ragged sizes, a grid narrower than a warp's 28 columns, fewer rows than the pipeline depth."""
     nx, ny = shape
     F, hx, hy = S.box_case(nx, ny, 6)
     r = np.random.default_rng(9)
@@ -459,7 +458,7 @@ def test_transport_marching_kernel_against_tiled_kernel_and_oracle(ctx, shape, b
         out[name] = {k: dyn.download(k) for k in ("H", "A")}
         dyn.close()
     for k in ("H", "A"):
-        assert maxrel(out["march"][k], out["tiled"][k]) < 1e-14, k
+        assert np.array_equal(out["march"][k], out["tiled"][k]), k
         if nx * ny <= 300 * 211:
             ref = F[k]
             for _ in range(3):
