@@ -208,20 +208,24 @@ class GpuStep(_State):
     def writeRestartFile(self, path, nx=None):
         """SoA restart (nextsimdg_b200/restart.py; the reference's structure/data layout of
         core/src/DevGridIO.cpp:160-201) straight from the device mirror, plus the hidden newice
-        state.  nx: edge of the square DevGrid (default: sqrt(ncells), else a 1 x n grid)."""
+        state: netCDF-4 / HDF5 (restart.write_netcdf) unless the name ends in .nsdgr (NSDGR1
+        container).  nx: edge of the square DevGrid (default: sqrt(ncells), else a 1 x n grid)."""
         from . import restart
         d = self.get_prognostic()
         d["newice"] = self.get_newice()
         if nx is None:
             r = int(round(self.n ** 0.5))
             nx = r if r * r == self.n else 1
-        restart.write_restart(path, d, nx, self.n // nx, self.nlayers)
+        writer = restart.write_restart if str(path).endswith(".nsdgr") else restart.write_netcdf
+        writer(path, d, nx, self.n // nx, self.nlayers)
 
     @classmethod
     def from_restart(cls, ctx, path, forcing, params=None):
         """Model::configure's restart read (core/src/Model.cpp:62-73) without ElementData."""
         from . import restart
-        st, meta = restart.read_restart(path)
+        with open(path, "rb") as f:
+            is_container = f.read(len(restart.MAGIC)) == restart.MAGIC
+        st, meta = restart.read_restart(path) if is_container else restart.read_netcdf(path)
         step = cls(ctx, meta["nx"] * meta["ny"], meta["nlayers"], params)
         step.setInitialData(st, forcing)
         if "newice" in st:

@@ -5,8 +5,10 @@ The reference reads/writes netCDF-4 through netCDF-cxx4 (core/src/DevGridIO.cpp:
 :160-201 write): group `structure` (attribute `type` = "devgrid"), group `data` with variables
 hice, cice, hsnow, sst, sss [x][y] and tice [x][y][nLayers]; DevGrid stores cell (i, j) at
 `i*nx + j`, x outer (DevGridIO.cpp:107-109), tice layer-fastest (:193-199).  Neither netCDF nor
-HDF5 exists in this image or on the GPU box, so the same content travels in a minimal
-self-describing container instead (same names, same dimension order, same element order):
+HDF5 exists in this image or on the GPU box.  `write_netcdf` writes that layout as an HDF5 file
+through this package's own minimal writer (`hdf5write`), `read_netcdf` reads it (and the
+reference's own files) through `hdf5lite`.  A second, trivially simple self-describing container
+carries the same content (same names, same dimension order, same element order):
 
     b"NSDGR1\\n" | uint64 little-endian header length | JSON header | raw little-endian float64
 
@@ -54,6 +56,38 @@ def write_restart(path, state, nx, ny=None, nlayers=1, structure=STRUCTURE_TYPE)
         f.write(header)
         for b in blobs:
             f.write(b)
+
+
+def write_netcdf(path, state, nx, ny=None, nlayers=1, structure=STRUCTURE_TYPE):
+    """The reference's own restart layout (core/src/DevGridIO.cpp:149-201; run/dev_res.py:1-21)
+    as a netCDF-4 / HDF5 file written by `hdf5write` (no netCDF or HDF5 library exists here):
+    group `structure` with attribute `type`, group `data` with dimensions x, y, nLayers and
+    float64 variables hice, cice, hsnow, sst, sss [x][y], tice [x][y][nLayers], in the order
+    dumpData creates them.  A `newice` entry (hidden state of the physics, not a reference
+    variable) is written as one more [x][y] variable; the reference's reader ignores it.
+    Readable by `read_netcdf` / `hdf5lite`; NOT checked against netCDF-C (none available)."""
+    from . import hdf5write
+    ny = nx if ny is None else ny
+    n = nx * ny
+    missing = [k for k in PROGNOSTIC if k not in state]
+    if missing:
+        raise ValueError(f"restart state lacks {missing}")
+    # DevGridIO.cpp:161-173: the five 2-D fields in the order of its name -> accessor map, then tice
+    order = [k for k in ("cice", "hice", "hsnow", "sss", "sst") ] + ["tice"] + \
+            [k for k in state if k not in PROGNOSTIC]
+    variables = []
+    for name in order:
+        a = np.ascontiguousarray(state[name], dtype=np.float64).ravel()
+        want = n * nlayers if name == "tice" else n
+        if a.size != want:
+            raise ValueError(f"{name}: expected {want} values, got {a.size}")
+        if name == "tice":
+            variables.append((name, ("x", "y", "nLayers"), a.reshape(nx, ny, nlayers)))
+        else:
+            variables.append((name, ("x", "y"), a.reshape(nx, ny)))
+    hdf5write.write_netcdf4(path, {
+        "structure": {"attrs": {"type": structure}},
+        "data": {"dims": [("x", nx), ("y", ny), ("nLayers", nlayers)], "vars": variables}})
 
 
 def read_restart(path):
@@ -106,6 +140,8 @@ def read_netcdf(nc_path):
         if missing:
             raise ValueError(f"{nc_path}: group 'data' lacks {missing}")
         arrays = {k: f.read("/data/" + k).astype(np.float64) for k in PROGNOSTIC}
+        if "newice" in f.names("/data"):  # this package's extra variable (write_netcdf)
+            arrays["newice"] = f.read("/data/newice").astype(np.float64)
         structure = f.attrs("/structure").get("type")
     if structure != STRUCTURE_TYPE:
         # core/src/StructureFactory.cpp:41-43 throws std::invalid_argument for an unknown structure
@@ -113,7 +149,7 @@ def read_netcdf(nc_path):
     if arrays["tice"].ndim != 3:
         raise ValueError(f"{nc_path}: tice must be [x][y][nLayers]")
     nx, ny, nl = arrays["tice"].shape
-    for k in PROGNOSTIC[:-1]:
+    for k in [q for q in arrays if q != "tice"]:
         if arrays[k].shape != (nx, ny):
             raise ValueError(f"{nc_path}: {k} has shape {arrays[k].shape}, expected {(nx, ny)}")
     state = {k: np.ascontiguousarray(a).ravel() for k, a in arrays.items()}

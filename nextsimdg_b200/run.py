@@ -29,7 +29,7 @@ from .config import thermo_params_from_ini
 # core/src/include/DummyExternalData.hpp:25-32
 DUMMY_FORCING = dict(tair=-1.0, tdew=-4.0, slp=1e5, qsw=0.0, qlw=311.0, mld=10.0, snowfall=0.0,
                      wind=0.0)
-FINAL_FILE_NAME = "restart.nsdgr"  # Model.cpp:33 "restart.nc" in the HDF5-free container
+FINAL_FILE_NAME = "restart.nc"  # Model.cpp:33; netCDF-4 layout of DevGridIO::dump via hdf5write
 
 
 def _int(text, key):
@@ -104,8 +104,8 @@ def run_config(cfg_path, ctx, out_path=None, base_dir=None):
     final["newice"] = step.get_newice()
     if out_path is None:
         out_path = FINAL_FILE_NAME if base_dir is None else os.path.join(base_dir, FINAL_FILE_NAME)
-    restart.write_restart(out_path, final, meta["nx"], meta["ny"], meta["nlayers"],
-                          structure=meta["structure"])
+    writer = restart.write_restart if out_path.endswith(".nsdgr") else restart.write_netcdf
+    writer(out_path, final, meta["nx"], meta["ny"], meta["nlayers"], structure=meta["structure"])
     return final, plan
 
 

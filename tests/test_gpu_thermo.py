@@ -281,13 +281,15 @@ def test_slab_ocean_closure(ctx):
     assert np.array_equal(on.get_prognostic()["sst"], before)
 
 
-def test_restart_write_resume_is_bit_identical(ctx, tmp_path):
+@pytest.mark.parametrize("name", ["mid.nc", "mid.nsdgr"])
+def test_restart_write_resume_is_bit_identical(ctx, tmp_path, name):
     """Restart written from the SoA device mirror and read back (incl. hidden newice): the
-    resumed run continues exactly like the uninterrupted one."""
+    resumed run continues exactly like the uninterrupted one.  Both formats: the reference's
+    netCDF-4 layout (hdf5write / hdf5lite) and the NSDGR1 container."""
     st, fo = S.thermo_inputs(64 * 64, 5)
     p = params("unesco_ccsm")
     step = run_gpu(ctx, p, st, fo, 600.0, 2)
-    path = str(tmp_path / "mid.nsdgr")
+    path = str(tmp_path / name)
     step.writeRestartFile(path)
     step.iterate(600.0, 2)
     want, want_ni = step.get_prognostic(), step.get_newice()
@@ -317,7 +319,8 @@ def test_dev1_config_end_to_end(ctx, tmp_path):
     for k, v in pins.items():
         assert final[k].shape == (nx * ny * (nl if k == "tice" else 1),)
         assert np.all(np.abs(final[k] - v) <= ATOL + RTOL * abs(v)), (k, final[k][0], v)
-    back, meta = R.read_restart(str(tmp_path / RUN.FINAL_FILE_NAME))
+    assert RUN.FINAL_FILE_NAME == "restart.nc"  # core/src/Model.cpp:33
+    back, meta = R.read_netcdf(str(tmp_path / RUN.FINAL_FILE_NAME))
     assert meta["nx"] == nx and meta["structure"] == "devgrid"
     for k in R.PROGNOSTIC:
         assert np.array_equal(back[k], final[k]), k
