@@ -608,7 +608,7 @@ def measure_parity(args, env):
     import mgpu_worker as W
     from nextsimdg_b200._abi import BC_BOX
     ctx = env.context()
-    variants = [v for v in W.VARIANTS if v[0] in ("peer", "peer-rows16", "nccl-overlap-rows16", "nccl-serial")]
+    variants = [v for v in W.VARIANTS if v[0] in ("peer", "peer-rows16", "peer-rows3", "nccl-overlap-rows16", "nccl-serial")]
     cases = [(48, 49 * env.world, BC_BOX, 0, 6), (300, 33 * env.world + 1, BC_BOX, 0, 8)]
     ok, worst, records = W.run_cases(ctx, env.rank, env.world, cases, variants, log=log)
     ctx.close()

@@ -878,7 +878,9 @@ __global__ void __launch_bounds__(MARCH_WPB * 32, 2) mevp_march_kernel(const __g
     if (PEER && band > 0)
         band = (band == 1) ? (int)gridDim.y - 1 : band - 1;
     const int b0 = A.r0 + band * A.band; // owned node/cell rows [b0, b1)
-    const int b1 = min(b0 + A.band, A.r1);
+    // PEER: the last band takes a one-row remainder along (the host leaves that band out of the
+    // grid), so that both rows the rank above needs are stored by the band that publishes them
+    const int b1 = (PEER && band == (int)gridDim.y - 1) ? A.r1 : min(b0 + A.band, A.r1);
     const int nsteps = b1 - b0 + 3;
     if (PEER) {
         // ghost rows below / above this band: produced by the neighbours' previous pair
@@ -1203,7 +1205,8 @@ int nsdg_mevp_peer_drain(nsdg_ctx* ctx)
     return NSDG_OK;
 }
 
-bool nsdg_mevp_peer_halo(nsdg_ctx* ctx) { return ctx->dyn && peer_possible(ctx->dyn) && march_rows(ctx) > 0; }
+// (bands of at least two rows: the bottom band publishes the two bottom rows)
+bool nsdg_mevp_peer_halo(nsdg_ctx* ctx) { return ctx->dyn && peer_possible(ctx->dyn) && march_rows(ctx) >= 2; }
 
 int nsdg_mevp_pair(nsdg_ctx* ctx, double dt, const double* u, const double* v, double* unew,
     double* vnew, double* const* Sold, double* const* Snew, int64_t r0, int64_t r1, cudaStream_t st,
@@ -1229,6 +1232,10 @@ int nsdg_mevp_pair(nsdg_ctx* ctx, double dt, const double* u, const double* v, d
         A.band = ry;
         dim3 block(MARCH_WPB * 32), grid((unsigned)((nwarps + MARCH_WPB - 1) / MARCH_WPB), (unsigned)((nrows + ry - 1) / ry));
         if (peer_seq) {
+            // the two top rows go to the rank above and are published by the LAST band: a
+            // remainder band of one row is merged into the band below it
+            if (grid.y > 1 && nrows - (int)(grid.y - 1) * ry < 2)
+                grid.y -= 1;
             NSDG_REQUIRE(ctx, peer_possible(d) && r0 == NSDG_GHOST && r1 == NSDG_GHOST + d->nyl && nwarps == d->nflagw,
                 NSDG_ESTATE, "peer halo launch needs the mapped neighbours and the whole strip");
             // the neighbours' copies of the five output arrays sit at the same plane offsets of

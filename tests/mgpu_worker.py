@@ -21,6 +21,7 @@ from nextsimdg_b200.gpu import Context, GpuDynamics  # noqa: E402
 NAMES = ("H", "A", "U", "V", "S11", "S12", "S22")
 VARIANTS = (("peer", {}),
             ("peer-rows16", {"march_rows": 16}),
+            ("peer-rows3", {"march_rows": 3}),  # remainder bands of one row in several cases
             ("nccl-overlap", {"halo_peer": -1}),
             ("nccl-overlap-rows16", {"halo_peer": -1, "march_rows": 16}),
             ("nccl-serial", {"halo_peer": -1, "halo_overlap": -1}),
