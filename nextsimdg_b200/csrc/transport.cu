@@ -682,12 +682,10 @@ int nsdg_transport_stage(nsdg_ctx* ctx, int nfields, double* const* src, double*
         for (int q = 0; q < 6; ++q)
             A.dtim[q] = dt * im[q];
     }
-    static int pf = -1; // NSDG_TRANSPORT_PREFETCH=0/1 (tuning)
-    if (pf < 0) {
-        const char* e = getenv("NSDG_TRANSPORT_PREFETCH");
-        pf = e ? atoi(e) : 1;
-    }
-    A.prefetch = pf;
+    // tiled kernel only: L2 prefetch of the streams a thread uses last.  (For the marching kernel an
+    // L2 prefetch 1-8 rows ahead of the register pipeline was measured SLOWER, 3.04-3.72 ms against
+    // 2.77-2.85 ms per H+A step at 4096^2: profiles/r2m_transport_prefetch.txt.)
+    A.prefetch = 1;
     const bool hb = base != nullptr;
     // dG2 on grids that do not live in L2: the marching kernel (nsdg_dyn_tuning.transport_march:
     // 1 forces it on any grid, -1 selects the one-thread-per-cell kernel)
@@ -708,23 +706,12 @@ int nsdg_transport_stage(nsdg_ctx* ctx, int nfields, double* const* src, double*
     dim3 block(64, 4);
     dim3 grid((unsigned)((d->nx + 63) / 64), (unsigned)((r1 - r0 + 3) / 4), (unsigned)nfields);
     nsdg_prof_begin(ctx, NSDG_K_TRANSPORT);
-    static int minb = 0; // NSDG_TRANSPORT_MINB: resident-CTA target of the dG2 register budget (tuning)
-    if (!minb) {
-        const char* e = getenv("NSDG_TRANSPORT_MINB");
-        minb = e ? atoi(e) : 4;
-    }
     if (d->nc == 1)
         launch_stage<1, 4>(A, hb, grid, block, ctx->stream);
     else if (d->nc == 3)
         launch_stage<3, 4>(A, hb, grid, block, ctx->stream);
-    else if (minb == 1)
-        launch_stage<6, 1>(A, hb, grid, block, ctx->stream);
-    else if (minb == 3)
-        launch_stage<6, 3>(A, hb, grid, block, ctx->stream);
-    else if (minb == 4)
-        launch_stage<6, 4>(A, hb, grid, block, ctx->stream);
     else
-        launch_stage<6, 2>(A, hb, grid, block, ctx->stream);
+        launch_stage<6, 4>(A, hb, grid, block, ctx->stream);
     nsdg_prof_end(ctx);
     NSDG_LAUNCHED(ctx);
     return NSDG_OK;
