@@ -794,15 +794,132 @@ __device__ __forceinline__ void peer_store(const MevpArgs& A, int rs, int gi, bo
     }
 }
 
+// ---- shared-memory ring of the marching kernel (RING variant) --------------------------------
+// The register pipeline keeps one row (21 values per lane) in flight per warp: 8 warps x 5.4 KB per
+// SM, which is what bounds the kernel.  Here the rows ahead are brought into a
+// shared-memory ring by the bulk-copy engine instead: a CTA's four warps own 112 adjacent columns,
+// so ONE cp.async.bulk per array and row moves the CTA's whole row segment (120 doubles: 112 + 2
+// halo columns on either side + the right neighbour of the last lane, padded to 16 bytes), 21
+// copies per row issued by 21 lanes of warp 0 in one instruction, completing on an mbarrier per
+// stage.  RING_NS - 1 rows (3 x 20 KB per CTA) are in flight; a lane reads its 21 values of the
+// next row from shared memory at the top of a step, exactly where the global loads were, so the
+// arithmetic and its order are untouched (bit-identical).  Segments that wrap around in x (first
+// and last CTA) are copied in pieces.  Needs an even nx (16-byte alignment of the pieces).
+constexpr int RING_NS = 4, RING_W = 120, RING_ARR = 21;
+struct RingSmem {
+    double data[RING_NS][RING_ARR][RING_W];
+    unsigned long long full[RING_NS], empty[RING_NS];
+    const double* base[RING_ARR];
+};
+
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned long long* bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(unsigned long long* bar, unsigned bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity)
+{
+    unsigned ok;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok)
+                     : "r"(smem_u32(bar)), "r"(parity)
+                     : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, unsigned long long* bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+                 "l"(__cvta_generic_to_global(src)), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+// warp 0 (all lanes enter): bring row r of the 21 arrays into stage st.  c0 = first owned column
+// of the CTA; the segment starts two columns to its left.
+__device__ __forceinline__ void ring_fill(const MevpArgs& A, RingSmem& R, int r, int st, int c0, int lane)
+{
+    if (lane == 0)
+        mbar_arrive_expect_tx(&R.full[st], RING_ARR * RING_W * (unsigned)sizeof(double));
+    __syncwarp();
+    if (lane < RING_ARR) {
+        const int row = plane_row(A, (lane == 13 || lane == 14) ? r + 1 : r); // u, v: node row r + 1
+        const double* src = R.base[lane] + row * A.nx;
+        double* dst = &R.data[st][lane][0];
+        int pos = c0 - MARCH_OFF, rem = RING_W, off = 0;
+        while (rem > 0) {
+            const int g = wrap_idx(pos, A.nx);
+            const int n = min(rem, A.nx - g);
+            bulk_g2s(dst + off, src + g, (unsigned)n * 8u, &R.full[st]);
+            pos += n;
+            off += n;
+            rem -= n;
+        }
+    }
+}
+
+// the lane's 21 values of row r (the k-th row of the band's march) from the ring
+__device__ __forceinline__ void ring_load(const MevpArgs& A, RingSmem& R, int r, int k, int gi, int col, int lane, MarchRow& Z)
+{
+    const int st = k % RING_NS;
+    mbar_wait(&R.full[st], (unsigned)(k / RING_NS) & 1u);
+    const int gr = plane_row(A, r);
+    Z.k = gr * A.nx + gi;
+    const double(*D)[RING_W] = R.data[st];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        Z.s11[c] = D[c][col];
+        Z.s12[c] = D[3 + c][col];
+        Z.s22[c] = D[6 + c][col];
+    }
+#pragma unroll
+    for (int g = 0; g < 4; ++g)
+        Z.pg[g] = D[9 + g][col];
+    Z.un = D[13][col];
+    Z.vn = D[14][col];
+    Z.unr = Z.vnr = 0.;
+    if (lane == 31) {
+        Z.unr = D[13][col + 1];
+        Z.vnr = D[14][col + 1];
+    }
+    Z.uo = D[15][col];
+    Z.vo = D[16][col];
+    Z.cx0 = D[17][col];
+    Z.cy0 = D[18][col];
+    Z.mdt = D[19][col];
+    Z.acd = D[20][col];
+    Z.act = !dirichlet(A, gi, gr - NSDG_GHOST);
+    // every lane's reads of the stage are done before it is handed back to the copy engine
+    __syncwarp();
+    if (lane == 0)
+        mbar_arrive(&R.empty[st]);
+}
+
 // One step of the march at row ra.  X: row ra-1 (S^{p+1}, P_g, node constants, u^{p+1}; its
 // un/vn/unr/vnr are u^p of node row ra), Y: the loaded data of row ra, Z: target of the loads of
 // row ra+1.  d2p: divergence coefficients of S^{p+2}, cell row ra-2.  own: this lane stores row
 // ra-1.
-template <bool PEER, bool CG>
+template <bool PEER, bool CG, bool RING>
 __device__ __forceinline__ void march_step(const MevpArgs& A, int ra, int gi, int gip, int lane, bool own,
-    MarchRow& X, MarchRow& Y, MarchRow& Z, double (&d2p)[7])
+    MarchRow& X, MarchRow& Y, MarchRow& Z, double (&d2p)[7], RingSmem* R, int s, int nsteps, int c0, int col)
 {
-    march_load<CG>(A, ra + 1, gi, gip, lane, Z); // consumed by the next step (wasted on the last one)
+    if (RING) {
+        // warp 0 refills the stage every warp has read in the previous step with the row RING_NS
+        // ahead of it, then every warp takes the next row (march row s + 1) from the ring
+        if (threadIdx.x < 32 && s + RING_NS <= nsteps) { // warp 0 of the CTA
+            mbar_wait(&R->empty[s % RING_NS], (unsigned)(s / RING_NS) & 1u);
+            ring_fill(A, *R, ra + RING_NS, s % RING_NS, c0, lane);
+        }
+        ring_load(A, *R, ra + 1, s + 1, gi, col, lane, Z);
+    } else
+        march_load<CG>(A, ra + 1, gi, gip, lane, Z); // consumed by the next step (wasted on the last one)
 
     // ---- A: stress p+1 of cell row ra
     Y.unr = from_right(Y.un, Y.unr, lane);
@@ -860,12 +977,40 @@ __device__ __forceinline__ void march_step(const MevpArgs& A, int ra, int gi, in
         d2p[c] = hi[c];
 }
 
-template <bool PEER, bool CG>
+template <bool PEER, bool CG, bool RING>
 __global__ void __launch_bounds__(MARCH_WPB * 32, 2) mevp_march_kernel(const __grid_constant__ MevpArgs A)
 {
+    extern __shared__ __align__(128) unsigned char ring_raw[];
+    RingSmem* R = reinterpret_cast<RingSmem*>(ring_raw);
     const int lane = threadIdx.x & 31;
     const int wg = blockIdx.x * MARCH_WPB + (threadIdx.x >> 5); // warp's column block
     const int cb = wg * MARCH_OWN; // first owned column
+    const int c0 = blockIdx.x * MARCH_WPB * MARCH_OWN; // first owned column of the CTA
+    const int col = (threadIdx.x >> 5) * MARCH_OWN + lane; // this lane's column in the CTA's row segment
+    if (RING) {
+        if (threadIdx.x == 0) {
+            const int nw = (A.nx + MARCH_OWN - 1) / MARCH_OWN; // warps with columns, over the grid
+            const int active = min(MARCH_WPB, nw - (int)blockIdx.x * MARCH_WPB);
+            for (int q = 0; q < RING_NS; ++q) {
+                mbar_init(&R->full[q], 1);
+                mbar_init(&R->empty[q], (unsigned)active);
+            }
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        if (threadIdx.x < RING_ARR) {
+            const int q = threadIdx.x;
+            const double* b = q < 3 ? A.S11 + q * A.plane : q < 6 ? A.S12 + (q - 3) * A.plane
+                : q < 9         ? A.S22 + (q - 6) * A.plane
+                : q < 13        ? A.pg + (q - 9) * A.plane
+                : q == 13       ? A.u
+                : q == 14       ? A.v
+                : q == 15       ? A.uo
+                : q == 16       ? A.vo
+                                : A.nd + (q - 17) * A.plane;
+            R->base[q] = b;
+        }
+        __syncthreads();
+    }
     if (cb >= A.nx)
         return; // whole warp
     const int cu = cb - MARCH_OFF + lane; // unwrapped column of this lane
@@ -900,10 +1045,19 @@ __global__ void __launch_bounds__(MARCH_WPB * 32, 2) mevp_march_kernel(const __g
         X.unr = from_right(X.un, ldm<CG>(A.u + g0 * A.nx + gip), lane);
         X.vnr = from_right(X.vn, ldm<CG>(A.v + g0 * A.nx + gip), lane);
     }
-    march_load<CG>(A, b0 - 2, gi, gip, lane, Y);
+    if (RING) {
+        if (PEER)
+            asm volatile("fence.proxy.async;" ::: "memory"); // peer stores seen above -> bulk-copy reads
+        if (threadIdx.x < 32) // warp 0: the first RING_NS rows of the march
+            for (int k = 0; k < RING_NS && k <= nsteps; ++k)
+                ring_fill(A, *R, b0 - 2 + k, k, c0, lane);
+        ring_load(A, *R, b0 - 2, 0, gi, col, lane, Y);
+    } else
+        march_load<CG>(A, b0 - 2, gi, gip, lane, Y);
     // step s works on row ra = b0 - 2 + s and stores the owned row ra - 1 when 3 <= s; the first
     // steps run phases C / D on the zero-initialised records (finite values, never stored)
-#define NSDG_STEP(s, X, Y, Z) march_step<PEER, CG>(A, b0 - 2 + (s), gi, gip, lane, own_col && (s) >= 3, X, Y, Z, d2p)
+#define NSDG_STEP(s, X, Y, Z) \
+    march_step<PEER, CG, RING>(A, b0 - 2 + (s), gi, gip, lane, own_col && (s) >= 3, X, Y, Z, d2p, R, (s), nsteps, c0, col)
     int s = 0;
 #pragma unroll 1
     for (; s + 2 < nsteps; s += 3) {
@@ -1231,6 +1385,16 @@ int nsdg_mevp_pair(nsdg_ctx* ctx, double dt, const double* u, const double* v, d
         const int nwarps = (int)((d->nx + MARCH_OWN - 1) / MARCH_OWN);
         A.band = ry;
         dim3 block(MARCH_WPB * 32), grid((unsigned)((nwarps + MARCH_WPB - 1) / MARCH_WPB), (unsigned)((nrows + ry - 1) / ry));
+        // shared-memory ring variant (nsdg_dyn_tuning.march_ring; needs an even nx)
+        const bool ring = d->tune.march_ring > 0 && d->nx % 2 == 0;
+        if (ring) {
+            static bool attr_set = false;
+            if (!attr_set) {
+                NSDG_CUDA(ctx, cudaFuncSetAttribute(mevp_march_kernel<false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RingSmem)));
+                NSDG_CUDA(ctx, cudaFuncSetAttribute(mevp_march_kernel<true, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RingSmem)));
+                attr_set = true;
+            }
+        }
         if (peer_seq) {
             // the two top rows go to the rank above and are published by the LAST band: a
             // remainder band of one row is merged into the band below it
@@ -1255,15 +1419,21 @@ int nsdg_mevp_pair(nsdg_ctx* ctx, double dt, const double* u, const double* v, d
             A.flag_up = d->up.flags;
             A.flag_dn = d->dn.flags;
             A.seq = peer_seq;
-            static const bool nc = getenv("NSDG_PEER_LDNC") && atoi(getenv("NSDG_PEER_LDNC")); // experiment
-            if (nc)
-                NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<true, false><<<grid, block, 0, st>>>(A)));
+            if (ring)
+                NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<true, true, true><<<grid, block, sizeof(RingSmem), st>>>(A)));
             else
-                NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<true, true><<<grid, block, 0, st>>>(A)));
+                NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<true, true, false><<<grid, block, 0, st>>>(A)));
+        } else if (ring) {
+            if (st == ctx->stream) {
+                NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<false, false, true><<<grid, block, sizeof(RingSmem), st>>>(A)));
+            } else {
+                mevp_march_kernel<false, false, true><<<grid, block, sizeof(RingSmem), st>>>(A);
+                NSDG_LAUNCHED(ctx);
+            }
         } else if (st == ctx->stream) {
-            NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<false, false><<<grid, block, 0, st>>>(A)));
+            NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<false, false, false><<<grid, block, 0, st>>>(A)));
         } else { /* the per-kernel profiler brackets the compute stream only */
-            mevp_march_kernel<false, false><<<grid, block, 0, st>>>(A);
+            mevp_march_kernel<false, false, false><<<grid, block, 0, st>>>(A);
             NSDG_LAUNCHED(ctx);
         }
         return NSDG_OK;

@@ -22,6 +22,7 @@ NAMES = ("H", "A", "U", "V", "S11", "S12", "S22")
 VARIANTS = (("peer", {}),
             ("peer-rows16", {"march_rows": 16}),
             ("peer-rows3", {"march_rows": 3}),  # remainder bands of one row in several cases
+            ("peer-ring", {"march_ring": 1}),  # ghost rows read by the bulk-copy engine
             ("nccl-overlap", {"halo_peer": -1}),
             ("nccl-overlap-rows16", {"halo_peer": -1, "march_rows": 16}),
             ("nccl-serial", {"halo_peer": -1, "halo_overlap": -1}),

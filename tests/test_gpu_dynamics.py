@@ -411,7 +411,8 @@ def test_error_behaviour(ctx):
 def test_pair_kernel_variants_bit_identical(ctx):
     """The sub-iteration kernels share their arithmetic: the marching pair kernel (default, band
     heights chosen per grid / 64 / 16 / 5 rows), the tiled pair kernel in two tile shapes,
-    single fused sub-iterations, CUDA-graph replay, and the marching / one-thread-per-cell dG2
+    single fused sub-iterations, CUDA-graph replay, the shared-memory-ring variant of the marching
+    kernel (rows ahead brought in by cp.async.bulk), and the marching / one-thread-per-cell dG2
     transport stage kernels give the same bits on periodic and box grids, ragged sizes and a
     grid narrower than the halo.  The variant is a per-context knob of the C ABI
     (nsdg_dyn_set_tuning), so all of them run in this one process."""
@@ -424,7 +425,8 @@ def test_pair_kernel_variants_bit_identical(ctx):
                 "tiled32x8": {"march_rows": -1, "pair_tile": "32x8"}, "single": {"pair": -1},
                 "graph": {"graph": 1}, "nograph": {"graph": -1},
                 "transport-march": {"transport_march": 1}, "transport-tiled": {"transport_march": -1},
-                "transport-march-rows16": {"transport_march": 1, "march_rows": 16}}
+                "transport-march-rows16": {"transport_march": 1, "march_rows": 16},
+                "ring": {"march_ring": 1}, "ring-rows5": {"march_ring": 1, "march_rows": 5}}
     digests = {k: dyn_digest.digest(ctx, v) for k, v in variants.items()}
     assert len(set(digests.values())) == 1, digests
 
