@@ -805,9 +805,13 @@ __device__ __forceinline__ void peer_store(const MevpArgs& A, int rs, int gi, bo
 // next row from shared memory at the top of a step, exactly where the global loads were, so the
 // arithmetic and its order are untouched (bit-identical).  Segments that wrap around in x (first
 // and last CTA) are copied in pieces.  Needs an even nx (16-byte alignment of the pieces).
-constexpr int RING_NS = 4, RING_W = 120, RING_ARR = 21;
-struct RingSmem {
-    double data[RING_NS][RING_ARR][RING_W];
+constexpr int RING_NS = 4, RING_ARR = 21;
+template <int WPB> struct RingSmem {
+    // the CTA's owned columns plus 16 on either side: the segment starts on a 128-byte boundary
+    // of the row (c0 is a multiple of 112 = 7 x 16 columns) and is a whole number of 128-byte lines
+    static constexpr int W = WPB * 28 + 32;
+    static constexpr int LEFT = 16; // columns in front of the first owned one
+    double data[RING_NS][RING_ARR][W];
     unsigned long long full[RING_NS], empty[RING_NS];
     const double* base[RING_ARR];
 };
@@ -844,8 +848,10 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned by
 
 // warp 0 (all lanes enter): bring row r of the 21 arrays into stage st.  c0 = first owned column
 // of the CTA; the segment starts two columns to its left.
-__device__ __forceinline__ void ring_fill(const MevpArgs& A, RingSmem& R, int r, int st, int c0, int lane)
+template <int WPB>
+__device__ __forceinline__ void ring_fill(const MevpArgs& A, RingSmem<WPB>& R, int r, int st, int c0, int lane)
 {
+    constexpr int RING_W = RingSmem<WPB>::W;
     if (lane == 0)
         mbar_arrive_expect_tx(&R.full[st], RING_ARR * RING_W * (unsigned)sizeof(double));
     __syncwarp();
@@ -853,7 +859,7 @@ __device__ __forceinline__ void ring_fill(const MevpArgs& A, RingSmem& R, int r,
         const int row = plane_row(A, (lane == 13 || lane == 14) ? r + 1 : r); // u, v: node row r + 1
         const double* src = R.base[lane] + row * A.nx;
         double* dst = &R.data[st][lane][0];
-        int pos = c0 - MARCH_OFF, rem = RING_W, off = 0;
+        int pos = c0 - RingSmem<WPB>::LEFT, rem = RING_W, off = 0;
         while (rem > 0) {
             const int g = wrap_idx(pos, A.nx);
             const int n = min(rem, A.nx - g);
@@ -866,8 +872,10 @@ __device__ __forceinline__ void ring_fill(const MevpArgs& A, RingSmem& R, int r,
 }
 
 // the lane's 21 values of row r (the k-th row of the band's march) from the ring
-__device__ __forceinline__ void ring_load(const MevpArgs& A, RingSmem& R, int r, int k, int gi, int col, int lane, MarchRow& Z)
+template <int WPB>
+__device__ __forceinline__ void ring_load(const MevpArgs& A, RingSmem<WPB>& R, int r, int k, int gi, int col, int lane, MarchRow& Z)
 {
+    constexpr int RING_W = RingSmem<WPB>::W;
     const int st = k % RING_NS;
     mbar_wait(&R.full[st], (unsigned)(k / RING_NS) & 1u);
     const int gr = plane_row(A, r);
@@ -906,9 +914,9 @@ __device__ __forceinline__ void ring_load(const MevpArgs& A, RingSmem& R, int r,
 // un/vn/unr/vnr are u^p of node row ra), Y: the loaded data of row ra, Z: target of the loads of
 // row ra+1.  d2p: divergence coefficients of S^{p+2}, cell row ra-2.  own: this lane stores row
 // ra-1.
-template <bool PEER, bool CG, bool RING>
+template <bool PEER, bool CG, bool RING, int WPB>
 __device__ __forceinline__ void march_step(const MevpArgs& A, int ra, int gi, int gip, int lane, bool own,
-    MarchRow& X, MarchRow& Y, MarchRow& Z, double (&d2p)[7], RingSmem* R, int s, int nsteps, int c0, int col)
+    MarchRow& X, MarchRow& Y, MarchRow& Z, double (&d2p)[7], RingSmem<WPB>* R, int s, int nsteps, int c0, int col)
 {
     if (RING) {
         // warp 0 refills the stage every warp has read in the previous step with the row RING_NS
@@ -977,16 +985,18 @@ __device__ __forceinline__ void march_step(const MevpArgs& A, int ra, int gi, in
         d2p[c] = hi[c];
 }
 
-template <bool PEER, bool CG, bool RING>
-__global__ void __launch_bounds__(MARCH_WPB * 32, 2) mevp_march_kernel(const __grid_constant__ MevpArgs A)
+template <bool PEER, bool CG, bool RING, int WPB>
+__global__ void __launch_bounds__(WPB * 32, 8 / WPB) mevp_march_kernel(const __grid_constant__ MevpArgs A)
 {
+    constexpr int MARCH_WPB = WPB; // warps (28-column blocks) per CTA: 4, or 8 for the ring variant
     extern __shared__ __align__(128) unsigned char ring_raw[];
-    RingSmem* R = reinterpret_cast<RingSmem*>(ring_raw);
+    RingSmem<WPB>* R = reinterpret_cast<RingSmem<WPB>*>(ring_raw);
     const int lane = threadIdx.x & 31;
     const int wg = blockIdx.x * MARCH_WPB + (threadIdx.x >> 5); // warp's column block
     const int cb = wg * MARCH_OWN; // first owned column
     const int c0 = blockIdx.x * MARCH_WPB * MARCH_OWN; // first owned column of the CTA
-    const int col = (threadIdx.x >> 5) * MARCH_OWN + lane; // this lane's column in the CTA's row segment
+    // this lane's column in the CTA's row segment (ring variant)
+    const int col = RingSmem<WPB>::LEFT - MARCH_OFF + (threadIdx.x >> 5) * MARCH_OWN + lane;
     if (RING) {
         if (threadIdx.x == 0) {
             const int nw = (A.nx + MARCH_OWN - 1) / MARCH_OWN; // warps with columns, over the grid
@@ -1057,7 +1067,7 @@ __global__ void __launch_bounds__(MARCH_WPB * 32, 2) mevp_march_kernel(const __g
     // step s works on row ra = b0 - 2 + s and stores the owned row ra - 1 when 3 <= s; the first
     // steps run phases C / D on the zero-initialised records (finite values, never stored)
 #define NSDG_STEP(s, X, Y, Z) \
-    march_step<PEER, CG, RING>(A, b0 - 2 + (s), gi, gip, lane, own_col && (s) >= 3, X, Y, Z, d2p, R, (s), nsteps, c0, col)
+    march_step<PEER, CG, RING, WPB>(A, b0 - 2 + (s), gi, gip, lane, own_col && (s) >= 3, X, Y, Z, d2p, R, (s), nsteps, c0, col)
     int s = 0;
 #pragma unroll 1
     for (; s + 2 < nsteps; s += 3) {
@@ -1385,15 +1395,19 @@ int nsdg_mevp_pair(nsdg_ctx* ctx, double dt, const double* u, const double* v, d
         const int nwarps = (int)((d->nx + MARCH_OWN - 1) / MARCH_OWN);
         A.band = ry;
         dim3 block(MARCH_WPB * 32), grid((unsigned)((nwarps + MARCH_WPB - 1) / MARCH_WPB), (unsigned)((nrows + ry - 1) / ry));
-        // shared-memory ring variant (nsdg_dyn_tuning.march_ring; needs an even nx)
-        const bool ring = d->tune.march_ring > 0 && d->nx % 2 == 0;
+        // shared-memory ring variant (nsdg_dyn_tuning.march_ring; needs an even nx): CTAs of eight
+        // warps, one per SM, so that a bulk copy moves 1.9 KB
+        const bool ring = d->tune.march_ring > 0 && d->nx % 16 == 0;
+        constexpr int RWPB = 4;
         if (ring) {
             static bool attr_set = false;
             if (!attr_set) {
-                NSDG_CUDA(ctx, cudaFuncSetAttribute(mevp_march_kernel<false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RingSmem)));
-                NSDG_CUDA(ctx, cudaFuncSetAttribute(mevp_march_kernel<true, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RingSmem)));
+                NSDG_CUDA(ctx, cudaFuncSetAttribute(mevp_march_kernel<false, false, true, RWPB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RingSmem<RWPB>)));
+                NSDG_CUDA(ctx, cudaFuncSetAttribute(mevp_march_kernel<true, true, true, RWPB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RingSmem<RWPB>)));
                 attr_set = true;
             }
+            block = dim3(RWPB * 32);
+            grid.x = (unsigned)((nwarps + RWPB - 1) / RWPB);
         }
         if (peer_seq) {
             // the two top rows go to the rank above and are published by the LAST band: a
@@ -1420,20 +1434,20 @@ int nsdg_mevp_pair(nsdg_ctx* ctx, double dt, const double* u, const double* v, d
             A.flag_dn = d->dn.flags;
             A.seq = peer_seq;
             if (ring)
-                NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<true, true, true><<<grid, block, sizeof(RingSmem), st>>>(A)));
+                NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<true, true, true, RWPB><<<grid, block, sizeof(RingSmem<RWPB>), st>>>(A)));
             else
-                NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<true, true, false><<<grid, block, 0, st>>>(A)));
+                NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<true, true, false, MARCH_WPB><<<grid, block, 0, st>>>(A)));
         } else if (ring) {
             if (st == ctx->stream) {
-                NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<false, false, true><<<grid, block, sizeof(RingSmem), st>>>(A)));
+                NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<false, false, true, RWPB><<<grid, block, sizeof(RingSmem<RWPB>), st>>>(A)));
             } else {
-                mevp_march_kernel<false, false, true><<<grid, block, sizeof(RingSmem), st>>>(A);
+                mevp_march_kernel<false, false, true, RWPB><<<grid, block, sizeof(RingSmem<RWPB>), st>>>(A);
                 NSDG_LAUNCHED(ctx);
             }
         } else if (st == ctx->stream) {
-            NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<false, false, false><<<grid, block, 0, st>>>(A)));
+            NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<false, false, false, MARCH_WPB><<<grid, block, 0, st>>>(A)));
         } else { /* the per-kernel profiler brackets the compute stream only */
-            mevp_march_kernel<false, false, false><<<grid, block, 0, st>>>(A);
+            mevp_march_kernel<false, false, false, MARCH_WPB><<<grid, block, 0, st>>>(A);
             NSDG_LAUNCHED(ctx);
         }
         return NSDG_OK;
