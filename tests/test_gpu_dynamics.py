@@ -496,3 +496,55 @@ def test_tuning_roundtrip_and_state_ownership(ctx):
     assert ctx.lib.nsdg_thermo_init(ctx.h, 10, 1) == 0
     assert ctx.lib.nsdg_thermo_init(ctx.h, 10, 1) == NSDG_ESTATE
     assert ctx.lib.nsdg_thermo_release(ctx.h) == 0
+
+
+def test_row_range_upload_download(ctx):
+    """nsdg_dyn_upload_rows / download_rows: chunked I/O of a strip equals the whole-field calls
+    (DG and node fields), and out-of-range rows are rejected."""
+    nx, ny = 40, 23
+    r = np.random.default_rng(2)
+    dyn = GpuDynamics(ctx, nx, ny, 1.0, 1.0, 6)
+    H = r.standard_normal((6, ny, nx))
+    U = r.standard_normal((ny, nx))
+    for c0 in range(0, ny, 7):
+        n = min(7, ny - c0)
+        dyn.upload_rows("H", c0, np.ascontiguousarray(H[:, c0:c0 + n]))
+        dyn.upload_rows("U", c0, np.ascontiguousarray(U[c0:c0 + n]))
+    assert np.array_equal(dyn.download("H"), H) and np.array_equal(dyn.download("U"), U)
+    assert np.array_equal(dyn.download_rows("H", 5, 9), H[:, 5:14])
+    assert np.array_equal(dyn.download_rows("U", 20, 3), U[20:23])
+    with pytest.raises(NsdgError):
+        dyn.download_rows("U", 20, 4)
+    with pytest.raises(ValueError):
+        dyn.upload_rows("H", 0, np.zeros((6, 2, nx - 1)))
+
+
+def test_graph_replay_follows_parameter_and_buffer_changes(ctx):
+    """CUDA-graph replay (forced on): captured launches bake in kernel arguments and buffer roles.
+    Changing the mEVP parameters, uploading new fields, an odd sub-iteration count (buffer roles
+    end up swapped) and deferred host steps (forcing buffers swap) must all give what plain
+    launches give."""
+    nx, ny = 72, 40
+    F, hx, hy = S.box_case(nx, ny, 6)
+    F["U"], F["V"] = random_velocity(nx, ny, 8, 0.05)
+    out = {}
+    for name, g in (("graph", 1), ("plain", -1)):
+        mp = MevpParams.defaults()
+        mp.bc = BC_BOX
+        dyn = GpuDynamics(ctx, nx, ny, hx, hy, 6, mevp=mp, tuning={"graph": g})
+        dyn.upload_all(F)
+        for nsub in (6, 7, 7, 6):  # odd counts leave the ping-pong buffers swapped
+            dyn.step(120.0, nsub)
+        mp.alpha = mp.beta = 200.0
+        dyn.set_mevp_params(mp)  # cached graphs must not survive this
+        dyn.step(120.0, 6)
+        dyn.upload("UATM", 0.5 * F["UATM"])
+        dyn.step(120.0, 6)
+        outs = [{k: np.empty(dyn.field_shape(k)) for k in ("H", "U", "S11")} for _ in range(3)]
+        for q in range(3):
+            dyn.step_host(120.0, 6, {"UATM": np.ascontiguousarray((1 + 0.1 * q) * F["UATM"])}, outs[q], deferred=True)
+        dyn.host_wait()
+        out[name] = [dyn.download(k) for k in ("H", "A", "U", "V", "S11", "S12", "S22")] + [o[k] for o in outs for k in o]
+        dyn.close()
+    for a, b in zip(out["graph"], out["plain"]):
+        assert np.array_equal(a, b)
