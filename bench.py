@@ -935,8 +935,8 @@ def use_all_host_threads():
 
 def trim(rec):
     """a sub-record keeps what it measured, not the contract's constant keys"""
-    if rec is None:
-        return None
+    if rec is None or "error" in rec:
+        return rec
     for k in ("higher_is_better", "vs_baseline", "dtype", "data"):
         rec.pop(k, None)
     return rec
@@ -958,16 +958,22 @@ def run_gpu(args):
         line = measure_north_star(args, env)
         log(f"north star done at {time.perf_counter() - t_start:.0f} s")
         if not args.main_only:
-            th = measure_thermo(args, env)
-            log(f"thermo done at {time.perf_counter() - t_start:.0f} s")
-            cone = measure_cone(args, env) if env.world == 1 else None
-            log(f"cone done at {time.perf_counter() - t_start:.0f} s")
-            strong = measure_north_star(args, env, strong=True, with_e2e=False, with_cpu=False,
-                                        steps=args.strong_steps, warmup=1)
-            log(f"strong done at {time.perf_counter() - t_start:.0f} s")
+            def sub(name, fn):
+                """a sub-record must never cost the main line: a failure is reported in its place"""
+                try:
+                    rec = fn()
+                except Exception as e:  # noqa: BLE001
+                    rec = {"error": f"{type(e).__name__}: {e}"}
+                    env.torch.cuda.empty_cache()
+                log(f"{name} done at {time.perf_counter() - t_start:.0f} s")
+                return rec
+            th = sub("thermo", lambda: measure_thermo(args, env))
+            cone = sub("cone", lambda: measure_cone(args, env)) if env.world == 1 else None
+            strong = sub("strong", lambda: measure_north_star(args, env, strong=True, with_e2e=False,
+                                                              with_cpu=False, steps=args.strong_steps, warmup=1))
             if env.rank == 0:
                 line["configs"] = {"thermo_4096sq": trim(th), "cone_1024sq": trim(cone)}
-                if strong:
+                if strong and "error" not in strong:
                     strong = trim(strong)
                     strong["cells_per_gpu"] = 16384 * 16384 // env.world
                     strong["note"] = ("strong scaling: the same 16384^2 grid at every N; efficiency at N "

@@ -130,17 +130,23 @@ int transport_fields(nsdg_ctx* ctx, int nfields, double** phi, double** s1, doub
         }
         return NSDG_OK;
     };
-    if (multi) { // velocity ghosts (upper node row is read by the top cell row)
-        PlaneSet ps;
-        ps.n = 0;
-        ps.p[ps.n++] = d->f[NSDG_DF_U];
-        ps.p[ps.n++] = d->f[NSDG_DF_V];
-        if ((rc = nsdg_halo_exchange(ctx, ps, 2)))
+    // stage 1: s1 = phi + dt L(phi).  Strips: one message per neighbour carries the upper ghost
+    // node row of the velocity (read by the top cell row of every stage) and the tracers' rows.
+    if (multi) {
+        HaloSpec hs[2];
+        hs[0].planes.n = 0;
+        hs[0].planes.p[hs[0].planes.n++] = d->f[NSDG_DF_U];
+        hs[0].planes.p[hs[0].planes.n++] = d->f[NSDG_DF_V];
+        hs[0].nlo = 0;
+        hs[0].nhi = 1;
+        hs[1].planes.n = 0;
+        for (int f = 0; f < nfields; ++f)
+            append(hs[1].planes, d, phi[f], d->nc);
+        hs[1].nlo = hs[1].nhi = 1;
+        if ((rc = nsdg_halo_exchange(ctx, hs, 2)))
             return rc;
     }
-    // stage 1: s1 = phi + dt L(phi)
-    if ((rc = halo(phi)) || (rc = nsdg_transport_stage(ctx, nfields, phi, nullptr, s1, 0., 1., dt, r0, r1))
-        || (rc = limit(s1)))
+    if ((rc = nsdg_transport_stage(ctx, nfields, phi, nullptr, s1, 0., 1., dt, r0, r1)) || (rc = limit(s1)))
         return rc;
     if (d->rk == 1) {
         // copy the interior of every component (interior rows are contiguous within a plane)
@@ -179,21 +185,22 @@ int mevp_cycle(nsdg_ctx* ctx, double dt, int nsub)
         // ghost rows the sub-cycle reads: H, A (strength on the recomputed ghost cells, nodal
         // means), the stress, and every node array (velocity, forcing) -- the pair kernel works
         // on a two-row halo below and above (one row above for cell data)
-        HaloSpec hs[2];
+        HaloSpec hs[3];
         hs[0].planes = planes_of(d, d->f[NSDG_DF_H], d->nc);
         append(hs[0].planes, d, d->f[NSDG_DF_A], d->nc);
         hs[0].nlo = 2;
         hs[0].nhi = 1;
-        if ((rc = nsdg_halo_exchange(ctx, hs, 1)))
-            return rc;
-        hs[0].planes = planes_of(d, d->f[NSDG_DF_S11], 3);
-        append(hs[0].planes, d, d->f[NSDG_DF_S12], 3);
-        append(hs[0].planes, d, d->f[NSDG_DF_S22], 3);
-        hs[1].planes.n = 0;
+        hs[1].planes = planes_of(d, d->f[NSDG_DF_S11], 3);
+        append(hs[1].planes, d, d->f[NSDG_DF_S12], 3);
+        append(hs[1].planes, d, d->f[NSDG_DF_S22], 3);
+        hs[1].nlo = 2;
+        hs[1].nhi = 1;
+        hs[2].planes.n = 0;
         for (int q : { NSDG_DF_U, NSDG_DF_V, NSDG_DF_UATM, NSDG_DF_VATM, NSDG_DF_UOCN, NSDG_DF_VOCN })
-            hs[1].planes.p[hs[1].planes.n++] = d->f[q];
-        hs[1].nlo = hs[1].nhi = 2;
-        if ((rc = nsdg_halo_exchange(ctx, hs, 2)))
+            hs[2].planes.p[hs[2].planes.n++] = d->f[q];
+        hs[2].nlo = hs[2].nhi = 2;
+        // one message per neighbour: 54 rows up, 33 down at dG2
+        if ((rc = nsdg_halo_exchange(ctx, hs, 3)))
             return rc;
     }
     if ((rc = nsdg_mevp_prepare(ctx, dt)))

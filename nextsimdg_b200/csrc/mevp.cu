@@ -1400,7 +1400,7 @@ int nsdg_mevp_pair(nsdg_ctx* ctx, double dt, const double* u, const double* v, d
         const bool ring = d->tune.march_ring > 0 && d->nx % 16 == 0;
         constexpr int RWPB = 4;
         if (ring) {
-            static bool attr_set = false;
+            bool& attr_set = ctx->ring_attr_set; // per device: the attribute belongs to the context's GPU
             if (!attr_set) {
                 NSDG_CUDA(ctx, cudaFuncSetAttribute(mevp_march_kernel<false, false, true, RWPB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RingSmem<RWPB>)));
                 NSDG_CUDA(ctx, cudaFuncSetAttribute(mevp_march_kernel<true, true, true, RWPB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RingSmem<RWPB>)));
