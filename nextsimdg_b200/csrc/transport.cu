@@ -253,10 +253,10 @@ __device__ __forceinline__ void dg1_edge(const double (&vn)[3], double m0, doubl
     M0 = F0 + F1;
     M1 = g * (F1 - F0);
 }
-// c: own coefficients; cl / cr / cb / ct: the neighbours' (left, right, below, above)
-__device__ __forceinline__ void dg1_cell(const double (&c)[3], const double (&cl)[3], const double (&cr)[3],
-    const double (&cb)[3], const double (&ct)[3], const double (&uL)[3], const double (&uR)[3], const double (&vB)[3],
-    const double (&vT)[3], double (&rr)[3])
+// rr from the flux moments (M0, M1) of the four edges
+__device__ __forceinline__ void dg1_cell_m(const double (&c)[3], const double (&uL)[3], const double (&uR)[3],
+    const double (&vB)[3], const double (&vT)[3], const double (&lm)[2], const double (&rm)[2], const double (&bm)[2],
+    const double (&tm)[2], double (&rr)[3])
 {
     constexpr double g = 0.28867513459481287;
     constexpr double XI[2] = { 0.5 - g, 0.5 + g };
@@ -276,22 +276,48 @@ __device__ __forceinline__ void dg1_cell(const double (&c)[3], const double (&cl
             }
         }
     }
-    double L0, L1, R0, R1;
-    // x-normal edges: own traces (c0 -+ c1/2, c2), the neighbours' facing traces
-    dg1_edge(uL, fma(0.5, cl[1], cl[0]), cl[2], fma(-0.5, c[1], c[0]), c[2], L0, L1);
-    dg1_edge(uR, fma(0.5, c[1], c[0]), c[2], fma(-0.5, cr[1], cr[0]), cr[2], R0, R1);
-    r0 += L0 - R0;
-    r1 = fma(-0.5, L0 + R0, r1);
-    r2 += L1 - R1;
-    // y-normal edges: traces (c0 -+ c2/2, c1)
-    dg1_edge(vB, fma(0.5, cb[2], cb[0]), cb[1], fma(-0.5, c[2], c[0]), c[1], L0, L1);
-    dg1_edge(vT, fma(0.5, c[2], c[0]), c[1], fma(-0.5, ct[2], ct[0]), ct[1], R0, R1);
-    r0 += L0 - R0;
-    r1 += L1 - R1;
-    r2 = fma(-0.5, L0 + R0, r2);
+    r0 += lm[0] - rm[0];
+    r1 = fma(-0.5, lm[0] + rm[0], r1);
+    r2 += lm[1] - rm[1];
+    r0 += bm[0] - tm[0];
+    r1 += bm[1] - tm[1];
+    r2 = fma(-0.5, bm[0] + tm[0], r2);
     rr[0] = r0;
     rr[1] = r1;
     rr[2] = r2;
+}
+// own traces of a dG1 cell: x-normal edges (c0 -+ c1/2, c2), y-normal edges (c0 -+ c2/2, c1)
+struct Traces1 {
+    double l[2], r[2], b[2], t[2];
+};
+__device__ __forceinline__ void dg1_traces(const double (&c)[3], Traces1& T)
+{
+    T.l[0] = fma(-0.5, c[1], c[0]);
+    T.l[1] = c[2];
+    T.r[0] = fma(0.5, c[1], c[0]);
+    T.r[1] = c[2];
+    T.b[0] = fma(-0.5, c[2], c[0]);
+    T.b[1] = c[1];
+    T.t[0] = fma(0.5, c[2], c[0]);
+    T.t[1] = c[1];
+}
+// c: own coefficients; cl / cr / cb / ct: the neighbours' (left, right, below, above)
+__device__ __forceinline__ void dg1_cell(const double (&c)[3], const double (&cl)[3], const double (&cr)[3],
+    const double (&cb)[3], const double (&ct)[3], const double (&uL)[3], const double (&uR)[3], const double (&vB)[3],
+    const double (&vT)[3], double (&rr)[3])
+{
+    Traces1 T, L, R, B, U;
+    dg1_traces(c, T);
+    dg1_traces(cl, L);
+    dg1_traces(cr, R);
+    dg1_traces(cb, B);
+    dg1_traces(ct, U);
+    double lm[2], rm[2], bm[2], tm[2];
+    dg1_edge(uL, L.r[0], L.r[1], T.l[0], T.l[1], lm[0], lm[1]);
+    dg1_edge(uR, T.r[0], T.r[1], R.l[0], R.l[1], rm[0], rm[1]);
+    dg1_edge(vB, B.t[0], B.t[1], T.b[0], T.b[1], bm[0], bm[1]);
+    dg1_edge(vT, T.t[0], T.t[1], U.b[0], U.b[1], tm[0], tm[1]);
+    dg1_cell_m(c, uL, uR, vB, vT, lm, rm, bm, tm, rr);
 }
 
 struct StageArgs {
@@ -308,11 +334,14 @@ struct StageArgs {
     int band; // rows per band of the marching kernel
 };
 
+template <int NQ>
 __device__ __forceinline__ void edge_velocities(const StageArgs& A, double u00, double u10, double u01, double u11,
     double v00, double v10, double v01, double v11, EdgeVel& V)
 {
+    if (NQ < 3)
+        V.uL[2] = V.uR[2] = V.vB[2] = V.vT[2] = 0.;
 #pragma unroll
-    for (int g = 0; g < 3; ++g) {
+    for (int g = 0; g < NQ; ++g) {
         V.uL[g] = edge_lerp(u00, u01, A.ku0[g], A.ku1[g]);
         V.uR[g] = edge_lerp(u10, u11, A.ku0[g], A.ku1[g]);
         V.vB[g] = edge_lerp(v00, v10, A.kv0[g], A.kv1[g]);
@@ -548,10 +577,10 @@ __global__ void limit_kernel(double* phi, int64_t nx, int64_t nyl, int64_t plane
 // The per-cell arithmetic is dg2_cell, shared with the tiled kernel: results are bit-identical.
 constexpr int TM_OWN = 28, TM_OFF = 2, TM_WPB = 4;
 
-struct TRow {
-    double c[6]; // src coefficients of cell row r
+template <int NC> struct TRow {
+    double c[NC]; // src coefficients of cell row r
     double u, v; // velocity at node row r, own column
-    double base[6]; // RK base of cell row r
+    double base[NC]; // RK base of cell row r
     int k; // plane index of (row r, own column)
 };
 
@@ -574,20 +603,20 @@ __device__ __forceinline__ int t_plane_row(const StageArgs& A, int r)
         return NSDG_GHOST + t_wrap(r - NSDG_GHOST, A.nyl);
     return max(0, min(r, A.nyl + 2 * NSDG_GHOST - 1));
 }
-__device__ __forceinline__ void tm_load_src(const StageArgs& A, int f, int r, int gi, TRow& R)
+template <int NC> __device__ __forceinline__ void tm_load_src(const StageArgs& A, int f, int r, int gi, TRow<NC>& R)
 {
     const int k = t_plane_row(A, r) * A.nx + gi;
     R.k = k;
 #pragma unroll
-    for (int q = 0; q < 6; ++q)
+    for (int q = 0; q < NC; ++q)
         R.c[q] = __ldg(A.src[f] + q * A.plane + k);
     R.u = __ldg(A.u + k);
     R.v = __ldg(A.v + k);
 }
-__device__ __forceinline__ void tm_load_base(const StageArgs& A, int f, TRow& R)
+template <int NC> __device__ __forceinline__ void tm_load_base(const StageArgs& A, int f, TRow<NC>& R)
 {
 #pragma unroll
-    for (int q = 0; q < 6; ++q)
+    for (int q = 0; q < NC; ++q)
         R.base[q] = __ldg(A.base[f] + q * A.plane + R.k);
 }
 
@@ -596,49 +625,66 @@ __device__ __forceinline__ void tm_load_base(const StageArgs& A, int f, TRow& R)
 // Every edge flux is computed ONCE: a lane computes the flux through its left edge and takes the
 // one through its right edge from the lane on its right; the flux through the top edge is kept
 // (bm) as the next row's bottom flux, and so are the top edge's normal velocities (vb).
-template <bool HAS_BASE>
-__device__ __forceinline__ void tm_step(const StageArgs& A, int f, int r, int gi, bool own, TRow& X, TRow& Y,
-    TRow& Z, double (&bm)[3], double (&vb)[3])
+template <int NC, bool HAS_BASE>
+__device__ __forceinline__ void tm_step(const StageArgs& A, int f, int r, int gi, bool own, TRow<NC>& X, TRow<NC>& Y,
+    TRow<NC>& Z, double (&bm)[3], double (&vb)[3])
 {
-    tm_load_src(A, f, r + 2, gi, Z);
+    constexpr int NT = NC == 6 ? 3 : 2; // numbers per edge trace / flux moments per edge / Gauss points
+    tm_load_src<NC>(A, f, r + 2, gi, Z);
     if (HAS_BASE)
-        tm_load_base(A, f, Y);
+        tm_load_base<NC>(A, f, Y);
     EdgeVel V;
     {
         const double u10 = __shfl_down_sync(0xffffffffu, X.u, 1), u11 = __shfl_down_sync(0xffffffffu, Y.u, 1);
         const double v10 = __shfl_down_sync(0xffffffffu, X.v, 1), v11 = __shfl_down_sync(0xffffffffu, Y.v, 1);
-        edge_velocities(A, X.u, u10, Y.u, u11, X.v, v10, Y.v, v11, V);
+        edge_velocities<NT>(A, X.u, u10, Y.u, u11, X.v, v10, Y.v, v11, V);
 #pragma unroll
         for (int q = 0; q < 3; ++q)
             V.vB[q] = vb[q]; // == the previous row's vT (same nodes, same expression)
     }
-    Traces T, TY;
-    dg2_traces(X.c, T);
-    dg2_traces(Y.c, TY);
-    double nbL[3], lm[3], rm[3], tm[3], rr[6];
+    double lm[3], rm[3], tm[3], rr[NC];
+    if constexpr (NC == 6) {
+        Traces T, TY;
+        dg2_traces(X.c, T);
+        dg2_traces(Y.c, TY);
+        double nbL[3];
 #pragma unroll
-    for (int q = 0; q < 3; ++q)
-        nbL[q] = __shfl_up_sync(0xffffffffu, T.r[q], 1); // left neighbour's xi = 1 trace
-    dg2_edge(V.uL, nbL, T.l, lm[0], lm[1], lm[2]);
+        for (int q = 0; q < 3; ++q)
+            nbL[q] = __shfl_up_sync(0xffffffffu, T.r[q], 1); // left neighbour's xi = 1 trace
+        dg2_edge(V.uL, nbL, T.l, lm[0], lm[1], lm[2]);
 #pragma unroll
-    for (int q = 0; q < 3; ++q)
-        rm[q] = __shfl_down_sync(0xffffffffu, lm[q], 1); // right edge = the right neighbour's left edge
-    dg2_edge(V.vT, T.t, TY.b, tm[0], tm[1], tm[2]);
-    dg2_cell_m(X.c, V, lm, rm, bm, tm, rr);
+        for (int q = 0; q < 3; ++q)
+            rm[q] = __shfl_down_sync(0xffffffffu, lm[q], 1); // right edge = the right neighbour's left edge
+        dg2_edge(V.vT, T.t, TY.b, tm[0], tm[1], tm[2]);
+        dg2_cell_m(X.c, V, lm, rm, bm, tm, rr);
+    } else {
+        Traces1 T, TY;
+        dg1_traces(X.c, T);
+        dg1_traces(Y.c, TY);
+        const double nb0 = __shfl_up_sync(0xffffffffu, T.r[0], 1), nb1 = __shfl_up_sync(0xffffffffu, T.r[1], 1);
+        dg1_edge(V.uL, nb0, nb1, T.l[0], T.l[1], lm[0], lm[1]);
+        rm[0] = __shfl_down_sync(0xffffffffu, lm[0], 1);
+        rm[1] = __shfl_down_sync(0xffffffffu, lm[1], 1);
+        dg1_edge(V.vT, T.t[0], T.t[1], TY.b[0], TY.b[1], tm[0], tm[1]);
+        const double l2[2] = { lm[0], lm[1] }, r2[2] = { rm[0], rm[1] }, b2[2] = { bm[0], bm[1] }, t2[2] = { tm[0], tm[1] };
+        dg1_cell_m(X.c, V.uL, V.uR, V.vB, V.vT, l2, r2, b2, t2, rr);
+        tm[2] = 0.;
+    }
     if (own) {
 #pragma unroll
-        for (int q = 0; q < 6; ++q)
+        for (int q = 0; q < NC; ++q)
             A.dst[f][q * A.plane + X.k] = stage_value<HAS_BASE>(X.c[q], rr[q], A.dtim[q], A.a, A.b, HAS_BASE ? X.base[q] : 0.);
     }
 #pragma unroll
-    for (int q = 0; q < 3; ++q) {
+    for (int q = 0; q < NT; ++q)
         bm[q] = tm[q];
+#pragma unroll
+    for (int q = 0; q < 3; ++q)
         vb[q] = V.vT[q];
-    }
 }
 
-template <bool HAS_BASE>
-__global__ void __launch_bounds__(TM_WPB * 32, 3) transport_march_kernel(const __grid_constant__ StageArgs A)
+template <int NC, bool HAS_BASE>
+__global__ void __launch_bounds__(TM_WPB * 32, NC == 6 ? 3 : 5) transport_march_kernel(const __grid_constant__ StageArgs A)
 {
     const int lane = threadIdx.x & 31;
     const int cb = (blockIdx.x * TM_WPB + (threadIdx.x >> 5)) * TM_OWN; // first owned column
@@ -655,23 +701,25 @@ __global__ void __launch_bounds__(TM_WPB * 32, 3) transport_march_kernel(const _
     // other row goes through, so a cell's result does not depend on where the band boundaries
     // fall (no separately compiled prologue arithmetic); nothing is stored for it.
     double bm[3] = { 0., 0., 0. }, vb[3] = { 0., 0., 0. };
-    TRow X, Y, Z;
-    tm_load_src(A, f, b0 - 1, gi, X);
-    tm_load_src(A, f, b0, gi, Y);
-    X.base[0] = X.base[1] = X.base[2] = X.base[3] = X.base[4] = X.base[5] = 0.;
+    TRow<NC> X, Y, Z;
+    tm_load_src<NC>(A, f, b0 - 1, gi, X);
+    tm_load_src<NC>(A, f, b0, gi, Y);
+#pragma unroll
+    for (int q = 0; q < NC; ++q)
+        X.base[q] = 0.;
     // (the not-stored first step is the loop's first iteration with a run-time predicate, not a
     // separately specialised copy of the step)
     int r = b0 - 1;
 #pragma unroll 1
     for (; r + 2 < b1; r += 3) {
-        tm_step<HAS_BASE>(A, f, r, gi, own && r >= b0, X, Y, Z, bm, vb);
-        tm_step<HAS_BASE>(A, f, r + 1, gi, own, Y, Z, X, bm, vb);
-        tm_step<HAS_BASE>(A, f, r + 2, gi, own, Z, X, Y, bm, vb);
+        tm_step<NC, HAS_BASE>(A, f, r, gi, own && r >= b0, X, Y, Z, bm, vb);
+        tm_step<NC, HAS_BASE>(A, f, r + 1, gi, own, Y, Z, X, bm, vb);
+        tm_step<NC, HAS_BASE>(A, f, r + 2, gi, own, Z, X, Y, bm, vb);
     }
     if (r < b1) {
-        tm_step<HAS_BASE>(A, f, r, gi, own && r >= b0, X, Y, Z, bm, vb);
+        tm_step<NC, HAS_BASE>(A, f, r, gi, own && r >= b0, X, Y, Z, bm, vb);
         if (r + 1 < b1)
-            tm_step<HAS_BASE>(A, f, r + 1, gi, own, Y, Z, X, bm, vb);
+            tm_step<NC, HAS_BASE>(A, f, r + 1, gi, own, Y, Z, X, bm, vb);
     }
 }
 
@@ -685,7 +733,7 @@ int transport_band_rows(int64_t nrows, int64_t ctas_per_band, int64_t slots)
         const int64_t ry = (nrows + nb - 1) / nb;
         if (ry > 2048)
             continue;
-        if (ry < 24)
+        if (ry < 12)
             break;
         const int64_t nbands = (nrows + ry - 1) / ry;
         const int64_t waves = (nbands * ctas_per_band + slots - 1) / slots;
@@ -758,15 +806,21 @@ int nsdg_transport_stage(nsdg_ctx* ctx, int nfields, double* const* src, double*
     // dG2 on grids that do not live in L2: the marching kernel (nsdg_dyn_tuning.transport_march:
     // 1 forces it on any grid, -1 selects the one-thread-per-cell kernel)
     const int tm = d->tune.transport_march;
-    if (d->nc == 6 && tm >= 0 && (tm > 0 || d->nx * d->nyl >= ((int64_t)1 << 20))) {
+    if (d->nc >= 3 && tm >= 0 && (tm > 0 || d->nx * d->nyl >= ((int64_t)1 << 20))) {
         const int64_t nwarps = (d->nx + TM_OWN - 1) / TM_OWN, gx = (nwarps + TM_WPB - 1) / TM_WPB;
-        A.band = transport_band_rows(r1 - r0, gx * nfields, 3 * (int64_t)ctx->sm_count);
+        // resident CTAs per SM: 3 (dG2, 168 registers) / 5 (dG1)
+        A.band = transport_band_rows(r1 - r0, gx * nfields, (d->nc == 6 ? 3 : 5) * (int64_t)ctx->sm_count);
         dim3 mblock(TM_WPB * 32), mgrid((unsigned)gx, (unsigned)((r1 - r0 + A.band - 1) / A.band), (unsigned)nfields);
         nsdg_prof_begin(ctx, NSDG_K_TRANSPORT_MARCH);
-        if (hb)
-            transport_march_kernel<true><<<mgrid, mblock, 0, ctx->stream>>>(A);
+        if (d->nc == 6) {
+            if (hb)
+                transport_march_kernel<6, true><<<mgrid, mblock, 0, ctx->stream>>>(A);
+            else
+                transport_march_kernel<6, false><<<mgrid, mblock, 0, ctx->stream>>>(A);
+        } else if (hb)
+            transport_march_kernel<3, true><<<mgrid, mblock, 0, ctx->stream>>>(A);
         else
-            transport_march_kernel<false><<<mgrid, mblock, 0, ctx->stream>>>(A);
+            transport_march_kernel<3, false><<<mgrid, mblock, 0, ctx->stream>>>(A);
         nsdg_prof_end(ctx);
         NSDG_LAUNCHED(ctx);
         return NSDG_OK;
