@@ -25,3 +25,25 @@ def test_strips_match_single_domain_oracle(world):
                        capture_output=True, text=True, timeout=1200)
     print(r.stdout[-12000:], r.stderr[-3000:])
     assert r.returncode == 0 and "MGPU PASS" in r.stdout
+
+
+@pytest.mark.gpu
+def test_full_size_strips_are_bit_identical_to_the_single_domain():
+    """BASELINE configs[2]/[4] sizes, as a size-independent property: 4096 x 8192 cells on one GPU
+    and cut into two 4096 x 4096 strips (peer-store halo and NCCL halo) give the same bits
+    (tools/strip_digest.py: per-row checksums gathered and hashed; the small cases of
+    mgpu_worker.py tie the single domain to the oracle)."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs at least 2 GPUs")
+    tool = os.path.join(ROOT, "tools", "strip_digest.py")
+    tr = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+          "127.0.0.1", "--master-port", "29617", tool, "8192"]
+    digests = []
+    for cmd in ([sys.executable, tool, "8192"], tr, tr + ["halo_peer=-1"]):
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+        lines = [ln for ln in r.stdout.splitlines() if ln.startswith("strip_digest")]
+        assert r.returncode == 0 and lines, r.stderr[-2000:]
+        print(lines[-1])
+        digests.append(lines[-1].rsplit(" ", 1)[-1])
+    assert len(set(digests)) == 1, digests
