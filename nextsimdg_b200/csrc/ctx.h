@@ -62,6 +62,7 @@ struct nsdg_ctx {
     cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
     int64_t launches = 0;
     int sm_count = 148;
+    bool lring_attr_set = false;
     bool ring_attr_set = false; // dynamic shared-memory limit of the ring kernels raised on this device
     std::string error;
     bool cuda_failed = false; // sticky

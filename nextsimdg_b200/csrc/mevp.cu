@@ -910,15 +910,93 @@ __device__ __forceinline__ void ring_load(const MevpArgs& A, RingSmem<WPB>& R, i
         mbar_arrive(&R.empty[st]);
 }
 
+// ---- per-lane asynchronous copies (RING == 2) ------------------------------------------------
+// The same idea without the copy engine and without any coupling between warps: every lane
+// brings ITS OWN 21 values of the rows ahead into a private shared-memory slot with 8-byte
+// cp.async (LDGSTS: no destination register, so the depth is not bounded by the register file),
+// LR_D rows deep, and reads them back into the row record one step before their use.  A lane
+// only ever reads what it copied itself: cp.async.wait_group orders that, no barrier is needed.
+constexpr int LR_NS = 4, LR_D = LR_NS - 1;
+struct LaneRing {
+    double d[MARCH_WPB][LR_NS][RING_ARR][33]; // [warp][stage][array][lane (+1: right neighbour of lane 31)]
+};
+__device__ __forceinline__ void cpa8(double* dst, const double* src)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(dst)), "l"(__cvta_generic_to_global(src)) : "memory");
+}
+__device__ __forceinline__ void lane_ring_fill(const MevpArgs& A, double (*D)[33], int r, int gi, int gip, int lane, bool valid)
+{
+    if (valid) {
+        const int gr = plane_row(A, r), grp = plane_row(A, r + 1);
+        const int k = gr * A.nx + gi, kp = grp * A.nx + gi;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            cpa8(&D[c][lane], A.S11 + c * A.plane + k);
+            cpa8(&D[3 + c][lane], A.S12 + c * A.plane + k);
+            cpa8(&D[6 + c][lane], A.S22 + c * A.plane + k);
+        }
+#pragma unroll
+        for (int g = 0; g < 4; ++g)
+            cpa8(&D[9 + g][lane], A.pg + g * A.plane + k);
+        cpa8(&D[13][lane], A.u + kp);
+        cpa8(&D[14][lane], A.v + kp);
+        if (lane == 31) {
+            cpa8(&D[13][32], A.u + grp * A.nx + gip);
+            cpa8(&D[14][32], A.v + grp * A.nx + gip);
+        }
+        cpa8(&D[15][lane], A.uo + k);
+        cpa8(&D[16][lane], A.vo + k);
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+            cpa8(&D[17 + q][lane], A.nd + q * A.plane + k);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory"); // (an empty group keeps the count uniform)
+}
+__device__ __forceinline__ void lane_ring_load(const MevpArgs& A, const double (*D)[33], int r, int gi, int lane, MarchRow& Z)
+{
+    asm volatile("cp.async.wait_group %0;" ::"n"(LR_D) : "memory");
+    const int gr = plane_row(A, r);
+    Z.k = gr * A.nx + gi;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        Z.s11[c] = D[c][lane];
+        Z.s12[c] = D[3 + c][lane];
+        Z.s22[c] = D[6 + c][lane];
+    }
+#pragma unroll
+    for (int g = 0; g < 4; ++g)
+        Z.pg[g] = D[9 + g][lane];
+    Z.un = D[13][lane];
+    Z.vn = D[14][lane];
+    Z.unr = Z.vnr = 0.;
+    if (lane == 31) {
+        Z.unr = D[13][32];
+        Z.vnr = D[14][32];
+    }
+    Z.uo = D[15][lane];
+    Z.vo = D[16][lane];
+    Z.cx0 = D[17][lane];
+    Z.cy0 = D[18][lane];
+    Z.mdt = D[19][lane];
+    Z.acd = D[20][lane];
+    Z.act = !dirichlet(A, gi, gr - NSDG_GHOST);
+}
+
 // One step of the march at row ra.  X: row ra-1 (S^{p+1}, P_g, node constants, u^{p+1}; its
 // un/vn/unr/vnr are u^p of node row ra), Y: the loaded data of row ra, Z: target of the loads of
 // row ra+1.  d2p: divergence coefficients of S^{p+2}, cell row ra-2.  own: this lane stores row
 // ra-1.
-template <bool PEER, bool CG, bool RING, int WPB>
+template <bool PEER, bool CG, int RING, int WPB>
 __device__ __forceinline__ void march_step(const MevpArgs& A, int ra, int gi, int gip, int lane, bool own,
     MarchRow& X, MarchRow& Y, MarchRow& Z, double (&d2p)[7], RingSmem<WPB>* R, int s, int nsteps, int c0, int col)
 {
-    if (RING) {
+    if (RING == 2) {
+        // row s + 1 + LR_D of the march goes out to shared memory, row s + 1 comes in from it
+        LaneRing* LR = reinterpret_cast<LaneRing*>(R);
+        const int w = threadIdx.x >> 5;
+        lane_ring_fill(A, LR->d[w][(s + 1 + LR_D) % LR_NS], ra + 1 + LR_D, gi, gip, lane, s + 1 + LR_D <= nsteps);
+        lane_ring_load(A, LR->d[w][(s + 1) % LR_NS], ra + 1, gi, lane, Z);
+    } else if (RING == 1) {
         // warp 0 refills the stage every warp has read in the previous step with the row RING_NS
         // ahead of it, then every warp takes the next row (march row s + 1) from the ring
         if (threadIdx.x < 32 && s + RING_NS <= nsteps) { // warp 0 of the CTA
@@ -985,7 +1063,7 @@ __device__ __forceinline__ void march_step(const MevpArgs& A, int ra, int gi, in
         d2p[c] = hi[c];
 }
 
-template <bool PEER, bool CG, bool RING, int WPB>
+template <bool PEER, bool CG, int RING, int WPB>
 __global__ void __launch_bounds__(WPB * 32, 8 / WPB) mevp_march_kernel(const __grid_constant__ MevpArgs A)
 {
     constexpr int MARCH_WPB = WPB; // warps (28-column blocks) per CTA: 4, or 8 for the ring variant
@@ -997,7 +1075,7 @@ __global__ void __launch_bounds__(WPB * 32, 8 / WPB) mevp_march_kernel(const __g
     const int c0 = blockIdx.x * MARCH_WPB * MARCH_OWN; // first owned column of the CTA
     // this lane's column in the CTA's row segment (ring variant)
     const int col = RingSmem<WPB>::LEFT - MARCH_OFF + (threadIdx.x >> 5) * MARCH_OWN + lane;
-    if (RING) {
+    if (RING == 1) {
         if (threadIdx.x == 0) {
             const int nw = (A.nx + MARCH_OWN - 1) / MARCH_OWN; // warps with columns, over the grid
             const int active = min(MARCH_WPB, nw - (int)blockIdx.x * MARCH_WPB);
@@ -1055,7 +1133,13 @@ __global__ void __launch_bounds__(WPB * 32, 8 / WPB) mevp_march_kernel(const __g
         X.unr = from_right(X.un, ldm<CG>(A.u + g0 * A.nx + gip), lane);
         X.vnr = from_right(X.vn, ldm<CG>(A.v + g0 * A.nx + gip), lane);
     }
-    if (RING) {
+    if (RING == 2) {
+        LaneRing* LR = reinterpret_cast<LaneRing*>(R);
+        const int w = threadIdx.x >> 5;
+        for (int k = 0; k <= LR_D; ++k)
+            lane_ring_fill(A, LR->d[w][k], b0 - 2 + k, gi, gip, lane, k <= nsteps);
+        lane_ring_load(A, LR->d[w][0], b0 - 2, gi, lane, Y);
+    } else if (RING == 1) {
         if (PEER)
             asm volatile("fence.proxy.async;" ::: "memory"); // peer stores seen above -> bulk-copy reads
         if (threadIdx.x < 32) // warp 0: the first RING_NS rows of the march
@@ -1397,13 +1481,27 @@ int nsdg_mevp_pair(nsdg_ctx* ctx, double dt, const double* u, const double* v, d
         dim3 block(MARCH_WPB * 32), grid((unsigned)((nwarps + MARCH_WPB - 1) / MARCH_WPB), (unsigned)((nrows + ry - 1) / ry));
         // shared-memory ring variant (nsdg_dyn_tuning.march_ring; needs an even nx): CTAs of eight
         // warps, one per SM, so that a bulk copy moves 1.9 KB
-        const bool ring = d->tune.march_ring > 0 && d->nx % 16 == 0;
+        const bool ring = d->tune.march_ring == 1 && d->nx % 16 == 0;
+        const bool lring = d->tune.march_ring == 2 && !peer_seq; // per-lane cp.async variant (single launch path)
+        if (lring) {
+            if (!ctx->lring_attr_set) {
+                NSDG_CUDA(ctx, cudaFuncSetAttribute(mevp_march_kernel<false, false, 2, MARCH_WPB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LaneRing)));
+                ctx->lring_attr_set = true;
+            }
+            if (st == ctx->stream) {
+                NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<false, false, 2, MARCH_WPB><<<grid, block, sizeof(LaneRing), st>>>(A)));
+            } else {
+                mevp_march_kernel<false, false, 2, MARCH_WPB><<<grid, block, sizeof(LaneRing), st>>>(A);
+                NSDG_LAUNCHED(ctx);
+            }
+            return NSDG_OK;
+        }
         constexpr int RWPB = 4;
         if (ring) {
             bool& attr_set = ctx->ring_attr_set; // per device: the attribute belongs to the context's GPU
             if (!attr_set) {
-                NSDG_CUDA(ctx, cudaFuncSetAttribute(mevp_march_kernel<false, false, true, RWPB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RingSmem<RWPB>)));
-                NSDG_CUDA(ctx, cudaFuncSetAttribute(mevp_march_kernel<true, true, true, RWPB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RingSmem<RWPB>)));
+                NSDG_CUDA(ctx, cudaFuncSetAttribute(mevp_march_kernel<false, false, 1, RWPB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RingSmem<RWPB>)));
+                NSDG_CUDA(ctx, cudaFuncSetAttribute(mevp_march_kernel<true, true, 1, RWPB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RingSmem<RWPB>)));
                 attr_set = true;
             }
             block = dim3(RWPB * 32);
@@ -1434,20 +1532,20 @@ int nsdg_mevp_pair(nsdg_ctx* ctx, double dt, const double* u, const double* v, d
             A.flag_dn = d->dn.flags;
             A.seq = peer_seq;
             if (ring)
-                NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<true, true, true, RWPB><<<grid, block, sizeof(RingSmem<RWPB>), st>>>(A)));
+                NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<true, true, 1, RWPB><<<grid, block, sizeof(RingSmem<RWPB>), st>>>(A)));
             else
-                NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<true, true, false, MARCH_WPB><<<grid, block, 0, st>>>(A)));
+                NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<true, true, 0, MARCH_WPB><<<grid, block, 0, st>>>(A)));
         } else if (ring) {
             if (st == ctx->stream) {
-                NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<false, false, true, RWPB><<<grid, block, sizeof(RingSmem<RWPB>), st>>>(A)));
+                NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<false, false, 1, RWPB><<<grid, block, sizeof(RingSmem<RWPB>), st>>>(A)));
             } else {
-                mevp_march_kernel<false, false, true, RWPB><<<grid, block, sizeof(RingSmem<RWPB>), st>>>(A);
+                mevp_march_kernel<false, false, 1, RWPB><<<grid, block, sizeof(RingSmem<RWPB>), st>>>(A);
                 NSDG_LAUNCHED(ctx);
             }
         } else if (st == ctx->stream) {
-            NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<false, false, false, MARCH_WPB><<<grid, block, 0, st>>>(A)));
+            NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<false, false, 0, MARCH_WPB><<<grid, block, 0, st>>>(A)));
         } else { /* the per-kernel profiler brackets the compute stream only */
-            mevp_march_kernel<false, false, false, MARCH_WPB><<<grid, block, 0, st>>>(A);
+            mevp_march_kernel<false, false, 0, MARCH_WPB><<<grid, block, 0, st>>>(A);
             NSDG_LAUNCHED(ctx);
         }
         return NSDG_OK;
