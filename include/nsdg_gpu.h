@@ -309,6 +309,25 @@ int nsdg_dyn_upload_forcing_level(nsdg_ctx* ctx, int32_t level, const double* ua
 int nsdg_dyn_blend_forcing(nsdg_ctx* ctx, double w);
 /* sum over this rank's cells of the mean coefficient times cell area (mass diagnostic) */
 int nsdg_dyn_mass(nsdg_ctx* ctx, int32_t field, double* mass);
+/* The same diagnostic for callers that cannot allocate (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Calls no cudaMalloc / cudaFree / allocating library routine and
+ * needs no dynamics state: the caller passes the input and the output,
+ *   mean      DEVICE pointer, ny rows of nx doubles, `pitch` elements from row to row (>= nx):
+ *             e.g. nsdg_dyn_field_ptr(H) + 2 * nx for the interior of a strip, pitch = nx
+ *   mass_out  DEVICE pointer to one double: hx hy sum(mean); written by work enqueued on the
+ *             context's compute stream (the call does not wait: nsdg_synchronize before reading)
+ * Its scratch (one partial sum per row) is a fixed __device__ array inside the library, 8 *
+ * NSDG_NOALLOC_MAX_ROWS bytes on every GPU that loads the library, held until the process exits:
+ * ny > NSDG_NOALLOC_MAX_ROWS fails with NSDG_EINVAL.  Every call on a GPU shares that array, so
+ * calls that OVERLAP on one GPU (other contexts / streams) race; calls on one context are ordered
+ * by its stream.  Nothing in it has to start at zero (each call overwrites the entries it reads).
+ * The result is reproducible bit for bit (fixed summation order), which nsdg_dyn_mass's atomic
+ * accumulation is not; the two agree to rounding.  The first call on each device resolves the
+ * array's device address (cudaGetSymbolAddress): make it outside a stream capture. */
+#define NSDG_NOALLOC_MAX_ROWS 16384
+int nsdg_dyn_mass_noalloc(nsdg_ctx* ctx, const double* mean, int64_t nx, int64_t ny, int64_t pitch,
+    double hx, double hy, double* mass_out);
 /* rows per band the mEVP marching kernel uses for a strip of nrows x nx cells on a GPU with
  * sm_count SMs (strip != 0: part of a strip decomposition, the halo exchange runs beside the
  * interior bands).  Pure host arithmetic (no GPU needed); the environment variable

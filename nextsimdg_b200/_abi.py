@@ -131,6 +131,8 @@ SYMBOLS = {
     "nsdg_dyn_upload_forcing_level": (ctypes.c_int, [_ctx, _i32] + [c_double_p] * 4),
     "nsdg_dyn_blend_forcing": (ctypes.c_int, [_ctx, _dbl]),
     "nsdg_dyn_mass": (ctypes.c_int, [_ctx, _i32, c_double_p]),
+    "nsdg_dyn_mass_noalloc": (ctypes.c_int, [_ctx, ctypes.c_void_p, _i64, _i64, _i64, _dbl, _dbl,
+                                             ctypes.c_void_p]),
     "nsdg_mevp_band_rows": (ctypes.c_int, [_i64, _i64, _i32, _i32]),
     "nsdg_comm_get_unique_id": (ctypes.c_int, [ctypes.c_void_p]),
     "nsdg_comm_init": (ctypes.c_int, [_ctx, ctypes.c_void_p, _i32, _i32]),

@@ -25,6 +25,7 @@ SOURCES = {
     "mevp.cu": [],
     "dyn.cu": [],
     "comm.cu": [],
+    "noalloc.cu": [],
 }
 
 
