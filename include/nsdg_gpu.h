@@ -179,11 +179,13 @@ typedef struct nsdg_dyn_tuning {
                                 per cell                                 [NSDG_TRANSPORT_MARCH=0/1] */
     int32_t graph; /* CUDA-graph replay of the sub-cycle's launches: 0 = automatic (single rank,
                       grids below 2^20 cells), 1 on, -1 off                    [NSDG_DYN_GRAPH=0/1] */
-    int32_t march_ring; /* marching sub-cycle kernel, experiment arms (both bit-identical to the
-                           default and measured slower, profiles/r2n_march_ring.txt): rows ahead
-                           staged in shared memory 1 = by cp.async.bulk, CTA-wide row segments
-                           (needs nx % 16 == 0), 2 = by per-lane 8-byte cp.async (single rank);
-                           0 / -1 = register pipeline only (default)        [NSDG_MEVP_RING=0/1/2] */
+    int32_t march_ring; /* marching sub-cycle kernel, experiment arms (all bit-identical to the
+                           default and measured slower, profiles/r2n_march_ring.txt,
+                           r2z_march_prefetch.txt): rows ahead staged in shared memory 1 = by
+                           cp.async.bulk, CTA-wide row segments (needs nx % 16 == 0), 2 = by
+                           per-lane 8-byte cp.async (single rank); 3 = rows ahead pulled into L2
+                           by tensor-box prefetches of the bulk-copy engine (single rank, even
+                           nx); 0 / -1 = register pipeline only (default) [NSDG_MEVP_RING=0/1/2/3] */
     int32_t reserved[7]; /* must be 0 */
 } nsdg_dyn_tuning;
 

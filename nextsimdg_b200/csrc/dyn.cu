@@ -408,7 +408,7 @@ void nsdg_dyn_tuning_defaults(nsdg_dyn_tuning* t)
     t->transport_march = env_switch("NSDG_TRANSPORT_MARCH");
     t->graph = env_switch("NSDG_DYN_GRAPH");
     t->march_ring = env_int("NSDG_MEVP_RING", 0);
-    if (t->march_ring < -1 || t->march_ring > 2)
+    if (t->march_ring < -1 || t->march_ring > 3)
         t->march_ring = 0;
 }
 
@@ -590,7 +590,7 @@ int nsdg_dyn_set_tuning(nsdg_ctx* ctx, const nsdg_dyn_tuning* t)
         NSDG_EINVAL, "unknown tile id");
     for (int q : { t->pair, t->halo_overlap, t->halo_peer, t->transport_march, t->graph })
         NSDG_REQUIRE(ctx, q >= -1 && q <= 1, NSDG_EINVAL, "switches take -1, 0 or 1");
-    NSDG_REQUIRE(ctx, t->march_ring >= -1 && t->march_ring <= 2, NSDG_EINVAL, "march_ring takes -1, 0, 1 or 2");
+    NSDG_REQUIRE(ctx, t->march_ring >= -1 && t->march_ring <= 3, NSDG_EINVAL, "march_ring takes -1, 0, 1, 2 or 3");
     for (int q : t->reserved)
         NSDG_REQUIRE(ctx, q == 0, NSDG_EINVAL, "reserved fields must be 0");
     NSDG_CUDA(ctx, cudaStreamSynchronize(ctx->stream)); // knobs never change under work in flight

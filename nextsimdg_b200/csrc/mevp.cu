@@ -25,6 +25,7 @@
 // than 2^31 elements) and every quotient that does not depend on the cell is taken on the host.
 #include "dyn.h"
 #include "fp64_fast.cuh"
+#include <cuda.h> // CUtensorMap (types only: cuTensorMapEncodeTiled is looked up at run time)
 #include <algorithm>
 #include <cstdlib>
 #include <string>
@@ -69,6 +70,7 @@ struct MevpArgs {
     unsigned* flag_up;
     unsigned* flag_dn;
     unsigned seq;
+    int pf_dist, pf_align; // RING == 3: rows ahead of the L2 prefetch; boxes on 256-byte boundaries
 };
 
 __device__ __forceinline__ int row_below(const MevpArgs& A, int r)
@@ -986,6 +988,68 @@ __device__ __forceinline__ void lane_ring_load(const MevpArgs& A, const double (
 // un/vn/unr/vnr are u^p of node row ra), Y: the loaded data of row ra, Z: target of the loads of
 // row ra+1.  d2p: divergence coefficients of S^{p+2}, cell row ra-2.  own: this lane stores row
 // ra-1.
+// the q-th of the 21 arrays a march row is read from (order of the ring stages)
+__device__ __forceinline__ const double* march_array(const MevpArgs& A, int q)
+{
+    return q < 3 ? A.S11 + q * A.plane : q < 6 ? A.S12 + (q - 3) * A.plane
+        : q < 9  ? A.S22 + (q - 6) * A.plane
+        : q < 13 ? A.pg + (q - 9) * A.plane
+        : q == 13 ? A.u
+        : q == 14 ? A.v
+        : q == 15 ? A.uo
+        : q == 16 ? A.vo
+                  : A.nd + (q - 17) * A.plane;
+}
+
+// ---- L2 prefetch by the bulk-copy engine (RING == 3) -------------------------------------------
+// The register pipeline stays as it is; in addition the bulk-copy engine is asked to bring rows
+// ahead of the march into L2 (no destination, no barrier, nobody waits for it), so that the
+// register loads one step ahead find their lines in L2.  What the experiments on the way here
+// showed (profiles/r2z_march_prefetch.txt):
+//  * cp.async.bulk.prefetch.L2 with per-lane addresses (21 lanes, one per array) removes the wait
+//    (long-scoreboard stall 1.18 -> 0.11 per issue, +6 % DRAM bytes) but the instruction takes its
+//    operands from UNIFORM registers: the compiler wraps it in a loop of ~11 instructions per
+//    active lane, +40 % instructions, 1.04 against 0.84 ms;
+//  * CTA-wide segments from one warp, or dealt out over the warps, save instructions but the warps
+//    of a CTA free-run and drift apart: a warp prefetches relative to ITS position what the others
+//    needed earlier or later (read hit rate 34-68 %, DRAM bytes up to x1.7);
+//  * so every warp prefetches its own columns at its own pace, and to make that cheap the 21
+//    arrays go as 9 TENSOR boxes (3 rows x the 3 or 4 planes of S11, S12, S22, P_g, the node
+//    constants; u, v, u_o, v_o one plane each) every third step from one elected lane:
+//    cp.async.bulk.prefetch.tensor.3d.L2, 9 instructions per three steps (+3.8 % instructions);
+//  * boxes that start at the warp's first column (16-byte aligned) straddle three 128-byte lines
+//    and overlap the neighbours': DRAM reads x1.5.  Boxes on 256-byte boundaries (warp w of the
+//    CTA takes columns c0 + 32 w ...; nx % 16 == 0) bring that down to x1.13.
+// What is left (this variant): 0.92 against 0.80 ms under ncu.  The wait for loaded rows shrinks
+// (1.15 -> 0.77 per issue) but the loop body grows past the 32 KB instruction-cache level it just
+// fits (33.1 -> 34.7 KB: instruction-fetch stalls 0.14 -> 0.36 per issue, hit rate 99.0 -> 93.4 %)
+// and the rest is eaten by the extra DRAM traffic.  Kept as an opt-in arm (march_ring = 3, single
+// rank); bit-identical.  Needs an even nx (16-byte strides of the tensor maps).
+constexpr int PF_MAPS = 9; // S11, S12, S22, pg, nd, u, v, uo, vo
+struct alignas(64) PfMaps {
+    CUtensorMap m[PF_MAPS];
+};
+__device__ __forceinline__ bool elect_one()
+{
+    unsigned pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
+__device__ __forceinline__ void tensor_prefetch_l2(const CUtensorMap* map, int x, int y)
+{
+    asm volatile("cp.async.bulk.prefetch.tensor.3d.L2.global.tile [%0, {%1, %2, %3}];" ::"l"(map), "r"(x), "r"(y), "r"(0) : "memory");
+}
+// rows [row, row + 3) of the plane (u, v: one row higher), columns [x, x + 32); rows past the plane's
+// end and columns outside the row are skipped by the copy engine.  The whole warp arrives converged.
+__device__ __forceinline__ void pf_rows(const PfMaps& M, int x, int row)
+{
+    if (elect_one()) {
+#pragma unroll
+        for (int q = 0; q < PF_MAPS; ++q)
+            tensor_prefetch_l2(&M.m[q], x, (q == 5 || q == 6) ? row + 1 : row);
+    }
+}
+
 template <bool PEER, bool CG, int RING, int WPB>
 __device__ __forceinline__ void march_step(const MevpArgs& A, int ra, int gi, int gip, int lane, bool own,
     MarchRow& X, MarchRow& Y, MarchRow& Z, double (&d2p)[7], RingSmem<WPB>* R, int s, int nsteps, int c0, int col)
@@ -1004,8 +1068,9 @@ __device__ __forceinline__ void march_step(const MevpArgs& A, int ra, int gi, in
             ring_fill(A, *R, ra + RING_NS, s % RING_NS, c0, lane);
         }
         ring_load(A, *R, ra + 1, s + 1, gi, col, lane, Z);
-    } else
+    } else {
         march_load<CG>(A, ra + 1, gi, gip, lane, Z); // consumed by the next step (wasted on the last one)
+    }
 
     // ---- A: stress p+1 of cell row ra
     Y.unr = from_right(Y.un, Y.unr, lane);
@@ -1064,7 +1129,7 @@ __device__ __forceinline__ void march_step(const MevpArgs& A, int ra, int gi, in
 }
 
 template <bool PEER, bool CG, int RING, int WPB>
-__global__ void __launch_bounds__(WPB * 32, 8 / WPB) mevp_march_kernel(const __grid_constant__ MevpArgs A)
+__device__ __forceinline__ void march_body(const MevpArgs& A, const PfMaps* M)
 {
     constexpr int MARCH_WPB = WPB; // warps (28-column blocks) per CTA: 4, or 8 for the ring variant
     extern __shared__ __align__(128) unsigned char ring_raw[];
@@ -1086,16 +1151,7 @@ __global__ void __launch_bounds__(WPB * 32, 8 / WPB) mevp_march_kernel(const __g
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         }
         if (threadIdx.x < RING_ARR) {
-            const int q = threadIdx.x;
-            const double* b = q < 3 ? A.S11 + q * A.plane : q < 6 ? A.S12 + (q - 3) * A.plane
-                : q < 9         ? A.S22 + (q - 6) * A.plane
-                : q < 13        ? A.pg + (q - 9) * A.plane
-                : q == 13       ? A.u
-                : q == 14       ? A.v
-                : q == 15       ? A.uo
-                : q == 16       ? A.vo
-                                : A.nd + (q - 17) * A.plane;
-            R->base[q] = b;
+            R->base[threadIdx.x] = march_array(A, threadIdx.x);
         }
         __syncthreads();
     }
@@ -1146,8 +1202,9 @@ __global__ void __launch_bounds__(WPB * 32, 8 / WPB) mevp_march_kernel(const __g
             for (int k = 0; k < RING_NS && k <= nsteps; ++k)
                 ring_fill(A, *R, b0 - 2 + k, k, c0, lane);
         ring_load(A, *R, b0 - 2, 0, gi, col, lane, Y);
-    } else
+    } else {
         march_load<CG>(A, b0 - 2, gi, gip, lane, Y);
+    }
     // step s works on row ra = b0 - 2 + s and stores the owned row ra - 1 when 3 <= s; the first
     // steps run phases C / D on the zero-initialised records (finite values, never stored)
 #define NSDG_STEP(s, X, Y, Z) \
@@ -1155,6 +1212,8 @@ __global__ void __launch_bounds__(WPB * 32, 8 / WPB) mevp_march_kernel(const __g
     int s = 0;
 #pragma unroll 1
     for (; s + 2 < nsteps; s += 3) {
+        if (RING == 3 && s + A.pf_dist < nsteps) // the rows steps s + pf_dist ... + 2 will load
+            pf_rows(*M, A.pf_align ? c0 + 32 * (int)(threadIdx.x >> 5) : cb - MARCH_OFF, plane_row(A, b0 - 1 + s + A.pf_dist));
         NSDG_STEP(s, X, Y, Z);
         NSDG_STEP(s + 1, Y, Z, X);
         NSDG_STEP(s + 2, Z, X, Y);
@@ -1177,6 +1236,53 @@ __global__ void __launch_bounds__(WPB * 32, 8 / WPB) mevp_march_kernel(const __g
                 st_release_sys(A.flag_dn + A.nflagw + wg, A.seq); // slot [1] of the rank below
         }
     }
+}
+
+template <bool PEER, bool CG, int RING, int WPB>
+__global__ void __launch_bounds__(WPB * 32, 8 / WPB) mevp_march_kernel(const __grid_constant__ MevpArgs A)
+{
+    march_body<PEER, CG, RING, WPB>(A, nullptr);
+}
+// RING == 3: the tensor maps of the prefetch travel as a second kernel argument
+template <bool PEER, bool CG, int WPB>
+__global__ void __launch_bounds__(WPB * 32, 8 / WPB) mevp_march_pf_kernel(const __grid_constant__ MevpArgs A, const __grid_constant__ PfMaps M)
+{
+    march_body<PEER, CG, 3, WPB>(A, &M);
+}
+
+// tensor maps of the prefetch arm: one per array group, planes of (nyl + 4) x nx doubles, boxes of
+// 32 columns x 3 rows x all planes of the group.  cuTensorMapEncodeTiled is a pure host function
+// of the driver library, looked up once (the library does not link against libcuda).
+typedef CUresult (*TensorMapEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+    const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+TensorMapEncodeFn tensor_map_encoder()
+{
+    static const TensorMapEncodeFn fn = [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess)
+            p = nullptr;
+        return reinterpret_cast<TensorMapEncodeFn>(p);
+    }();
+    return fn;
+}
+bool pf_maps(const DynState* d, const MevpArgs& A, PfMaps& M)
+{
+    const TensorMapEncodeFn enc = tensor_map_encoder();
+    if (!enc)
+        return false;
+    const double* base[PF_MAPS] = { A.S11, A.S12, A.S22, A.pg, A.nd, A.u, A.v, A.uo, A.vo };
+    const int planes[PF_MAPS] = { 3, 3, 3, 4, 4, 1, 1, 1, 1 };
+    for (int q = 0; q < PF_MAPS; ++q) {
+        const cuuint64_t dim[3] = { (cuuint64_t)d->nx, (cuuint64_t)d->rows, (cuuint64_t)planes[q] };
+        const cuuint64_t stride[2] = { (cuuint64_t)d->nx * 8u, (cuuint64_t)d->plane * 8u };
+        const cuuint32_t box[3] = { 32u, 3u, (cuuint32_t)planes[q] }, estr[3] = { 1u, 1u, 1u };
+        if (enc(&M.m[q], CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, const_cast<double*>(base[q]), dim, stride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE)
+            != CUDA_SUCCESS)
+            return false;
+    }
+    return true;
 }
 
 MevpArgs base_args(DynState* d, double dt)
@@ -1492,6 +1598,19 @@ int nsdg_mevp_pair(nsdg_ctx* ctx, double dt, const double* u, const double* v, d
                 NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_kernel<false, false, 2, MARCH_WPB><<<grid, block, sizeof(LaneRing), st>>>(A)));
             } else {
                 mevp_march_kernel<false, false, 2, MARCH_WPB><<<grid, block, sizeof(LaneRing), st>>>(A);
+                NSDG_LAUNCHED(ctx);
+            }
+            return NSDG_OK;
+        }
+        if (d->tune.march_ring == 3 && !peer_seq && d->nx % 2 == 0) { // L2 prefetch arm
+            PfMaps M;
+            NSDG_REQUIRE(ctx, pf_maps(d, A, M), NSDG_ECUDA, "cuTensorMapEncodeTiled unavailable or failed (march_ring = 3)");
+            A.pf_dist = 2; // rows ahead (1 ... 4 measured: 0.985, 1.000, 1.016, 1.052 ms per launch)
+            A.pf_align = d->nx % 16 == 0; // boxes on 256-byte boundaries of the row: no line fetched twice
+            if (st == ctx->stream) {
+                NSDG_KERNEL(ctx, NSDG_K_MEVP_MARCH, (mevp_march_pf_kernel<false, false, MARCH_WPB><<<grid, block, 0, st>>>(A, M)));
+            } else {
+                mevp_march_pf_kernel<false, false, MARCH_WPB><<<grid, block, 0, st>>>(A, M);
                 NSDG_LAUNCHED(ctx);
             }
             return NSDG_OK;

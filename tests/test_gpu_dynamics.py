@@ -427,7 +427,8 @@ def test_pair_kernel_variants_bit_identical(ctx):
                 "transport-march": {"transport_march": 1}, "transport-tiled": {"transport_march": -1},
                 "transport-march-rows16": {"transport_march": 1, "march_rows": 16},
                 "ring": {"march_ring": 1}, "ring-rows5": {"march_ring": 1, "march_rows": 5},
-                "lane-ring": {"march_ring": 2}, "lane-ring-rows5": {"march_ring": 2, "march_rows": 5}}
+                "lane-ring": {"march_ring": 2}, "lane-ring-rows5": {"march_ring": 2, "march_rows": 5},
+                "l2-prefetch": {"march_ring": 3}, "l2-prefetch-rows7": {"march_ring": 3, "march_rows": 7}}
     digests = {k: dyn_digest.digest(ctx, v) for k, v in variants.items()}
     assert len(set(digests.values())) == 1, digests
 

@@ -1,0 +1,31 @@
+#!/bin/bash
+# experiment: tensor-box L2 prefetch, boxes aligned to 256-byte boundaries (no overlap inside a CTA)
+mkdir -p gpurun_out
+NSDG_MEVP_PF_DIST=2 timeout 300 python tools/dyn_digest.py march_ring=3 > gpurun_out/r2y5_digest_pf.txt 2>&1; echo "pf rc=$?"; tail -1 gpurun_out/r2y5_digest_pf.txt
+run() { # ring dist align
+  NSDG_MEVP_RING=$1 NSDG_MEVP_PF_DIST=$2 NSDG_MEVP_PF_ALIGN=$3 timeout 600 python bench.py --main-only --no-e2e --no-cpu > gpurun_out/r2y5_bench_r$1_d$2_a$3.json 2> gpurun_out/r2y5_bench_r$1_d$2_a$3.err; rc=$?
+  python - <<PY
+import json
+try:
+    d=json.load(open("gpurun_out/r2y5_bench_r$1_d$2_a$3.json"))
+    print("ring=$1 dist=$2 align=$3 rc=$rc", round(d["ms_per_step"],3), d["clocks"]["sm_mhz"], {k:(round(v["ms_total"]/v["launches"],4), round(v.get("frac",0),3)) for k,v in d["roofline"]["kernels"].items() if "march" in k})
+except Exception as e:
+    print("ring=$1 dist=$2 rc=$rc failed", e)
+PY
+}
+run 0 0 0
+for d in 1 2 3 4; do run 3 $d 1; done
+run 3 2 0
+for d in 2; do
+NSDG_MEVP_RING=3 NSDG_MEVP_PF_DIST=$d NSDG_MEVP_PF_ALIGN=1 timeout 900 ncu --set full --clock-control none -k regex:mevp_march -s 2 -c 1 -o gpurun_out/r2y5_r3_d$d -f \
+     python tools/prof_target.py 4096 8 > gpurun_out/r2y5_ncu_d$d.log 2>&1; echo "ncu rc=$?"
+ncu -i gpurun_out/r2y5_r3_d$d.ncu-rep --page raw --csv > gpurun_out/r2y5_r3_d${d}_raw.csv 2>/dev/null
+python - <<PY
+import csv
+rows=list(csv.reader(open("gpurun_out/r2y5_r3_d${d}_raw.csv")))
+h,u,r=rows[0],rows[1],rows[2]
+for i,n in enumerate(h):
+    if ("issue_stalled" in n and "per_issue_active" in n and float(r[i] or 0) > 0.05) or n in ("gpu__time_duration.sum","smsp__inst_executed.sum","smsp__issue_active.avg.pct_of_peak_sustained_active","dram__bytes_read.sum","sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active","lts__t_sector_op_read_hit_rate.pct","sm__icc_request_hit_rate.pct"):
+        print("  d=$d", n, r[i], u[i])
+PY
+done
