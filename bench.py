@@ -851,8 +851,10 @@ def measure_cone(args, env):
     sampler = ClockSampler(env.local, rank == 0).start()
     l0 = ctx.launches
     ctx.timer_start()
+    t_host = time.perf_counter()
     for _ in range(steps):
         dyn.transport_step(dt, "H")
+    t_host = time.perf_counter() - t_host  # the host's share: enqueueing only (the queue never fills)
     ms = ctx.timer_stop()
     launches = ctx.launches - l0
     env.barrier()
@@ -893,7 +895,10 @@ def measure_cone(args, env):
         kname = max(prof.items(), key=lambda kv: kv[1][0])[0]
         ktot, kcnt = prof[kname]
         kavg = ktot / kcnt
-        kbytes = CONE_BYTES * n / 2.0  # two stage launches per step
+        # default: both Heun stages in ONE launch (transport_heun_march_kernel): phi in, u, v, phi out
+        # = 8 doubles per cell are all it has to move; with transport_fused = -1 two stage launches
+        fused = kcnt <= 50
+        kbytes = 8 * 8 * n if fused else CONE_BYTES * n / 2.0
         achieved = kbytes / (kavg * 1e-3) / 1e9
         cpu = None
         if world == 1 and not args.no_cpu:
@@ -911,12 +916,17 @@ def measure_cone(args, env):
                 "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": cone_config(world),
                 "clocks": clocks, "e2e": e2e,
                 "gpu_launches": int(launches), "mass_drift_rel": drift,
-                "launch_mode": "CUDA-graph replay of the step's two stage launches" if dyn.get_tuning().graph >= 0 else "plain launches",
+                "launch_mode": "one plain launch per step (both Heun stages fused)" if fused and dyn.get_tuning().graph <= 0
+                else ("CUDA-graph replay of the step's " + ("one fused two-stage launch" if fused else "two stage launches"))
+                if dyn.get_tuning().graph >= 0 else "plain launches",
+                "host_enqueue_us_per_step": t_host / steps * 1e6,
                 "roofline": {"bound": "hbm", "kernel": kname, "achieved": achieved,
                              "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "peak_source": peak_src, "traffic": None,
                              "algorithmic_bytes_per_launch": kbytes,
-                             "units_per_launch": f"{n} cells x {CONE_BYTES}/2 B (one of two RK stages)",
+                             "units_per_launch": (f"{n} cells x 64 B (phi in, u, v, phi out: both Heun stages in one launch; "
+                                                  f"SURVEY.md 8d counts {CONE_BYTES} B per cell and step for stage-by-stage passes)")
+                             if fused else f"{n} cells x {CONE_BYTES}/2 B (one of two RK stages)",
                              "avg_launch_ms": kavg, "launches": kcnt,
                              "whole_step": {"bytes_per_cell": CONE_BYTES,
                                             "achieved": CONE_BYTES * n * steps / (ms * 1e-3) / 1e9,

@@ -186,7 +186,11 @@ typedef struct nsdg_dyn_tuning {
                            per-lane 8-byte cp.async (single rank); 3 = rows ahead pulled into L2
                            by tensor-box prefetches of the bulk-copy engine (single rank, even
                            nx); 0 / -1 = register pipeline only (default) [NSDG_MEVP_RING=0/1/2/3] */
-    int32_t reserved[7]; /* must be 0 */
+    int32_t transport_fused; /* dG1 + Heun on a single rank without limiter: both Runge-Kutta
+                                stages in one launch (transport_heun_march_kernel; the tracer and
+                                its stage buffer swap roles, so nsdg_dyn_field_ptr(H / A) changes
+                                with every step): 0/1 on, -1 off          [NSDG_TRANSPORT_FUSED=0/1] */
+    int32_t reserved[6]; /* must be 0 */
 } nsdg_dyn_tuning;
 
 /* ---- context ---- */
@@ -272,7 +276,10 @@ int nsdg_dyn_download_rows(nsdg_ctx* ctx, int32_t field, int64_t row0, int64_t n
 int nsdg_dyn_field_ncomp(const nsdg_ctx* ctx, int32_t field);
 /* device pointer of component 0, row 0 of the padded array: ny_local+4 rows, of which rows
  * 0,1 and ny_local+2, ny_local+3 are ghost rows of the strip decomposition and rows
- * 2..ny_local+1 the interior; pitch_elems = nx, comp_stride = (ny_local+4)*nx */
+ * 2..ny_local+1 the interior; pitch_elems = nx, comp_stride = (ny_local+4)*nx.  The value is valid
+ * until the next stepping call: U, V and the stress alternate between two buffers in the
+ * sub-cycle, H and A in fused dG1 transport steps (nsdg_dyn_tuning.transport_fused), the forcing
+ * fields in deferred host steps. */
 int nsdg_dyn_field_ptr(nsdg_ctx* ctx, int32_t field, void** device_ptr);
 /* advance tracer `field` (NSDG_DF_H or NSDG_DF_A) by dt with the current U,V */
 int nsdg_transport_step(nsdg_ctx* ctx, int32_t field, double dt);

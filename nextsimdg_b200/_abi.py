@@ -68,7 +68,7 @@ class DynTuning(ctypes.Structure):
     """nsdg_dyn_tuning: 0 = default in every field (include/nsdg_gpu.h)."""
     _fields_ = [(n, ctypes.c_int32) for n in (
         "march_rows", "pair", "halo_overlap", "halo_peer", "pair_tile", "fused_tile",
-        "transport_march", "graph", "march_ring")] + [("reserved", ctypes.c_int32 * 7)]
+        "transport_march", "graph", "march_ring", "transport_fused")] + [("reserved", ctypes.c_int32 * 6)]
 
     PAIR_TILES = ("16x16", "32x8", "32x16", "16x16m3", "16x8", "16x12")
     FUSED_TILES = ("32x8", "64x4", "32x16", "64x8", "16x16")

@@ -103,14 +103,31 @@ void append(PlaneSet& ps, DynState* d, double* base, int ncomp)
         ps.p[ps.n++] = base + (size_t)c * d->plane;
 }
 
-// one RK time step for nfields tracers (phi[f] updated in place)
-int transport_fields(nsdg_ctx* ctx, int nfields, double** phi, double** s1, double** s2,
+// dG1 + Heun on a single rank, no limiter between the stages: the whole step is one launch
+bool heun_fused(nsdg_ctx* ctx)
+{
+    const DynState* d = ctx->dyn;
+    return d->rk == 2 && d->nc == 3 && !nsdg_comm_active(ctx) && !d->cfg.limiter && d->tune.transport_fused >= 0;
+}
+
+// one RK time step for the nfields tracers fld[0..nfields) (d->f[fld[f]] advanced; s1 = the
+// stage-1 slots d->stage1, which trade places with the tracers in the fused Heun step)
+int transport_fields(nsdg_ctx* ctx, int nfields, const int* fld, double** s1, double** s2,
     const double* lo, const double* hi, double dt)
 {
     DynState* d = ctx->dyn;
     const bool multi = nsdg_comm_active(ctx);
     const int64_t r0 = NSDG_GHOST, r1 = NSDG_GHOST + d->nyl;
     int rc;
+    double* phi[2] = { d->f[fld[0]], nfields > 1 ? d->f[fld[1]] : nullptr };
+    // both stages in one launch, the result lands in the stage buffer and the two trade places
+    if (heun_fused(ctx)) {
+        if ((rc = nsdg_transport_heun(ctx, nfields, phi, s1, dt, r0, r1)))
+            return rc;
+        for (int f = 0; f < nfields; ++f)
+            std::swap(d->f[fld[f]], s1[f]);
+        return NSDG_OK;
+    }
     auto halo = [&](double** arr) -> int {
         if (!multi)
             return NSDG_OK;
@@ -332,11 +349,14 @@ template <class Body> int graphed(nsdg_ctx* ctx, int kind, int field, double dt,
         return body();
     uint64_t dtbits;
     memcpy(&dtbits, &dt, 8);
-    const uint64_t key[7] = { (uint64_t)kind, (uint64_t)field, (uint64_t)nsub, dtbits,
+    const uint64_t key[11] = { (uint64_t)kind, (uint64_t)field, (uint64_t)nsub, dtbits,
         (uint64_t)(uintptr_t)d->f[NSDG_DF_U], (uint64_t)(uintptr_t)d->f[NSDG_DF_S11],
         // the forcing buffers swap with their alternates in deferred host steps
         (uint64_t)(uintptr_t)d->f[NSDG_DF_UATM] ^ ((uint64_t)(uintptr_t)d->f[NSDG_DF_VATM] << 1)
-            ^ ((uint64_t)(uintptr_t)d->f[NSDG_DF_UOCN] << 2) ^ ((uint64_t)(uintptr_t)d->f[NSDG_DF_VOCN] << 3) };
+            ^ ((uint64_t)(uintptr_t)d->f[NSDG_DF_UOCN] << 2) ^ ((uint64_t)(uintptr_t)d->f[NSDG_DF_VOCN] << 3),
+        // the tracers swap with their stage buffers in fused Heun steps
+        (uint64_t)(uintptr_t)d->f[NSDG_DF_H], (uint64_t)(uintptr_t)d->f[NSDG_DF_A], (uint64_t)(uintptr_t)d->stage1[0],
+        (uint64_t)(uintptr_t)d->stage1[1] };
     auto roles = [&](double** r) {
         r[0] = d->f[NSDG_DF_U];
         r[1] = d->f[NSDG_DF_V];
@@ -348,6 +368,10 @@ template <class Body> int graphed(nsdg_ctx* ctx, int kind, int field, double dt,
         r[7] = d->s2[0];
         r[8] = d->s2[1];
         r[9] = d->s2[2];
+        r[10] = d->f[NSDG_DF_H];
+        r[11] = d->f[NSDG_DF_A];
+        r[12] = d->stage1[0];
+        r[13] = d->stage1[1];
     };
     for (auto& g : d->graphs)
         if (!memcmp(g.key, key, sizeof key)) {
@@ -363,6 +387,10 @@ template <class Body> int graphed(nsdg_ctx* ctx, int kind, int field, double dt,
             d->s2[0] = g.after[7];
             d->s2[1] = g.after[8];
             d->s2[2] = g.after[9];
+            d->f[NSDG_DF_H] = g.after[10];
+            d->f[NSDG_DF_A] = g.after[11];
+            d->stage1[0] = g.after[12];
+            d->stage1[1] = g.after[13];
             return NSDG_OK;
         }
     const int64_t l0 = ctx->launches;
@@ -407,6 +435,7 @@ void nsdg_dyn_tuning_defaults(nsdg_dyn_tuning* t)
     t->fused_tile = env_tile("NSDG_FUSED_TILE", fused_tiles, 5);
     t->transport_march = env_switch("NSDG_TRANSPORT_MARCH");
     t->graph = env_switch("NSDG_DYN_GRAPH");
+    t->transport_fused = env_switch("NSDG_TRANSPORT_FUSED");
     t->march_ring = env_int("NSDG_MEVP_RING", 0);
     if (t->march_ring < -1 || t->march_ring > 3)
         t->march_ring = 0;
@@ -588,7 +617,7 @@ int nsdg_dyn_set_tuning(nsdg_ctx* ctx, const nsdg_dyn_tuning* t)
     NSDG_REQUIRE(ctx, t->march_rows >= -1 && t->march_rows <= 4096, NSDG_EINVAL, "march_rows in -1..4096");
     NSDG_REQUIRE(ctx, t->pair_tile >= 0 && t->pair_tile <= 5 && t->fused_tile >= 0 && t->fused_tile <= 4,
         NSDG_EINVAL, "unknown tile id");
-    for (int q : { t->pair, t->halo_overlap, t->halo_peer, t->transport_march, t->graph })
+    for (int q : { t->pair, t->halo_overlap, t->halo_peer, t->transport_march, t->graph, t->transport_fused })
         NSDG_REQUIRE(ctx, q >= -1 && q <= 1, NSDG_EINVAL, "switches take -1, 0 or 1");
     NSDG_REQUIRE(ctx, t->march_ring >= -1 && t->march_ring <= 3, NSDG_EINVAL, "march_ring takes -1, 0, 1, 2 or 3");
     for (int q : t->reserved)
@@ -706,13 +735,14 @@ int nsdg_transport_step(nsdg_ctx* ctx, int32_t field, double dt)
     NSDG_REQUIRE(ctx, d, NSDG_ESTATE, "nsdg_dyn_init has not been called");
     NSDG_REQUIRE(ctx, field == NSDG_DF_H || field == NSDG_DF_A, NSDG_EINVAL,
         "only the tracers H and A can be transported");
-    return graphed(ctx, 1, field, dt, 0, [&]() {
-        double* phi[1] = { d->f[field] };
-        double* s1[1] = { d->stage1[0] };
-        double* s2[1] = { d->stage2[0] };
+    auto body = [&]() {
+        const int fld[1] = { field };
         const double lo[1] = { 0. }, hi[1] = { field == NSDG_DF_A ? 1. : 1e300 };
-        return transport_fields(ctx, 1, phi, s1, s2, lo, hi, dt);
-    });
+        return transport_fields(ctx, 1, fld, d->stage1, d->stage2, lo, hi, dt);
+    };
+    if (heun_fused(ctx) && d->tune.graph <= 0) // a single launch: replaying a graph of it only costs host time
+        return body();
+    return graphed(ctx, 1, field, dt, 0, body);
 }
 
 int nsdg_transport_step_HA(nsdg_ctx* ctx, double dt)
@@ -720,11 +750,14 @@ int nsdg_transport_step_HA(nsdg_ctx* ctx, double dt)
     NSDG_ENTER(ctx);
     DynState* d = ctx->dyn;
     NSDG_REQUIRE(ctx, d, NSDG_ESTATE, "nsdg_dyn_init has not been called");
-    return graphed(ctx, 0, 0, dt, 0, [&]() {
-        double* phi[2] = { d->f[NSDG_DF_H], d->f[NSDG_DF_A] };
+    auto body = [&]() {
+        const int fld[2] = { NSDG_DF_H, NSDG_DF_A };
         const double lo[2] = { 0., 0. }, hi[2] = { 1e300, 1. };
-        return transport_fields(ctx, 2, phi, d->stage1, d->stage2, lo, hi, dt);
-    });
+        return transport_fields(ctx, 2, fld, d->stage1, d->stage2, lo, hi, dt);
+    };
+    if (heun_fused(ctx) && d->tune.graph <= 0)
+        return body();
+    return graphed(ctx, 0, 0, dt, 0, body);
 }
 
 int nsdg_mevp_step(nsdg_ctx* ctx, double dt, int32_t nsub)

@@ -73,10 +73,10 @@ struct DynState {
     // CUDA-graph replay of the launch sequences of one step (single rank; dyn.cu): on small grids
     // a step is launch bound (100 sub-iterations = 50 pair launches of a few microseconds)
     struct Graph {
-        uint64_t key[7];
+        uint64_t key[11];
         cudaGraphExec_t exec;
         int64_t launches; // kernels in the graph (nsdg_launch_count keeps counting)
-        double* after[12]; // f[U], f[V], u2, v2, f[S11..S22], s2[0..2], pad: buffer roles after the body
+        double* after[14]; // f[U], f[V], u2, v2, f[S11..S22], s2[0..2], f[H], f[A], stage1[0..1]: buffer roles after the body
     };
     std::vector<Graph> graphs;
 };
@@ -98,6 +98,8 @@ struct HaloSpec {
 // dst = a*base + b*(src + dt*L(src)) for nfields tracers sharing the velocity; rows [r0,r1)
 int nsdg_transport_stage(nsdg_ctx* ctx, int nfields, double* const* src, double* const* base,
     double* const* dst, double a, double b, double dt, int64_t r0, int64_t r1);
+// dG1 + Heun, both stages in one launch: dst = Heun step of src (dst != src); single rank only
+int nsdg_transport_heun(nsdg_ctx* ctx, int nfields, double* const* src, double* const* dst, double dt, int64_t r0, int64_t r1);
 int nsdg_transport_limit(nsdg_ctx* ctx, double* phi, double lo, double hi);
 
 // mevp.cu -----------------------------------------------------------------------------------

@@ -723,6 +723,140 @@ __global__ void __launch_bounds__(TM_WPB * 32, NC == 6 ? 3 : 5) transport_march_
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// dG1, Heun: BOTH Runge-Kutta stages in one launch (temporal blocking, like the sub-cycle's pair
+// kernel).  Step r of the march runs stage 1 on cell row r in lanes 1..30 (k1 = phi + dt L(phi),
+// kept in registers, never stored) and stage 2 on row r-1 in the owned lanes 2..29
+// (phi' = 1/2 phi + 1/2 (k1 + dt L(k1))), whose neighbours are k1 of rows r-2 (through the kept
+// bottom flux), r-1 and r and of the lanes next door.  The velocity does not change between the
+// stages, so the edge velocities of a row are computed once and kept for its second stage.
+// phi crosses HBM / L2 once per STEP instead of twice per stage-pair plus the k1 round trip
+// (3 reads + 2 writes of every coefficient become 1 + 1), one launch instead of two; the price is
+// stage 1 on a 1-column / 1-row halo (30/28 in x, 3 extra march steps per band).  Same device
+// functions, same operand order as the stage kernels: bit-identical to two transport_march /
+// transport_stage launches.  The result cannot go back in place (neighbouring warps and bands
+// still read phi): it is written to the stage buffer and the host swaps the two pointers.
+// Single rank, limiter off.
+struct HRow {
+    double c[3]; // phi of cell row r
+    double u, v; // velocity at node row r, own column
+    int k;
+};
+__device__ __forceinline__ void th_load(const StageArgs& A, int f, int r, int gi, HRow& R)
+{
+    const int k = t_plane_row(A, r) * A.nx + gi;
+    R.k = k;
+#pragma unroll
+    for (int q = 0; q < 3; ++q)
+        R.c[q] = __ldg(A.src[f] + q * A.plane + k);
+    R.u = __ldg(A.u + k);
+    R.v = __ldg(A.v + k);
+}
+struct HKeep { // what stage 2 of row r-1 needs from the steps before
+    double k0[3]; // k1 of row r-1
+    double pc[3]; // phi of row r-1 (the RK base)
+    double uL[3], uR[3], vB[3], vT[3]; // edge velocities of row r-1
+    double bm1[2], bm2[2]; // flux through the bottom edge of row r (stage 1) / row r-1 (stage 2)
+    double vb[3]; // stage 1: the previous row's vT
+    int pk; // plane index of (row r-1, own column)
+};
+__device__ __forceinline__ void th_step(const StageArgs& A, int f, int r, int gi, bool store, HRow& X, HRow& Y, HRow& Z, HKeep& K)
+{
+    th_load(A, f, r + 2, gi, Z);
+    EdgeVel V;
+    {
+        const double u10 = __shfl_down_sync(0xffffffffu, X.u, 1), u11 = __shfl_down_sync(0xffffffffu, Y.u, 1);
+        const double v10 = __shfl_down_sync(0xffffffffu, X.v, 1), v11 = __shfl_down_sync(0xffffffffu, Y.v, 1);
+        edge_velocities<2>(A, X.u, u10, Y.u, u11, X.v, v10, Y.v, v11, V);
+#pragma unroll
+        for (int q = 0; q < 3; ++q)
+            V.vB[q] = K.vb[q];
+    }
+    double k1[3];
+    { // ---- stage 1 on row r (as tm_step<3, false>)
+        Traces1 T, TY;
+        dg1_traces(X.c, T);
+        dg1_traces(Y.c, TY);
+        double lm[2], rm[2], tm[2], rr[3];
+        const double nb0 = __shfl_up_sync(0xffffffffu, T.r[0], 1), nb1 = __shfl_up_sync(0xffffffffu, T.r[1], 1);
+        dg1_edge(V.uL, nb0, nb1, T.l[0], T.l[1], lm[0], lm[1]);
+        rm[0] = __shfl_down_sync(0xffffffffu, lm[0], 1);
+        rm[1] = __shfl_down_sync(0xffffffffu, lm[1], 1);
+        dg1_edge(V.vT, T.t[0], T.t[1], TY.b[0], TY.b[1], tm[0], tm[1]);
+        dg1_cell_m(X.c, V.uL, V.uR, V.vB, V.vT, lm, rm, K.bm1, tm, rr);
+#pragma unroll
+        for (int q = 0; q < 3; ++q)
+            k1[q] = stage_value<false>(X.c[q], rr[q], A.dtim[q], 0., 1., 0.);
+        K.bm1[0] = tm[0];
+        K.bm1[1] = tm[1];
+    }
+    { // ---- stage 2 on row r-1 (as tm_step<3, true> with src = k1, base = phi)
+        Traces1 T, TY;
+        dg1_traces(K.k0, T);
+        dg1_traces(k1, TY);
+        double lm[2], rm[2], tm[2], rr[3];
+        const double nb0 = __shfl_up_sync(0xffffffffu, T.r[0], 1), nb1 = __shfl_up_sync(0xffffffffu, T.r[1], 1);
+        dg1_edge(K.uL, nb0, nb1, T.l[0], T.l[1], lm[0], lm[1]);
+        rm[0] = __shfl_down_sync(0xffffffffu, lm[0], 1);
+        rm[1] = __shfl_down_sync(0xffffffffu, lm[1], 1);
+        dg1_edge(K.vT, T.t[0], T.t[1], TY.b[0], TY.b[1], tm[0], tm[1]);
+        dg1_cell_m(K.k0, K.uL, K.uR, K.vB, K.vT, lm, rm, K.bm2, tm, rr);
+        if (store) {
+#pragma unroll
+            for (int q = 0; q < 3; ++q)
+                A.dst[f][q * A.plane + K.pk] = stage_value<true>(K.k0[q], rr[q], A.dtim[q], A.a, A.b, K.pc[q]);
+        }
+        K.bm2[0] = tm[0];
+        K.bm2[1] = tm[1];
+    }
+#pragma unroll
+    for (int q = 0; q < 3; ++q) {
+        K.k0[q] = k1[q];
+        K.pc[q] = X.c[q];
+        K.uL[q] = V.uL[q];
+        K.uR[q] = V.uR[q];
+        K.vB[q] = V.vB[q];
+        K.vT[q] = V.vT[q];
+        K.vb[q] = V.vT[q];
+    }
+    K.pk = X.k;
+}
+
+// (128 registers at 4 CTAs per SM; 3 CTAs: no faster, 5: spills, 26.4 against 24.6 us on the 1024^2
+// cone, profiles/r2ab_heun_sweep.txt)
+__global__ void __launch_bounds__(TM_WPB * 32, 4) transport_heun_march_kernel(const __grid_constant__ StageArgs A)
+{
+    const int lane = threadIdx.x & 31;
+    const int cb = (blockIdx.x * TM_WPB + (threadIdx.x >> 5)) * TM_OWN; // first owned column
+    if (cb >= A.nx)
+        return; // whole warp
+    const int cu = cb - TM_OFF + lane;
+    const int gi = t_wrap(cu, A.nx);
+    const bool own = lane >= TM_OFF && lane < TM_OFF + TM_OWN && cu < A.nx;
+    const int f = blockIdx.z;
+    const int b0 = A.r0 + blockIdx.y * A.band; // owned rows [b0, b1)
+    const int b1 = min(b0 + A.band, A.r1);
+    // The march starts two rows below the band and ends one row above it; the first steps are
+    // ordinary loop iterations on zero-initialised kept values (never stored), so a cell's result
+    // does not depend on where the band boundaries fall.
+    HKeep K = {};
+    HRow X, Y, Z;
+    th_load(A, f, b0 - 2, gi, X);
+    th_load(A, f, b0 - 1, gi, Y);
+    int r = b0 - 2;
+#pragma unroll 1
+    for (; r + 2 <= b1; r += 3) {
+        th_step(A, f, r, gi, own && r > b0, X, Y, Z, K);
+        th_step(A, f, r + 1, gi, own && r + 1 > b0, Y, Z, X, K);
+        th_step(A, f, r + 2, gi, own && r + 2 > b0, Z, X, Y, K);
+    }
+    if (r <= b1) {
+        th_step(A, f, r, gi, own && r > b0, X, Y, Z, K);
+        if (r + 1 <= b1)
+            th_step(A, f, r + 1, gi, own && r + 1 > b0, Y, Z, X, K);
+    }
+}
+
 // rows per band: all CTAs of a launch cost rows + 3 steps and `slots` are resident at a time, so
 // the launch takes whole waves; taller bands have fewer halo rows (cf. march_auto_rows, mevp.cu)
 int transport_band_rows(int64_t nrows, int64_t ctas_per_band, int64_t slots)
@@ -757,12 +891,9 @@ void launch_stage(const StageArgs& A, bool has_base, dim3 grid, dim3 block, cuda
 
 } // namespace
 
-int nsdg_transport_stage(nsdg_ctx* ctx, int nfields, double* const* src, double* const* base,
-    double* const* dst, double a, double b, double dt, int64_t r0, int64_t r1)
+static StageArgs stage_args(DynState* d, int nfields, double* const* src, double* const* base, double* const* dst,
+    double a, double b, double dt, int64_t r0, int64_t r1)
 {
-    DynState* d = ctx->dyn;
-    if (r1 <= r0)
-        return NSDG_OK;
     StageArgs A;
     for (int f = 0; f < 2; ++f) {
         A.src[f] = f < nfields ? src[f] : nullptr;
@@ -782,22 +913,46 @@ int nsdg_transport_stage(nsdg_ctx* ctx, int nfields, double* const* src, double*
     A.r0 = (int)r0;
     A.r1 = (int)r1;
     A.wrap = d->wrap ? 1 : 0;
-    {
-        const int nq = d->nc == 1 ? 1 : (d->nc == 3 ? 2 : 3);
-        const double g2 = 0.28867513459481287, g3 = 0.3872983346207417;
-        const double xs[3][3] = { { 0.5, 0., 0. }, { 0.5 - g2, 0.5 + g2, 0. }, { 0.5 - g3, 0.5, 0.5 + g3 } };
-        const double ws[3][3] = { { 1., 0., 0. }, { 0.5, 0.5, 0. }, { 5. / 18., 8. / 18., 5. / 18. } };
-        for (int g = 0; g < 3; ++g) {
-            const double sx = xs[nq - 1][g], w = ws[nq - 1][g];
-            A.ku0[g] = (1. - sx) * w * A.ihx;
-            A.ku1[g] = sx * w * A.ihx;
-            A.kv0[g] = (1. - sx) * w * A.ihy;
-            A.kv1[g] = sx * w * A.ihy;
-        }
-        const double im[6] = { 1., 12., 12., 180., 180., 144. };
-        for (int q = 0; q < 6; ++q)
-            A.dtim[q] = dt * im[q];
+    A.prefetch = 0;
+    A.band = 0;
+    const int nq = d->nc == 1 ? 1 : (d->nc == 3 ? 2 : 3);
+    const double g2 = 0.28867513459481287, g3 = 0.3872983346207417;
+    const double xs[3][3] = { { 0.5, 0., 0. }, { 0.5 - g2, 0.5 + g2, 0. }, { 0.5 - g3, 0.5, 0.5 + g3 } };
+    const double ws[3][3] = { { 1., 0., 0. }, { 0.5, 0.5, 0. }, { 5. / 18., 8. / 18., 5. / 18. } };
+    for (int g = 0; g < 3; ++g) {
+        const double sx = xs[nq - 1][g], w = ws[nq - 1][g];
+        A.ku0[g] = (1. - sx) * w * A.ihx;
+        A.ku1[g] = sx * w * A.ihx;
+        A.kv0[g] = (1. - sx) * w * A.ihy;
+        A.kv1[g] = sx * w * A.ihy;
     }
+    const double im[6] = { 1., 12., 12., 180., 180., 144. };
+    for (int q = 0; q < 6; ++q)
+        A.dtim[q] = dt * im[q];
+    return A;
+}
+
+int nsdg_transport_heun(nsdg_ctx* ctx, int nfields, double* const* src, double* const* dst, double dt, int64_t r0, int64_t r1)
+{
+    DynState* d = ctx->dyn;
+    if (r1 <= r0)
+        return NSDG_OK;
+    NSDG_REQUIRE(ctx, d->nc == 3 && d->wrap, NSDG_ESTATE, "the fused Heun step is for dG1 on a single rank");
+    StageArgs A = stage_args(d, nfields, src, nullptr, dst, 0.5, 0.5, dt, r0, r1);
+    const int64_t nwarps = (d->nx + TM_OWN - 1) / TM_OWN, gx = (nwarps + TM_WPB - 1) / TM_WPB;
+    A.band = transport_band_rows(r1 - r0, gx * nfields, 4 * (int64_t)ctx->sm_count);
+    dim3 block(TM_WPB * 32), grid((unsigned)gx, (unsigned)((r1 - r0 + A.band - 1) / A.band), (unsigned)nfields);
+    NSDG_KERNEL(ctx, NSDG_K_TRANSPORT_MARCH, (transport_heun_march_kernel<<<grid, block, 0, ctx->stream>>>(A)));
+    return NSDG_OK;
+}
+
+int nsdg_transport_stage(nsdg_ctx* ctx, int nfields, double* const* src, double* const* base,
+    double* const* dst, double a, double b, double dt, int64_t r0, int64_t r1)
+{
+    DynState* d = ctx->dyn;
+    if (r1 <= r0)
+        return NSDG_OK;
+    StageArgs A = stage_args(d, nfields, src, base, dst, a, b, dt, r0, r1);
     // tiled kernel only: L2 prefetch of the streams a thread uses last.  (For the marching kernel an
     // L2 prefetch 1-8 rows ahead of the register pipeline was measured SLOWER, 3.04-3.72 ms against
     // 2.77-2.85 ms per H+A step at 4096^2: profiles/r2m_transport_prefetch.txt.)

@@ -441,6 +441,9 @@ def test_transport_marching_kernel_against_tiled_kernel_and_oracle(ctx, shape, b
     from registers) against the one-thread-per-cell kernel: same integrals with every fused
     multiply-add written out (transport.cu is compiled without automatic contraction), so the
     two agree BIT FOR BIT after three SSP-RK3 steps, and both are within 1e-11 of the oracle.
+    dG1 has a third arm, the default one: both Heun stages in ONE launch (transport_heun_march_kernel,
+    stage 1 kept in registers on a one-cell halo, tracer and stage buffer trade places), also bit
+    for bit; single-tracer steps (nsdg_transport_step) go through the same three arms.
     Ragged sizes, a grid narrower than a warp's 28 columns, fewer rows than the pipeline depth."""
     nx, ny = shape
     F, hx, hy = S.box_case(nx, ny, nc)
@@ -455,15 +458,24 @@ def test_transport_marching_kernel_against_tiled_kernel_and_oracle(ctx, shape, b
     mp.bc = bc
     dt = 0.1 * min(hx, hy) / 1.5
     out = {}
-    for name, tm in (("march", 1), ("tiled", -1)):
-        dyn = GpuDynamics(ctx, nx, ny, hx, hy, nc, mevp=mp, tuning={"transport_march": tm})
+    arms = [("march", {"transport_march": 1, "transport_fused": -1}),
+            ("tiled", {"transport_march": -1, "transport_fused": -1})]
+    if nc == 3:
+        arms += [("fused", {}), ("fused-graph", {"graph": 1}), ("fused-single", {})]
+    for name, tune in arms:
+        dyn = GpuDynamics(ctx, nx, ny, hx, hy, nc, mevp=mp, tuning=tune)
         dyn.upload_all({k: v for k, v in F.items() if k in ("H", "A", "U", "V")})
         for _ in range(3):
-            dyn.transport_step(dt)
+            if name == "fused-single":  # one tracer at a time: nsdg_transport_step
+                dyn.transport_step(dt, "A")
+                dyn.transport_step(dt, "H")
+            else:
+                dyn.transport_step(dt)
         out[name] = {k: dyn.download(k) for k in ("H", "A")}
         dyn.close()
     for k in ("H", "A"):
-        assert np.array_equal(out["march"][k], out["tiled"][k]), k
+        for name, _ in arms[1:]:
+            assert np.array_equal(out["march"][k], out[name][k]), (k, name)
         if nx * ny <= 300 * 211:
             ref = F[k]
             for _ in range(3):
