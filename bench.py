@@ -57,6 +57,9 @@ BYTES_STRESS = (9 + 2 + 4 + 9) * 8  # r S(9) u,v(2) P_g(4)  w S(9)
 BYTES_VELOCITY = (7 + 2 + 2 + 4 + 2) * 8  # r S(7 of 9) u,v u_o,v_o node constants(4)  w u,v
 BYTES_FUSED = (9 + 2 + 4 + 2 + 4 + 9 + 2) * 8  # one fused sub-iteration: 32 doubles
 BYTES_TRANSPORT_STEP = (2 * 8 * NCOMP + 6) * 8  # H and A, SSP-RK3, shared velocity reads
+# stages 1 + 2 in one launch (transport_pair_march_kernel, single rank): per tracer 6 in + 6 out,
+# then stage 3 with 6 + 6 in, 6 out; the velocity is read by two launches instead of three
+BYTES_TRANSPORT_STEP_FUSED = (2 * 5 * NCOMP + 4) * 8
 BYTES_PREPARE = (12 + 4 + 8 + 4) * 8  # P_g from H,A; node constants from H0,A0,u_a,u,u_o
 # the pair kernels run TWO sub-iterations per pass over HBM (temporal blocking): the compulsory
 # DRAM bytes of a launch are those of ONE fused sub-iteration
@@ -328,12 +331,14 @@ def kernel_table(prof, ms, cells_local, steps, peak):
     """Per-kernel CUDA-event totals of the timed region with the algorithmic (compulsory DRAM)
     bytes each kernel class has to move in it, and the fraction of the HBM peak that gives."""
     pairs = steps * (NSUB // 2)
+    tm = prof.get("transport_march_kernel")
+    transport = BYTES_TRANSPORT_STEP_FUSED if tm and tm[1] == 2 * steps else BYTES_TRANSPORT_STEP
     total_bytes = {
         # one pass over HBM per launch (= per pair for the pair kernels)
         "mevp_march_kernel": BYTES_FUSED * cells_local * pairs,
         "mevp_pair_kernel": BYTES_FUSED * cells_local * pairs,
         "transport_stage_kernel": BYTES_TRANSPORT_STEP * cells_local * steps,
-        "transport_march_kernel": BYTES_TRANSPORT_STEP * cells_local * steps,
+        "transport_march_kernel": transport * cells_local * steps,
         "pressure_kernel": (12 + 4) * 8 * cells_local * steps,
         "nodal_kernel": (8 + 4) * 8 * cells_local * steps,
     }
@@ -502,6 +507,9 @@ def measure_north_star(args, env, strong=False, with_e2e=True, with_cpu=True, st
         split = "stress_kernel" in prof
         paired = units > 1
         BYTES_STEP = BYTES_STEP_SPLIT if split else (BYTES_STEP_PAIR if paired else BYTES_STEP_FUSED)
+        tm = prof.get("transport_march_kernel")
+        if tm and tm[1] == 2 * steps:  # two launches per step: stages 1 + 2 share one pass
+            BYTES_STEP += BYTES_TRANSPORT_STEP_FUSED - BYTES_TRANSPORT_STEP
         step_gbs = BYTES_STEP * cells_local * steps / (ms * 1e-3) / 1e9
         single_launch = world == 1 or ctx.halo_peer
         traffic = NCU_TRAFFIC_4096SQ.get(kname) if (cells_local == 4096 * 4096 and single_launch) else None

@@ -186,10 +186,12 @@ typedef struct nsdg_dyn_tuning {
                            per-lane 8-byte cp.async (single rank); 3 = rows ahead pulled into L2
                            by tensor-box prefetches of the bulk-copy engine (single rank, even
                            nx); 0 / -1 = register pipeline only (default) [NSDG_MEVP_RING=0/1/2/3] */
-    int32_t transport_fused; /* dG1 + Heun on a single rank without limiter: both Runge-Kutta
-                                stages in one launch (transport_heun_march_kernel; the tracer and
-                                its stage buffer swap roles, so nsdg_dyn_field_ptr(H / A) changes
-                                with every step): 0/1 on, -1 off          [NSDG_TRANSPORT_FUSED=0/1] */
+    int32_t transport_fused; /* two Runge-Kutta stages per launch (transport_pair_march_kernel;
+                                single rank, limiter off): the whole Heun step of dG1 (the tracer
+                                and its stage buffer swap roles, so nsdg_dyn_field_ptr(H / A)
+                                changes with every step), stages 1 + 2 of the SSP-RK3 step of dG2:
+                                0 = where the marching stage kernel is the choice (transport_march),
+                                1 on any grid, -1 off                  [NSDG_TRANSPORT_FUSED=0/1] */
     int32_t reserved[6]; /* must be 0 */
 } nsdg_dyn_tuning;
 

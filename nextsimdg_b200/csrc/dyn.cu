@@ -103,12 +103,18 @@ void append(PlaneSet& ps, DynState* d, double* base, int ncomp)
         ps.p[ps.n++] = base + (size_t)c * d->plane;
 }
 
-// dG1 + Heun on a single rank, no limiter between the stages: the whole step is one launch
-bool heun_fused(nsdg_ctx* ctx)
+// Two RK stages per launch (transport_pair_march_kernel): single rank, no limiter between the
+// stages, and a grid on which the marching kernels are the choice anyway (transport_fused = 1
+// forces it on any grid, -1 switches it off)
+bool stages_fused(nsdg_ctx* ctx)
 {
     const DynState* d = ctx->dyn;
-    return d->rk == 2 && d->nc == 3 && !nsdg_comm_active(ctx) && !d->cfg.limiter && d->tune.transport_fused >= 0;
+    const int tf = d->tune.transport_fused;
+    return d->nc >= 3 && d->rk == (d->nc == 3 ? 2 : 3) && !nsdg_comm_active(ctx) && !d->cfg.limiter
+        && (tf > 0 || (tf == 0 && nsdg_transport_marching(ctx)));
 }
+// dG1 + Heun: the whole step is one launch
+bool heun_fused(nsdg_ctx* ctx) { return ctx->dyn->nc == 3 && stages_fused(ctx); }
 
 // one RK time step for the nfields tracers fld[0..nfields) (d->f[fld[f]] advanced; s1 = the
 // stage-1 slots d->stage1, which trade places with the tracers in the fused Heun step)
@@ -122,7 +128,7 @@ int transport_fields(nsdg_ctx* ctx, int nfields, const int* fld, double** s1, do
     double* phi[2] = { d->f[fld[0]], nfields > 1 ? d->f[fld[1]] : nullptr };
     // both stages in one launch, the result lands in the stage buffer and the two trade places
     if (heun_fused(ctx)) {
-        if ((rc = nsdg_transport_heun(ctx, nfields, phi, s1, dt, r0, r1)))
+        if ((rc = nsdg_transport_pair(ctx, nfields, phi, s1, 0.5, 0.5, dt, r0, r1)))
             return rc;
         for (int f = 0; f < nfields; ++f)
             std::swap(d->f[fld[f]], s1[f]);
@@ -147,6 +153,12 @@ int transport_fields(nsdg_ctx* ctx, int nfields, const int* fld, double** s1, do
         }
         return NSDG_OK;
     };
+    if (stages_fused(ctx)) { // dG2, SSP-RK3: stages 1 + 2 in one launch (s1 stays in registers), then stage 3
+        if ((rc = nsdg_transport_pair(ctx, nfields, phi, s2, 0.75, 0.25, dt, r0, r1))
+            || (rc = nsdg_transport_stage(ctx, nfields, s2, phi, phi, 1. / 3., 2. / 3., dt, r0, r1)))
+            return rc;
+        return NSDG_OK;
+    }
     // stage 1: s1 = phi + dt L(phi).  Strips: one message per neighbour carries the upper ghost
     // node row of the velocity (read by the top cell row of every stage) and the tracers' rows.
     if (multi) {

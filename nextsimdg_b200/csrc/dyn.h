@@ -98,8 +98,11 @@ struct HaloSpec {
 // dst = a*base + b*(src + dt*L(src)) for nfields tracers sharing the velocity; rows [r0,r1)
 int nsdg_transport_stage(nsdg_ctx* ctx, int nfields, double* const* src, double* const* base,
     double* const* dst, double a, double b, double dt, int64_t r0, int64_t r1);
-// dG1 + Heun, both stages in one launch: dst = Heun step of src (dst != src); single rank only
-int nsdg_transport_heun(nsdg_ctx* ctx, int nfields, double* const* src, double* const* dst, double dt, int64_t r0, int64_t r1);
+bool nsdg_transport_marching(const nsdg_ctx* ctx);
+// two RK stages in one launch: dst = a src + b (k1 + dt L(k1)), k1 = src + dt L(src); dst != src;
+// dG1 / dG2, single rank only
+int nsdg_transport_pair(nsdg_ctx* ctx, int nfields, double* const* src, double* const* dst, double a, double b, double dt,
+    int64_t r0, int64_t r1);
 int nsdg_transport_limit(nsdg_ctx* ctx, double* phi, double lo, double hi);
 
 // mevp.cu -----------------------------------------------------------------------------------

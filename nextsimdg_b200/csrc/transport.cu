@@ -724,107 +724,126 @@ __global__ void __launch_bounds__(TM_WPB * 32, NC == 6 ? 3 : 5) transport_march_
 }
 
 // ---------------------------------------------------------------------------------------------
-// dG1, Heun: BOTH Runge-Kutta stages in one launch (temporal blocking, like the sub-cycle's pair
-// kernel).  Step r of the march runs stage 1 on cell row r in lanes 1..30 (k1 = phi + dt L(phi),
-// kept in registers, never stored) and stage 2 on row r-1 in the owned lanes 2..29
-// (phi' = 1/2 phi + 1/2 (k1 + dt L(k1))), whose neighbours are k1 of rows r-2 (through the kept
-// bottom flux), r-1 and r and of the lanes next door.  The velocity does not change between the
-// stages, so the edge velocities of a row are computed once and kept for its second stage.
-// phi crosses HBM / L2 once per STEP instead of twice per stage-pair plus the k1 round trip
-// (3 reads + 2 writes of every coefficient become 1 + 1), one launch instead of two; the price is
-// stage 1 on a 1-column / 1-row halo (30/28 in x, 3 extra march steps per band).  Same device
-// functions, same operand order as the stage kernels: bit-identical to two transport_march /
-// transport_stage launches.  The result cannot go back in place (neighbouring warps and bands
-// still read phi): it is written to the stage buffer and the host swaps the two pointers.
-// Single rank, limiter off.
-struct HRow {
-    double c[3]; // phi of cell row r
+// TWO Runge-Kutta stages in one launch (temporal blocking, like the sub-cycle's pair kernel):
+//   k1  = phi + dt L(phi)                       stage 1, kept in registers, never stored
+//   dst = a phi + b (k1 + dt L(k1))             stage 2, the RK base is the source itself
+// = the whole Heun step of dG1 (a = b = 1/2) and stages 1 + 2 of the SSP-RK3 step of dG2
+// (a = 3/4, b = 1/4; stage 3 follows as an ordinary stage launch).  Step r of the march runs
+// stage 1 on cell row r in lanes 1..30 and stage 2 on row r-1 in the owned lanes 2..29, whose
+// neighbours are k1 of rows r-2 (through the kept bottom flux), r-1 and r and of the lanes next
+// door.  The velocity does not change between the stages, so the edge velocities of a row are
+// computed once and kept for its second stage.  Heun: phi crosses HBM / L2 once per STEP (1 read
+// + 1 write of every coefficient instead of 3 + 2), one launch instead of two; RK3: 12 + 18
+// doubles per cell and tracer for the step instead of 12 + 18 + 18.  The price is stage 1 on a
+// 1-column / 1-row halo (30/28 in x, 3 extra march steps per band).  Same device functions, same
+// operand order as the stage kernels: bit-identical to separate transport_march / transport_stage
+// launches.  dst must not be the source (neighbouring warps and bands still read it): Heun
+// writes to the stage buffer and the host swaps the two pointers.  Single rank, limiter off.
+template <int NC> struct HRow {
+    double c[NC]; // phi of cell row r
     double u, v; // velocity at node row r, own column
     int k;
 };
-__device__ __forceinline__ void th_load(const StageArgs& A, int f, int r, int gi, HRow& R)
+template <int NC> __device__ __forceinline__ void th_load(const StageArgs& A, int f, int r, int gi, HRow<NC>& R)
 {
     const int k = t_plane_row(A, r) * A.nx + gi;
     R.k = k;
 #pragma unroll
-    for (int q = 0; q < 3; ++q)
+    for (int q = 0; q < NC; ++q)
         R.c[q] = __ldg(A.src[f] + q * A.plane + k);
     R.u = __ldg(A.u + k);
     R.v = __ldg(A.v + k);
 }
-struct HKeep { // what stage 2 of row r-1 needs from the steps before
-    double k0[3]; // k1 of row r-1
-    double pc[3]; // phi of row r-1 (the RK base)
-    double uL[3], uR[3], vB[3], vT[3]; // edge velocities of row r-1
-    double bm1[2], bm2[2]; // flux through the bottom edge of row r (stage 1) / row r-1 (stage 2)
+template <int NC> struct HKeep { // what stage 2 of row r-1 needs from the steps before
+    double k0[NC]; // k1 of row r-1
+    double pc[NC]; // phi of row r-1 (the RK base)
+    EdgeVel V; // edge velocities of row r-1
+    double bm1[3], bm2[3]; // flux through the bottom edge of row r (stage 1) / row r-1 (stage 2)
     double vb[3]; // stage 1: the previous row's vT
     int pk; // plane index of (row r-1, own column)
 };
-__device__ __forceinline__ void th_step(const StageArgs& A, int f, int r, int gi, bool store, HRow& X, HRow& Y, HRow& Z, HKeep& K)
+// rr of the cells of one row from their coefficients c, the row above's cy, the edge velocities V
+// and the kept flux through the bottom edge bm (replaced by the flux through the top edge):
+// exactly the arithmetic of tm_step
+template <int NC>
+__device__ __forceinline__ void th_row(const double (&c)[NC], const double (&cy)[NC], const EdgeVel& V, double (&bm)[3], double (&rr)[NC])
 {
-    th_load(A, f, r + 2, gi, Z);
-    EdgeVel V;
-    {
-        const double u10 = __shfl_down_sync(0xffffffffu, X.u, 1), u11 = __shfl_down_sync(0xffffffffu, Y.u, 1);
-        const double v10 = __shfl_down_sync(0xffffffffu, X.v, 1), v11 = __shfl_down_sync(0xffffffffu, Y.v, 1);
-        edge_velocities<2>(A, X.u, u10, Y.u, u11, X.v, v10, Y.v, v11, V);
+    double lm[3], rm[3], tm[3];
+    if constexpr (NC == 6) {
+        Traces T, TY;
+        dg2_traces(c, T);
+        dg2_traces(cy, TY);
+        double nbL[3];
 #pragma unroll
         for (int q = 0; q < 3; ++q)
-            V.vB[q] = K.vb[q];
-    }
-    double k1[3];
-    { // ---- stage 1 on row r (as tm_step<3, false>)
+            nbL[q] = __shfl_up_sync(0xffffffffu, T.r[q], 1);
+        dg2_edge(V.uL, nbL, T.l, lm[0], lm[1], lm[2]);
+#pragma unroll
+        for (int q = 0; q < 3; ++q)
+            rm[q] = __shfl_down_sync(0xffffffffu, lm[q], 1);
+        dg2_edge(V.vT, T.t, TY.b, tm[0], tm[1], tm[2]);
+        dg2_cell_m(c, V, lm, rm, bm, tm, rr);
+    } else {
         Traces1 T, TY;
-        dg1_traces(X.c, T);
-        dg1_traces(Y.c, TY);
-        double lm[2], rm[2], tm[2], rr[3];
+        dg1_traces(c, T);
+        dg1_traces(cy, TY);
         const double nb0 = __shfl_up_sync(0xffffffffu, T.r[0], 1), nb1 = __shfl_up_sync(0xffffffffu, T.r[1], 1);
         dg1_edge(V.uL, nb0, nb1, T.l[0], T.l[1], lm[0], lm[1]);
         rm[0] = __shfl_down_sync(0xffffffffu, lm[0], 1);
         rm[1] = __shfl_down_sync(0xffffffffu, lm[1], 1);
         dg1_edge(V.vT, T.t[0], T.t[1], TY.b[0], TY.b[1], tm[0], tm[1]);
-        dg1_cell_m(X.c, V.uL, V.uR, V.vB, V.vT, lm, rm, K.bm1, tm, rr);
+        const double l2[2] = { lm[0], lm[1] }, r2[2] = { rm[0], rm[1] }, b2[2] = { bm[0], bm[1] }, t2[2] = { tm[0], tm[1] };
+        dg1_cell_m(c, V.uL, V.uR, V.vB, V.vT, l2, r2, b2, t2, rr);
+        tm[2] = 0.;
+    }
+#pragma unroll
+    for (int q = 0; q < 3; ++q)
+        bm[q] = tm[q];
+}
+template <int NC>
+__device__ __forceinline__ void th_step(const StageArgs& A, int f, int r, int gi, bool store, HRow<NC>& X, HRow<NC>& Y, HRow<NC>& Z,
+    HKeep<NC>& K)
+{
+    constexpr int NT = NC == 6 ? 3 : 2;
+    th_load<NC>(A, f, r + 2, gi, Z);
+    EdgeVel V;
+    {
+        const double u10 = __shfl_down_sync(0xffffffffu, X.u, 1), u11 = __shfl_down_sync(0xffffffffu, Y.u, 1);
+        const double v10 = __shfl_down_sync(0xffffffffu, X.v, 1), v11 = __shfl_down_sync(0xffffffffu, Y.v, 1);
+        edge_velocities<NT>(A, X.u, u10, Y.u, u11, X.v, v10, Y.v, v11, V);
 #pragma unroll
         for (int q = 0; q < 3; ++q)
-            k1[q] = stage_value<false>(X.c[q], rr[q], A.dtim[q], 0., 1., 0.);
-        K.bm1[0] = tm[0];
-        K.bm1[1] = tm[1];
+            V.vB[q] = K.vb[q];
     }
-    { // ---- stage 2 on row r-1 (as tm_step<3, true> with src = k1, base = phi)
-        Traces1 T, TY;
-        dg1_traces(K.k0, T);
-        dg1_traces(k1, TY);
-        double lm[2], rm[2], tm[2], rr[3];
-        const double nb0 = __shfl_up_sync(0xffffffffu, T.r[0], 1), nb1 = __shfl_up_sync(0xffffffffu, T.r[1], 1);
-        dg1_edge(K.uL, nb0, nb1, T.l[0], T.l[1], lm[0], lm[1]);
-        rm[0] = __shfl_down_sync(0xffffffffu, lm[0], 1);
-        rm[1] = __shfl_down_sync(0xffffffffu, lm[1], 1);
-        dg1_edge(K.vT, T.t[0], T.t[1], TY.b[0], TY.b[1], tm[0], tm[1]);
-        dg1_cell_m(K.k0, K.uL, K.uR, K.vB, K.vT, lm, rm, K.bm2, tm, rr);
-        if (store) {
+    double k1[NC], rr[NC];
+    // ---- stage 1 on row r (as tm_step<NC, false>)
+    th_row<NC>(X.c, Y.c, V, K.bm1, rr);
 #pragma unroll
-            for (int q = 0; q < 3; ++q)
-                A.dst[f][q * A.plane + K.pk] = stage_value<true>(K.k0[q], rr[q], A.dtim[q], A.a, A.b, K.pc[q]);
-        }
-        K.bm2[0] = tm[0];
-        K.bm2[1] = tm[1];
+    for (int q = 0; q < NC; ++q)
+        k1[q] = stage_value<false>(X.c[q], rr[q], A.dtim[q], 0., 1., 0.);
+    // ---- stage 2 on row r-1 (as tm_step<NC, true> with src = k1, base = phi)
+    th_row<NC>(K.k0, k1, K.V, K.bm2, rr);
+    if (store) {
+#pragma unroll
+        for (int q = 0; q < NC; ++q)
+            A.dst[f][q * A.plane + K.pk] = stage_value<true>(K.k0[q], rr[q], A.dtim[q], A.a, A.b, K.pc[q]);
     }
 #pragma unroll
-    for (int q = 0; q < 3; ++q) {
+    for (int q = 0; q < NC; ++q) {
         K.k0[q] = k1[q];
         K.pc[q] = X.c[q];
-        K.uL[q] = V.uL[q];
-        K.uR[q] = V.uR[q];
-        K.vB[q] = V.vB[q];
-        K.vT[q] = V.vT[q];
-        K.vb[q] = V.vT[q];
     }
+    K.V = V;
+#pragma unroll
+    for (int q = 0; q < 3; ++q)
+        K.vb[q] = V.vT[q];
     K.pk = X.k;
 }
 
-// (128 registers at 4 CTAs per SM; 3 CTAs: no faster, 5: spills, 26.4 against 24.6 us on the 1024^2
-// cone, profiles/r2ab_heun_sweep.txt)
-__global__ void __launch_bounds__(TM_WPB * 32, 4) transport_heun_march_kernel(const __grid_constant__ StageArgs A)
+// dG1: 128 registers at 4 CTAs per SM (3 CTAs: no faster, 5: spills, 26.4 against 24.6 us on the
+// 1024^2 cone, profiles/r2ab_heun_sweep.txt); dG2: 2 CTAs per SM
+template <int NC>
+__global__ void __launch_bounds__(TM_WPB * 32, NC == 6 ? 2 : 4) transport_pair_march_kernel(const __grid_constant__ StageArgs A)
 {
     const int lane = threadIdx.x & 31;
     const int cb = (blockIdx.x * TM_WPB + (threadIdx.x >> 5)) * TM_OWN; // first owned column
@@ -839,21 +858,21 @@ __global__ void __launch_bounds__(TM_WPB * 32, 4) transport_heun_march_kernel(co
     // The march starts two rows below the band and ends one row above it; the first steps are
     // ordinary loop iterations on zero-initialised kept values (never stored), so a cell's result
     // does not depend on where the band boundaries fall.
-    HKeep K = {};
-    HRow X, Y, Z;
-    th_load(A, f, b0 - 2, gi, X);
-    th_load(A, f, b0 - 1, gi, Y);
+    HKeep<NC> K = {};
+    HRow<NC> X, Y, Z;
+    th_load<NC>(A, f, b0 - 2, gi, X);
+    th_load<NC>(A, f, b0 - 1, gi, Y);
     int r = b0 - 2;
 #pragma unroll 1
     for (; r + 2 <= b1; r += 3) {
-        th_step(A, f, r, gi, own && r > b0, X, Y, Z, K);
-        th_step(A, f, r + 1, gi, own && r + 1 > b0, Y, Z, X, K);
-        th_step(A, f, r + 2, gi, own && r + 2 > b0, Z, X, Y, K);
+        th_step<NC>(A, f, r, gi, own && r > b0, X, Y, Z, K);
+        th_step<NC>(A, f, r + 1, gi, own && r + 1 > b0, Y, Z, X, K);
+        th_step<NC>(A, f, r + 2, gi, own && r + 2 > b0, Z, X, Y, K);
     }
     if (r <= b1) {
-        th_step(A, f, r, gi, own && r > b0, X, Y, Z, K);
+        th_step<NC>(A, f, r, gi, own && r > b0, X, Y, Z, K);
         if (r + 1 <= b1)
-            th_step(A, f, r + 1, gi, own && r + 1 > b0, Y, Z, X, K);
+            th_step<NC>(A, f, r + 1, gi, own && r + 1 > b0, Y, Z, X, K);
     }
 }
 
@@ -932,17 +951,30 @@ static StageArgs stage_args(DynState* d, int nfields, double* const* src, double
     return A;
 }
 
-int nsdg_transport_heun(nsdg_ctx* ctx, int nfields, double* const* src, double* const* dst, double dt, int64_t r0, int64_t r1)
+// the launcher's choice between the marching and the one-thread-per-cell stage kernel
+// (nsdg_dyn_tuning.transport_march: 1 marching on any grid, -1 never, 0 from 2^20 cells)
+bool nsdg_transport_marching(const nsdg_ctx* ctx)
+{
+    const DynState* d = ctx->dyn;
+    const int tm = d->tune.transport_march;
+    return d->nc >= 3 && tm >= 0 && (tm > 0 || d->nx * d->nyl >= ((int64_t)1 << 20));
+}
+
+int nsdg_transport_pair(nsdg_ctx* ctx, int nfields, double* const* src, double* const* dst, double a, double b, double dt,
+    int64_t r0, int64_t r1)
 {
     DynState* d = ctx->dyn;
     if (r1 <= r0)
         return NSDG_OK;
-    NSDG_REQUIRE(ctx, d->nc == 3 && d->wrap, NSDG_ESTATE, "the fused Heun step is for dG1 on a single rank");
-    StageArgs A = stage_args(d, nfields, src, nullptr, dst, 0.5, 0.5, dt, r0, r1);
+    NSDG_REQUIRE(ctx, d->nc >= 3 && d->wrap, NSDG_ESTATE, "the two-stage launch is for dG1 / dG2 on a single rank");
+    StageArgs A = stage_args(d, nfields, src, nullptr, dst, a, b, dt, r0, r1);
     const int64_t nwarps = (d->nx + TM_OWN - 1) / TM_OWN, gx = (nwarps + TM_WPB - 1) / TM_WPB;
-    A.band = transport_band_rows(r1 - r0, gx * nfields, 4 * (int64_t)ctx->sm_count);
+    A.band = transport_band_rows(r1 - r0, gx * nfields, (d->nc == 6 ? 2 : 4) * (int64_t)ctx->sm_count);
     dim3 block(TM_WPB * 32), grid((unsigned)gx, (unsigned)((r1 - r0 + A.band - 1) / A.band), (unsigned)nfields);
-    NSDG_KERNEL(ctx, NSDG_K_TRANSPORT_MARCH, (transport_heun_march_kernel<<<grid, block, 0, ctx->stream>>>(A)));
+    if (d->nc == 6)
+        NSDG_KERNEL(ctx, NSDG_K_TRANSPORT_MARCH, (transport_pair_march_kernel<6><<<grid, block, 0, ctx->stream>>>(A)));
+    else
+        NSDG_KERNEL(ctx, NSDG_K_TRANSPORT_MARCH, (transport_pair_march_kernel<3><<<grid, block, 0, ctx->stream>>>(A)));
     return NSDG_OK;
 }
 
@@ -960,8 +992,7 @@ int nsdg_transport_stage(nsdg_ctx* ctx, int nfields, double* const* src, double*
     const bool hb = base != nullptr;
     // dG2 on grids that do not live in L2: the marching kernel (nsdg_dyn_tuning.transport_march:
     // 1 forces it on any grid, -1 selects the one-thread-per-cell kernel)
-    const int tm = d->tune.transport_march;
-    if (d->nc >= 3 && tm >= 0 && (tm > 0 || d->nx * d->nyl >= ((int64_t)1 << 20))) {
+    if (nsdg_transport_marching(ctx)) {
         const int64_t nwarps = (d->nx + TM_OWN - 1) / TM_OWN, gx = (nwarps + TM_WPB - 1) / TM_WPB;
         // resident CTAs per SM: 3 (dG2, 168 registers) / 5 (dG1)
         A.band = transport_band_rows(r1 - r0, gx * nfields, (d->nc == 6 ? 3 : 5) * (int64_t)ctx->sm_count);

@@ -426,6 +426,7 @@ def test_pair_kernel_variants_bit_identical(ctx):
                 "graph": {"graph": 1}, "nograph": {"graph": -1},
                 "transport-march": {"transport_march": 1}, "transport-tiled": {"transport_march": -1},
                 "transport-march-rows16": {"transport_march": 1, "march_rows": 16},
+                "transport-fused": {"transport_fused": 1}, "transport-unfused": {"transport_fused": -1},
                 "ring": {"march_ring": 1}, "ring-rows5": {"march_ring": 1, "march_rows": 5},
                 "lane-ring": {"march_ring": 2}, "lane-ring-rows5": {"march_ring": 2, "march_rows": 5},
                 "l2-prefetch": {"march_ring": 3}, "l2-prefetch-rows7": {"march_ring": 3, "march_rows": 7}}
@@ -441,9 +442,10 @@ def test_transport_marching_kernel_against_tiled_kernel_and_oracle(ctx, shape, b
     from registers) against the one-thread-per-cell kernel: same integrals with every fused
     multiply-add written out (transport.cu is compiled without automatic contraction), so the
     two agree BIT FOR BIT after three SSP-RK3 steps, and both are within 1e-11 of the oracle.
-    dG1 has a third arm, the default one: both Heun stages in ONE launch (transport_heun_march_kernel,
-    stage 1 kept in registers on a one-cell halo, tracer and stage buffer trade places), also bit
-    for bit; single-tracer steps (nsdg_transport_step) go through the same three arms.
+    Third arm (the default from 2^20 cells): TWO stages in one launch (transport_pair_march_kernel,
+    stage 1 kept in registers on a one-cell halo): the whole Heun step of dG1 (tracer and stage
+    buffer trade places) / stages 1 + 2 of the dG2 step, also bit for bit, also through graph
+    replay and as single-tracer steps (nsdg_transport_step).
     Ragged sizes, a grid narrower than a warp's 28 columns, fewer rows than the pipeline depth."""
     nx, ny = shape
     F, hx, hy = S.box_case(nx, ny, nc)
@@ -460,8 +462,9 @@ def test_transport_marching_kernel_against_tiled_kernel_and_oracle(ctx, shape, b
     out = {}
     arms = [("march", {"transport_march": 1, "transport_fused": -1}),
             ("tiled", {"transport_march": -1, "transport_fused": -1})]
-    if nc == 3:
-        arms += [("fused", {}), ("fused-graph", {"graph": 1}), ("fused-single", {})]
+    # two stages per launch: the whole Heun step (dG1) / stages 1 + 2 of SSP-RK3 (dG2)
+    arms += [("fused", {"transport_fused": 1}), ("fused-graph", {"transport_fused": 1, "graph": 1}),
+             ("fused-single", {"transport_fused": 1}), ("fused-march3", {"transport_fused": 1, "transport_march": 1})]
     for name, tune in arms:
         dyn = GpuDynamics(ctx, nx, ny, hx, hy, nc, mevp=mp, tuning=tune)
         dyn.upload_all({k: v for k, v in F.items() if k in ("H", "A", "U", "V")})
