@@ -187,7 +187,8 @@ typedef struct nsdg_dyn_tuning {
                            by tensor-box prefetches of the bulk-copy engine (single rank, even
                            nx); 0 / -1 = register pipeline only (default) [NSDG_MEVP_RING=0/1/2/3] */
     int32_t transport_fused; /* two Runge-Kutta stages per launch (transport_pair_march_kernel;
-                                single rank, limiter off): the whole Heun step of dG1 (the tracer
+                                limiter off; strips exchange two ghost rows in front of it and
+                                have one exchange less per step): the whole Heun step of dG1 (the tracer
                                 and its stage buffer swap roles, so nsdg_dyn_field_ptr(H / A)
                                 changes with every step), stages 1 + 2 of the SSP-RK3 step of dG2:
                                 0 = where the marching stage kernel is the choice (transport_march),

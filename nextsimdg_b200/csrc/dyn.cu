@@ -103,15 +103,15 @@ void append(PlaneSet& ps, DynState* d, double* base, int ncomp)
         ps.p[ps.n++] = base + (size_t)c * d->plane;
 }
 
-// Two RK stages per launch (transport_pair_march_kernel): single rank, no limiter between the
-// stages, and a grid on which the marching kernels are the choice anyway (transport_fused = 1
-// forces it on any grid, -1 switches it off)
+// Two RK stages per launch (transport_pair_march_kernel): no limiter between the stages, and a grid
+// on which the marching kernels are the choice anyway (transport_fused = 1 forces it on any grid,
+// -1 switches it off).  Strips: the first launch then needs TWO ghost rows of the tracers and of
+// the velocity on either side, and the step has one halo exchange less.
 bool stages_fused(nsdg_ctx* ctx)
 {
     const DynState* d = ctx->dyn;
     const int tf = d->tune.transport_fused;
-    return d->nc >= 3 && d->rk == (d->nc == 3 ? 2 : 3) && !nsdg_comm_active(ctx) && !d->cfg.limiter
-        && (tf > 0 || (tf == 0 && nsdg_transport_marching(ctx)));
+    return d->nc >= 3 && d->rk == (d->nc == 3 ? 2 : 3) && !d->cfg.limiter && (tf > 0 || (tf == 0 && nsdg_transport_marching(ctx)));
 }
 // dG1 + Heun: the whole step is one launch
 bool heun_fused(nsdg_ctx* ctx) { return ctx->dyn->nc == 3 && stages_fused(ctx); }
@@ -126,14 +126,22 @@ int transport_fields(nsdg_ctx* ctx, int nfields, const int* fld, double** s1, do
     const int64_t r0 = NSDG_GHOST, r1 = NSDG_GHOST + d->nyl;
     int rc;
     double* phi[2] = { d->f[fld[0]], nfields > 1 ? d->f[fld[1]] : nullptr };
-    // both stages in one launch, the result lands in the stage buffer and the two trade places
-    if (heun_fused(ctx)) {
-        if ((rc = nsdg_transport_pair(ctx, nfields, phi, s1, 0.5, 0.5, dt, r0, r1)))
-            return rc;
+    // one message per neighbour: ghost node rows of the velocity and ghost rows of the tracers
+    auto halo_uv_phi = [&](int nlo_uv, int nhi_uv, int nphi) -> int {
+        if (!multi)
+            return NSDG_OK;
+        HaloSpec hs[2];
+        hs[0].planes.n = 0;
+        hs[0].planes.p[hs[0].planes.n++] = d->f[NSDG_DF_U];
+        hs[0].planes.p[hs[0].planes.n++] = d->f[NSDG_DF_V];
+        hs[0].nlo = nlo_uv;
+        hs[0].nhi = nhi_uv;
+        hs[1].planes.n = 0;
         for (int f = 0; f < nfields; ++f)
-            std::swap(d->f[fld[f]], s1[f]);
-        return NSDG_OK;
-    }
+            append(hs[1].planes, d, phi[f], d->nc);
+        hs[1].nlo = hs[1].nhi = nphi;
+        return nsdg_halo_exchange(ctx, hs, 2);
+    };
     auto halo = [&](double** arr) -> int {
         if (!multi)
             return NSDG_OK;
@@ -153,28 +161,28 @@ int transport_fields(nsdg_ctx* ctx, int nfields, const int* fld, double** s1, do
         }
         return NSDG_OK;
     };
-    if (stages_fused(ctx)) { // dG2, SSP-RK3: stages 1 + 2 in one launch (s1 stays in registers), then stage 3
-        if ((rc = nsdg_transport_pair(ctx, nfields, phi, s2, 0.75, 0.25, dt, r0, r1))
+    if (stages_fused(ctx)) {
+        // stage 1 is computed on one ghost cell row on either side: two ghost rows of the tracers,
+        // the ghost node rows 1 and nyl+2, nyl+3 of the velocity
+        if ((rc = halo_uv_phi(NSDG_GHOST, NSDG_GHOST, NSDG_GHOST)))
+            return rc;
+        if (d->nc == 3) { // Heun: the whole step in one launch; it lands in the stage buffer and the two trade places
+            if ((rc = nsdg_transport_pair(ctx, nfields, phi, s1, 0.5, 0.5, dt, r0, r1)))
+                return rc;
+            for (int f = 0; f < nfields; ++f)
+                std::swap(d->f[fld[f]], s1[f]);
+            return NSDG_OK;
+        }
+        // SSP-RK3: stages 1 + 2 in one launch (s1 stays in registers), then stage 3
+        if ((rc = nsdg_transport_pair(ctx, nfields, phi, s2, 0.75, 0.25, dt, r0, r1)) || (rc = halo(s2))
             || (rc = nsdg_transport_stage(ctx, nfields, s2, phi, phi, 1. / 3., 2. / 3., dt, r0, r1)))
             return rc;
         return NSDG_OK;
     }
     // stage 1: s1 = phi + dt L(phi).  Strips: one message per neighbour carries the upper ghost
     // node row of the velocity (read by the top cell row of every stage) and the tracers' rows.
-    if (multi) {
-        HaloSpec hs[2];
-        hs[0].planes.n = 0;
-        hs[0].planes.p[hs[0].planes.n++] = d->f[NSDG_DF_U];
-        hs[0].planes.p[hs[0].planes.n++] = d->f[NSDG_DF_V];
-        hs[0].nlo = 0;
-        hs[0].nhi = 1;
-        hs[1].planes.n = 0;
-        for (int f = 0; f < nfields; ++f)
-            append(hs[1].planes, d, phi[f], d->nc);
-        hs[1].nlo = hs[1].nhi = 1;
-        if ((rc = nsdg_halo_exchange(ctx, hs, 2)))
-            return rc;
-    }
+    if ((rc = halo_uv_phi(0, 1, 1)))
+        return rc;
     if ((rc = nsdg_transport_stage(ctx, nfields, phi, nullptr, s1, 0., 1., dt, r0, r1)) || (rc = limit(s1)))
         return rc;
     if (d->rk == 1) {

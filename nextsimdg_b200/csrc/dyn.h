@@ -100,7 +100,7 @@ int nsdg_transport_stage(nsdg_ctx* ctx, int nfields, double* const* src, double*
     double* const* dst, double a, double b, double dt, int64_t r0, int64_t r1);
 bool nsdg_transport_marching(const nsdg_ctx* ctx);
 // two RK stages in one launch: dst = a src + b (k1 + dt L(k1)), k1 = src + dt L(src); dst != src;
-// dG1 / dG2, single rank only
+// dG1 / dG2; strips: two ghost rows of src and of the velocity on either side current
 int nsdg_transport_pair(nsdg_ctx* ctx, int nfields, double* const* src, double* const* dst, double a, double b, double dt,
     int64_t r0, int64_t r1);
 int nsdg_transport_limit(nsdg_ctx* ctx, double* phi, double lo, double hi);

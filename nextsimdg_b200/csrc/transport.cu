@@ -738,7 +738,8 @@ __global__ void __launch_bounds__(TM_WPB * 32, NC == 6 ? 3 : 5) transport_march_
 // 1-column / 1-row halo (30/28 in x, 3 extra march steps per band).  Same device functions, same
 // operand order as the stage kernels: bit-identical to separate transport_march / transport_stage
 // launches.  dst must not be the source (neighbouring warps and bands still read it): Heun
-// writes to the stage buffer and the host swaps the two pointers.  Single rank, limiter off.
+// writes to the stage buffer and the host swaps the two pointers.  Limiter off.  Strips: two
+// ghost rows of the source and of the velocity on either side must be current.
 template <int NC> struct HRow {
     double c[NC]; // phi of cell row r
     double u, v; // velocity at node row r, own column
@@ -966,7 +967,7 @@ int nsdg_transport_pair(nsdg_ctx* ctx, int nfields, double* const* src, double* 
     DynState* d = ctx->dyn;
     if (r1 <= r0)
         return NSDG_OK;
-    NSDG_REQUIRE(ctx, d->nc >= 3 && d->wrap, NSDG_ESTATE, "the two-stage launch is for dG1 / dG2 on a single rank");
+    NSDG_REQUIRE(ctx, d->nc >= 3, NSDG_ESTATE, "the two-stage launch is for dG1 / dG2");
     StageArgs A = stage_args(d, nfields, src, nullptr, dst, a, b, dt, r0, r1);
     const int64_t nwarps = (d->nx + TM_OWN - 1) / TM_OWN, gx = (nwarps + TM_WPB - 1) / TM_WPB;
     A.band = transport_band_rows(r1 - r0, gx * nfields, (d->nc == 6 ? 2 : 4) * (int64_t)ctx->sm_count);

@@ -29,7 +29,11 @@ VARIANTS = (("peer", {}),
             ("nccl-rows64", {"halo_peer": -1, "march_rows": 64}),
             ("tiled", {"march_rows": -1}),
             ("transport-march", {"transport_march": 1}),
-            ("transport-tiled", {"transport_march": -1}))
+            ("transport-tiled", {"transport_march": -1}),
+            # stages 1 + 2 of the transport step in one launch: two-deep ghost rows, one exchange less
+            ("transport-fused", {"transport_fused": 1}),
+            ("transport-fused-march", {"transport_fused": 1, "transport_march": 1}),
+            ("transport-unfused", {"transport_fused": -1}))
 
 
 def all_cases(world):
@@ -124,6 +128,56 @@ def run_cases(ctx, rank, world, cases, variants=VARIANTS, log=print):
     return ok, worst, records
 
 
+def run_dg1_transport(ctx, rank, world, log=print):
+    """dG1 tracers on strips, transport only (Heun): the one-launch step (tracer and stage buffer
+    trade places, two-deep ghost rows) against two stage launches and the single-domain oracle."""
+    ok, worst = True, 0.0
+    for nx, ny in ((60, 7 * world + 2), (130, 2 * world)):
+        F, hx, hy = S.box_case(nx, ny, 3)
+        rng = np.random.default_rng(21)
+        for k in range(1, 3):
+            F["H"][k] = 0.02 * rng.standard_normal((ny, nx))
+            F["A"][k] = 0.01 * rng.standard_normal((ny, nx))
+        F["U"] = 0.3 * rng.standard_normal((ny, nx))
+        F["V"] = 0.3 * rng.standard_normal((ny, nx))
+        dt = 0.1 * min(hx, hy) / 1.5
+        ref = None
+        if rank == 0:
+            from oracle import cpu_oracle as O
+            ref = {k: F[k] for k in ("H", "A")}
+            for _ in range(3):
+                ref = {k: O.transport_step(ref[k], F["U"], F["V"], hx, hy, dt) for k in ("H", "A")}
+        first = None
+        for vname, tuning in (("fused", {"transport_fused": 1}), ("unfused", {"transport_fused": -1}),
+                              ("unfused-march", {"transport_fused": -1, "transport_march": 1})):
+            j0, nl = strips.strip_rows(ny, world, rank)
+            dyn = GpuDynamics(ctx, nx, ny, hx, hy, 3, ny_local=nl, j0=j0, tuning=tuning)
+            dyn.upload_all({k: strips.cut(F[k], world, rank) for k in ("H", "A", "U", "V")})
+            for _ in range(3):
+                dyn.transport_step(dt)
+            got = {}
+            for k in ("H", "A"):
+                mine = torch.from_numpy(dyn.download(k)).cuda()
+                parts = []
+                for r in range(world):
+                    _, nlr = strips.strip_rows(ny, world, r)
+                    buf = mine if r == rank else torch.empty((3, nlr, nx), dtype=torch.float64, device="cuda")
+                    dist.broadcast(buf, src=r)
+                    parts.append(buf.cpu().numpy())
+                got[k] = np.concatenate(parts, axis=-2)
+            dyn.close()
+            if first is None:
+                first = got
+            same = all(np.array_equal(got[k], first[k]) for k in got)
+            if rank == 0:
+                err = max(np.abs(got[k] - ref[k]).max() / np.abs(ref[k]).max() for k in got)
+                worst = max(worst, err)
+                good = err < 1e-11 and same
+                ok = ok and good
+                log(f"dG1 transport {nx}x{ny} {vname}: maxrel={err:.3e} same_bits={same} {'ok' if good else 'FAIL'}")
+    return ok, worst
+
+
 def main():
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     local = int(os.environ.get("LOCAL_RANK", rank))
@@ -138,6 +192,9 @@ def main():
     if only:
         cases = [cases[int(q)] for q in only.split(",")]
     ok, worst, _ = run_cases(ctx, rank, world, cases)
+    if not only:
+        ok1, worst1 = run_dg1_transport(ctx, rank, world)
+        ok, worst = ok and ok1, max(worst, worst1)
     flag = torch.tensor([1 if ok else 0], device="cuda")
     dist.broadcast(flag, src=0)
     ok = bool(flag.item())
