@@ -23,7 +23,7 @@ s=d.get("strong_16384sq")
 if s: print("strong", round(s["ms_per_step"],3), s["value"], "march avg", round(s["roofline"]["avg_launch_ms"],4))
 e=d["e2e"]; print("e2e", e["value"], e.get("roof",{}).get("frac"))
 c=d.get("configs",{})
-if "thermo_4096sq" in c: print("thermo", c["thermo_4096sq"]["value"], c["thermo_4096sq"]["roofline"]["frac"])
-if "cone_1024sq" in c: print("cone", c["cone_1024sq"]["value"])
+if c.get("thermo_4096sq"): print("thermo", c["thermo_4096sq"]["value"], c["thermo_4096sq"]["roofline"]["frac"])
+if c.get("cone_1024sq"): print("cone", c["cone_1024sq"]["value"])
 print("cpu", d.get("cpu_baseline",{}).get("value"), "wall", d.get("bench_wall_s"), "launches", d.get("gpu_launches"))
 PY
