@@ -25,5 +25,5 @@ e=d["e2e"]; print("e2e", e["value"], e.get("roof",{}).get("frac"))
 c=d.get("configs",{})
 if c.get("thermo_4096sq"): print("thermo", c["thermo_4096sq"]["value"], c["thermo_4096sq"]["roofline"]["frac"])
 if c.get("cone_1024sq"): print("cone", c["cone_1024sq"]["value"])
-print("cpu", d.get("cpu_baseline",{}).get("value"), "wall", d.get("bench_wall_s"), "launches", d.get("gpu_launches"))
+print("cpu", (d.get("cpu_baseline") or {}).get("value"), "wall", d.get("bench_wall_s"), "launches", d.get("gpu_launches"))
 PY
