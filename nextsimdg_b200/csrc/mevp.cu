@@ -681,10 +681,19 @@ template <bool CG> __device__ __forceinline__ double ldm(const double* p)
     return CG ? __ldcg(p) : __ldg(p);
 }
 
-template <bool CG>
-__device__ __forceinline__ void march_load(const MevpArgs& A, int r, int gi, int gip, int lane, MarchRow& R)
+// the plane row above plane row g: what plane_row(A, r + 1) is when g = plane_row(A, r), without
+// the general modulo (whose never-taken division path would sit in every copy of the march step:
+// the loop body is at the size of the 32 KB instruction-cache level)
+__device__ __forceinline__ int plane_row_above(const MevpArgs& A, int g)
 {
-    const int gr = plane_row(A, r), grp = plane_row(A, r + 1);
+    if (A.wrap)
+        return g + 1 == NSDG_GHOST + A.nyl ? NSDG_GHOST : g + 1;
+    return min(g + 1, A.nyl + 2 * NSDG_GHOST - 1);
+}
+// gr = plane_row(A, r) of the row to load, grp = plane_row(A, r + 1)
+template <bool CG>
+__device__ __forceinline__ void march_load(const MevpArgs& A, int gr, int grp, int gi, int gip, int lane, MarchRow& R)
+{
     const int k = gr * A.nx + gi;
     R.k = k;
 #pragma unroll
@@ -1020,11 +1029,13 @@ __device__ __forceinline__ const double* march_array(const MevpArgs& A, int q)
 //  * boxes that start at the warp's first column (16-byte aligned) straddle three 128-byte lines
 //    and overlap the neighbours': DRAM reads x1.5.  Boxes on 256-byte boundaries (warp w of the
 //    CTA takes columns c0 + 32 w ...; nx % 16 == 0) bring that down to x1.13.
-// What is left (this variant): 0.92 against 0.80 ms under ncu.  The wait for loaded rows shrinks
-// (1.15 -> 0.77 per issue) but the loop body grows past the 32 KB instruction-cache level it just
-// fits (33.1 -> 34.7 KB: instruction-fetch stalls 0.14 -> 0.36 per issue, hit rate 99.0 -> 93.4 %)
-// and the rest is eaten by the extra DRAM traffic.  Kept as an opt-in arm (march_ring = 3, single
-// rank); bit-identical.  Needs an even nx (16-byte strides of the tensor maps).
+// What is left (this variant): 0.92 against 0.80 ms under ncu when the loop body was 33.1 KB
+// (34.7 KB with the prefetch: past the 32 KB instruction-cache level, instruction-fetch stalls 0.14
+// -> 0.36 per issue), and still 0.98 against 0.83 ms now that the body is 29.7 KB (31.1 KB with
+// the prefetch, hit rate 99.6 %): DRAM reads x1.24 and the wait for loaded rows is where it was
+// (1.66 against 1.74 per issue) -- box prefetches of 256-byte rows cost bandwidth and do not arrive
+// ahead of the demand loads.  Kept as an opt-in arm (march_ring = 3, single rank); bit-identical.
+// Needs an even nx (16-byte strides of the tensor maps).
 constexpr int PF_MAPS = 9; // S11, S12, S22, pg, nd, u, v, uo, vo
 struct alignas(64) PfMaps {
     CUtensorMap m[PF_MAPS];
@@ -1052,7 +1063,7 @@ __device__ __forceinline__ void pf_rows(const PfMaps& M, int x, int row)
 
 template <bool PEER, bool CG, int RING, int WPB>
 __device__ __forceinline__ void march_step(const MevpArgs& A, int ra, int gi, int gip, int lane, bool own,
-    MarchRow& X, MarchRow& Y, MarchRow& Z, double (&d2p)[7], RingSmem<WPB>* R, int s, int nsteps, int c0, int col)
+    MarchRow& X, MarchRow& Y, MarchRow& Z, double (&d2p)[7], RingSmem<WPB>* R, int s, int nsteps, int c0, int col, int& grn)
 {
     if (RING == 2) {
         // row s + 1 + LR_D of the march goes out to shared memory, row s + 1 comes in from it
@@ -1069,7 +1080,10 @@ __device__ __forceinline__ void march_step(const MevpArgs& A, int ra, int gi, in
         }
         ring_load(A, *R, ra + 1, s + 1, gi, col, lane, Z);
     } else {
-        march_load<CG>(A, ra + 1, gi, gip, lane, Z); // consumed by the next step (wasted on the last one)
+        // grn = plane row of row ra + 1, carried from step to step
+        const int grp = plane_row_above(A, grn);
+        march_load<CG>(A, grn, grp, gi, gip, lane, Z); // consumed by the next step (wasted on the last one)
+        grn = grp;
     }
 
     // ---- A: stress p+1 of cell row ra
@@ -1181,6 +1195,7 @@ __device__ __forceinline__ void march_body(const MevpArgs& A, const PfMaps* M)
 
     MarchRow X = {}, Y, Z;
     X.mdt = 1.;
+    int grn = plane_row(A, b0 - 1); // plane row of the row the next march_load takes
     double d2p[7] = { 0., 0., 0., 0., 0., 0., 0. };
     {
         const int g0 = plane_row(A, b0 - 2);
@@ -1203,12 +1218,12 @@ __device__ __forceinline__ void march_body(const MevpArgs& A, const PfMaps* M)
                 ring_fill(A, *R, b0 - 2 + k, k, c0, lane);
         ring_load(A, *R, b0 - 2, 0, gi, col, lane, Y);
     } else {
-        march_load<CG>(A, b0 - 2, gi, gip, lane, Y);
+        march_load<CG>(A, plane_row(A, b0 - 2), grn, gi, gip, lane, Y);
     }
     // step s works on row ra = b0 - 2 + s and stores the owned row ra - 1 when 3 <= s; the first
     // steps run phases C / D on the zero-initialised records (finite values, never stored)
 #define NSDG_STEP(s, X, Y, Z) \
-    march_step<PEER, CG, RING, WPB>(A, b0 - 2 + (s), gi, gip, lane, own_col && (s) >= 3, X, Y, Z, d2p, R, (s), nsteps, c0, col)
+    march_step<PEER, CG, RING, WPB>(A, b0 - 2 + (s), gi, gip, lane, own_col && (s) >= 3, X, Y, Z, d2p, R, (s), nsteps, c0, col, grn)
     int s = 0;
 #pragma unroll 1
     for (; s + 2 < nsteps; s += 3) {
