@@ -1,9 +1,16 @@
-// DG tracer transport: one fused kernel per Runge-Kutta stage.
+// DG tracer transport: fused Runge-Kutta stage kernels.
 //
 // NOT IN THE REFERENCE SNAPSHOT (its CMakeLists.txt:43-46 comments "dynamics" out); the scheme
 // is the one stated in oracle/dg_transport.c and DESIGN.md, parity is against that oracle only.
 //
-// One thread owns one cell and gathers everything it needs (no atomics, deterministic):
+// Three forms of the same arithmetic (dg1_* / dg2_* device functions), bit-identical to one another:
+//   transport_stage_kernel        one thread per cell, one stage per launch (dG0; small grids)
+//   transport_march_kernel        a warp marches up a band of rows, one stage per launch
+//   transport_pair_march_kernel   the same march with TWO stages per launch (the whole Heun step of
+//                                 dG1, stages 1 + 2 of SSP-RK3 for dG2), stage 1 kept in registers
+//
+// transport_stage_kernel: one thread owns one cell and gathers everything it needs (no atomics,
+// deterministic):
 //   volume term + the four edge upwind fluxes + inverse mass + the RK stage combination
 //     dst = a*base + b*(src + dt*L(src))
 // for one tracer (blockIdx.z selects it).  Each thread computes both fluxes of its own
