@@ -43,6 +43,29 @@ def test_struct_layout_matches_header():
         assert getattr(m, f) == getattr(dm, f), f
 
 
+def test_struct_offsets_match_the_c_header(tmp_path):
+    """Every field of every POD of the C ABI sits where the ctypes mirror puts it: a C program
+    compiled against include/nsdg_gpu.h prints sizeof / offsetof, compared with ctypes."""
+    import subprocess
+    pods = {"nsdg_thermo_params": _abi.ThermoParams, "nsdg_mevp_params": _abi.MevpParams,
+            "nsdg_dyn_config": _abi.DynConfig, "nsdg_dyn_tuning": _abi.DynTuning}
+    lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "nsdg_gpu.h"', "int main(void) {"]
+    for cname, cls in pods.items():
+        lines.append(f'printf("{cname} %zu\\n", sizeof({cname}));')
+        for f, _ in cls._fields_:
+            lines.append(f'printf("{cname}.{f} %zu\\n", offsetof({cname}, {f}));')
+    lines += ["return 0; }"]
+    src = tmp_path / "layout.c"
+    src.write_text("\n".join(lines))
+    exe = tmp_path / "layout"
+    subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
+    got = dict(ln.split() for ln in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.splitlines())
+    for cname, cls in pods.items():
+        assert int(got[cname]) == ctypes.sizeof(cls), cname
+        for f, _ in cls._fields_:
+            assert int(got[f"{cname}.{f}"]) == getattr(cls, f).offset, f"{cname}.{f}"
+
+
 @pytest.mark.skipif(os.path.exists("/dev/nvidia0"), reason="GPU present")
 def test_no_cpu_fallback():
     """On a box without a GPU the product path must fail loudly, not compute on the CPU."""
