@@ -1,4 +1,5 @@
 #!/bin/bash
+# (historical record of an experiment: the NSDG_MEVP_PF_* / NSDG_HEUN_* environment knobs it sets existed only while it ran)
 # sweep: resident CTAs per SM / band height of the fused Heun kernel on the 1024^2 cone
 mkdir -p gpurun_out
 run() {

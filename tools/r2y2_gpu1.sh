@@ -1,4 +1,5 @@
 #!/bin/bash
+# (historical record of an experiment: the NSDG_MEVP_PF_* / NSDG_HEUN_* environment knobs it sets existed only while it ran)
 # experiment: bulk L2 prefetch arm, elected-lane CTA-wide variant (pf_cta = 2)
 mkdir -p gpurun_out
 NSDG_MEVP_PF_DIST=2 NSDG_MEVP_PF_CTA=2 timeout 300 python tools/dyn_digest.py march_ring=3 > gpurun_out/r2y2_digest_pf.txt 2>&1; echo "pf rc=$?"; tail -1 gpurun_out/r2y2_digest_pf.txt

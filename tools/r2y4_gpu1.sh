@@ -1,4 +1,5 @@
 #!/bin/bash
+# (historical record of an experiment: the NSDG_MEVP_PF_* / NSDG_HEUN_* environment knobs it sets existed only while it ran)
 # experiment: bulk L2 prefetch arm, per-warp tensor boxes (3 rows x planes) every third step
 mkdir -p gpurun_out
 NSDG_MEVP_PF_DIST=2 timeout 300 python tools/dyn_digest.py march_ring=3 > gpurun_out/r2y4_digest_pf.txt 2>&1; echo "pf rc=$?"; tail -1 gpurun_out/r2y4_digest_pf.txt

@@ -1,4 +1,5 @@
 #!/bin/bash
+# (historical record of an experiment: the NSDG_MEVP_PF_* / NSDG_HEUN_* environment knobs it sets existed only while it ran)
 # experiment: bulk L2 prefetch arm of the marching sub-cycle kernel (march_ring = 3)
 mkdir -p gpurun_out
 timeout 300 python tools/dyn_digest.py > gpurun_out/r2y_digest_default.txt 2>&1; echo "default rc=$?"; tail -1 gpurun_out/r2y_digest_default.txt

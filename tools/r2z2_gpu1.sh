@@ -1,4 +1,5 @@
 #!/bin/bash
+# (historical record of an experiment: the NSDG_MEVP_PF_* / NSDG_HEUN_* environment knobs it sets existed only while it ran)
 # all stall reasons of the marching kernel with and without the elected-lane bulk L2 prefetch
 mkdir -p gpurun_out
 for cfg in "0 0 0" "3 2 2"; do
